@@ -1,0 +1,149 @@
+"""ctypes binding of libede_sm100.so (the C ABI declared in include/ede.h).
+
+No torch types cross this boundary: pointers are ``tensor.data_ptr()`` integers, the
+stream is ``torch.cuda.current_stream().cuda_stream``.  There is NO fallback: if the
+shared library is missing or a call fails, a RuntimeError is raised.
+"""
+import ctypes as C
+import os
+from ctypes import POINTER, Structure, Union, c_double, c_float, c_int32, c_int64, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libede_sm100.so")
+
+F32, BF16 = 0, 1
+ACT_NONE, ACT_RELU, ACT_SWISH, ACT_SIGMOID = 0, 1, 2, 3
+NHWC, NCHW = 0, 1
+(OP_CONV, OP_DWCONV, OP_SE_FC, OP_SE_SCALE, OP_RESIZE, OP_MAXPOOL, OP_ELTWISE, OP_TO_NHWC, OP_TO_NCHW,
+ OP_ZERO) = range(1, 11)
+
+
+def _ints(*names):
+    return [(n, c_int32) for n in names]
+
+
+class EdeConv(Structure):
+    _fields_ = [("x", c_void_p), ("y", c_void_p), ("res", c_void_p), ("scale", c_void_p), ("shift", c_void_p),
+                ("w_umma", c_void_p), ("w_direct", c_void_p)] + _ints(
+        "n", "h", "w", "cin_p", "x_cs", "x_co", "oh", "ow", "cout_p", "y_cs", "y_co", "res_cs", "res_co",
+        "kh", "kw", "sh", "sw", "pt", "pl", "act", "act_c_end", "x_dtype", "y_dtype", "x_layout", "relu_in",
+        "w_umma_cout_p", "w_umma_cin_p", "force_direct")
+
+
+class EdeUmmaCfg(Structure):
+    _fields_ = _ints("eligible", "a_mode", "ck", "swizzle", "bh", "bw", "pitch", "box_rows", "m_tiles", "n_pad",
+                     "n_tiles", "a_stages", "b_stages", "a_stage_bytes", "b_stage_bytes", "smem_bytes",
+                     "tmem_cols", "tiles_w", "tiles_h", "flat") + [("useful_frac", c_double)]
+
+
+class EdeDwConv(Structure):
+    _fields_ = [("x", c_void_p), ("y", c_void_p), ("w", c_void_p), ("scale", c_void_p), ("shift", c_void_p),
+                ("pool_sum", c_void_p)] + _ints(
+        "n", "h", "w_", "c_p", "x_cs", "x_co", "oh", "ow", "y_cs", "y_co", "k", "s", "pt", "pl", "act", "dtype")
+
+
+class EdeSeFc(Structure):
+    _fields_ = [("pool_sum", c_void_p), ("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p),
+                ("gate", c_void_p)] + _ints("n", "c", "c_p", "csq") + [("inv_hw", c_float)]
+
+
+class EdeSeScale(Structure):
+    _fields_ = [("x", c_void_p), ("y", c_void_p), ("gate", c_void_p)] + _ints(
+        "n", "hw", "c_p", "x_cs", "x_co", "y_cs", "y_co", "dtype")
+
+
+class EdeResize(Structure):
+    _fields_ = [("x", c_void_p), ("y", c_void_p)] + _ints(
+        "n", "h", "w", "c_p", "x_cs", "x_co", "oh", "ow", "y_cs", "y_co", "x_dtype", "y_dtype")
+
+
+class EdeMaxPool(Structure):
+    _fields_ = [("x", c_void_p), ("y", c_void_p)] + _ints(
+        "n", "h", "w", "c_p", "x_cs", "x_co", "oh", "ow", "y_cs", "y_co", "dtype")
+
+
+class EdeEltwise(Structure):
+    _fields_ = [("x", c_void_p), ("x2", c_void_p), ("y", c_void_p)] + _ints(
+        "n_pix", "c_p", "x_cs", "x_co", "x2_cs", "x2_co", "y_cs", "y_co", "act", "dtype")
+
+
+class EdeLayout(Structure):
+    _fields_ = [("src", c_void_p), ("dst", c_void_p)] + _ints("n", "c", "h", "w", "c_p", "cs", "co", "dtype")
+
+
+class _Zero(Structure):
+    _fields_ = [("p", c_void_p), ("bytes", c_int64)]
+
+
+class _OpU(Union):
+    _fields_ = [("conv", EdeConv), ("dw", EdeDwConv), ("se_fc", EdeSeFc), ("se_scale", EdeSeScale),
+                ("resize", EdeResize), ("maxpool", EdeMaxPool), ("eltwise", EdeEltwise), ("layout", EdeLayout),
+                ("zero", _Zero)]
+
+
+class EdeOp(Structure):
+    _fields_ = [("kind", c_int32), ("_pad", c_int32), ("u", _OpU)]
+
+
+OP_FIELD = {OP_CONV: "conv", OP_DWCONV: "dw", OP_SE_FC: "se_fc", OP_SE_SCALE: "se_scale", OP_RESIZE: "resize",
+            OP_MAXPOOL: "maxpool", OP_ELTWISE: "eltwise", OP_TO_NHWC: "layout", OP_TO_NCHW: "layout",
+            OP_ZERO: "zero"}
+
+# every symbol include/ede.h declares (checked by tests/test_cabi.py without a GPU)
+EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_dwconv2d", "ede_se_fc", "ede_se_scale",
+           "ede_resize_bilinear_ac", "ede_resize_planes_f32", "ede_maxpool3x3s2", "ede_eltwise", "ede_nchw_to_nhwc", "ede_nhwc_to_nchw",
+           "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_plan_run",
+           "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available"]
+
+_lib = None
+
+
+def lib():
+    """The loaded library; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(efficientdepthestimation_b200 has no CPU or PyTorch fallback)")
+    L = C.CDLL(LIB_PATH)
+    for name, st in (("ede_conv2d", EdeConv), ("ede_dwconv2d", EdeDwConv), ("ede_se_fc", EdeSeFc),
+                     ("ede_se_scale", EdeSeScale), ("ede_resize_bilinear_ac", EdeResize),
+                     ("ede_maxpool3x3s2", EdeMaxPool), ("ede_eltwise", EdeEltwise),
+                     ("ede_nchw_to_nhwc", EdeLayout), ("ede_nhwc_to_nchw", EdeLayout)):
+        f = getattr(L, name)
+        f.argtypes = [POINTER(st), c_void_p]
+        f.restype = c_int32
+    L.ede_conv2d_umma_config.argtypes = [POINTER(EdeConv), POINTER(EdeUmmaCfg)]
+    L.ede_conv2d_umma_config.restype = c_int32
+    L.ede_fill_zero.argtypes = [c_void_p, c_int64, c_void_p]
+    L.ede_fill_zero.restype = c_int32
+    L.ede_resize_planes_f32.argtypes = [c_void_p, c_void_p, c_int64, c_int32, c_int32, c_int32, c_int32, c_void_p]
+    L.ede_resize_planes_f32.restype = c_int32
+    L.ede_sobel.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p]
+    L.ede_sobel.restype = c_int32
+    L.ede_sobel_loss_metrics.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]
+    L.ede_sobel_loss_metrics.restype = c_int32
+    L.ede_edge_counts.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_float, c_void_p, c_void_p]
+    L.ede_edge_counts.restype = c_int32
+    L.ede_plan_run.argtypes = [POINTER(EdeOp), c_int32, c_void_p]
+    L.ede_plan_run.restype = c_int32
+    L.ede_launch_count.argtypes = [c_int32]
+    L.ede_launch_count.restype = c_int64
+    L.ede_version.restype = c_int32
+    L.ede_last_error.restype = C.c_char_p
+    L.ede_umma_available.restype = c_int32
+    _lib = L
+    return L
+
+
+def check(rc: int, what: str = "libede"):
+    if rc != 0:
+        raise RuntimeError(f"{what} failed (code {rc}): {lib().ede_last_error().decode(errors='replace')}")
+
+
+def umma_config(conv: EdeConv) -> EdeUmmaCfg:
+    cfg = EdeUmmaCfg()
+    check(lib().ede_conv2d_umma_config(C.byref(conv), C.byref(cfg)), "ede_conv2d_umma_config")
+    return cfg

@@ -1,0 +1,369 @@
+// bandwidth.cu -- the HBM-bound kernels of the ReSIDE forward path (NHWC, 16-byte vectors).
+//
+// Every thread owns one 8-channel vector (16 B of bf16 / 32 B of fp32) of one pixel, with the
+// channel-group index fastest across a warp so that global accesses are fully coalesced.
+#include "common.cuh"
+
+namespace ede {
+
+static inline unsigned grid_for(long long work, int block) {
+    long long g = (work + block - 1) / block;
+    if (g < 1) g = 1;
+    if (g > 0x7fffffffLL) g = 0x7fffffffLL;
+    return (unsigned)g;
+}
+
+// ------------------------------------------------------------------ depthwise conv + BN + act + SE squeeze
+template <typename T>
+__global__ void __launch_bounds__(256) dwconv_kernel(const EdeDwConv a) {
+    extern __shared__ float pool_s[];                     // [c_p] per-block partial sums (if pool_sum)
+    const int cg = a.c_p >> 3;
+    const int n = blockIdx.y;
+    const long long per_img = (long long)a.oh * a.ow * cg;
+    if (a.pool_sum) {
+        for (int i = threadIdx.x; i < a.c_p; i += blockDim.x) pool_s[i] = 0.f;
+        __syncthreads();
+    }
+    const T* __restrict__ x = reinterpret_cast<const T*>(a.x);
+    T* __restrict__ y = reinterpret_cast<T*>(a.y);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int g = (int)(i % cg);
+        const long long pix = i / cg;
+        const int ow = (int)(pix % a.ow), oh = (int)(pix / a.ow);
+        const int c = g << 3;
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        const int ih0 = oh * a.s - a.pt, iw0 = ow * a.s - a.pl;
+        for (int ky = 0; ky < a.k; ++ky) {
+            const int ih = ih0 + ky;
+            if (ih < 0 || ih >= a.h) continue;
+            for (int kx = 0; kx < a.k; ++kx) {
+                const int iw = iw0 + kx;
+                if (iw < 0 || iw >= a.w_) continue;
+                float xv[8], wv[8];
+                load8<T>(x + (((long long)n * a.h + ih) * a.w_ + iw) * a.x_cs + a.x_co + c, xv);
+                load8<float>(a.w + (long long)(ky * a.k + kx) * a.c_p + c, wv);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] = fmaf(xv[j], wv[j], acc[j]);
+            }
+        }
+        float sc[8], sf[8];
+        load8<float>(a.scale + c, sc);
+        load8<float>(a.shift + c, sf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = apply_act(fmaf(acc[j], sc[j], sf[j]), a.act);
+        store8<T>(y + (((long long)n * a.oh + oh) * a.ow + ow) * a.y_cs + a.y_co + c, acc);
+        if (a.pool_sum) {
+            // the squeeze must see exactly what the next layer reads: the value rounded to T
+            float rv[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) rv[j] = round_as<T>(acc[j]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) atomicAdd(&pool_s[c + j], rv[j]);
+        }
+    }
+    if (a.pool_sum) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < a.c_p; i += blockDim.x) atomicAdd(a.pool_sum + (long long)n * a.c_p + i, pool_s[i]);
+    }
+}
+
+// ------------------------------------------------------------------ squeeze-excite FCs
+__global__ void __launch_bounds__(256) se_fc_kernel(const EdeSeFc a) {
+    extern __shared__ float sm[];                          // mean[c_p] | hidden[csq]
+    float* mean = sm;
+    float* hid = sm + a.c_p;
+    const int n = blockIdx.x;
+    for (int i = threadIdx.x; i < a.c_p; i += blockDim.x)
+        mean[i] = i < a.c ? a.pool_sum[(long long)n * a.c_p + i] * a.inv_hw : 0.f;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    for (int j = warp; j < a.csq; j += nw) {
+        float s = 0.f;
+        for (int c = lane; c < a.c; c += 32) s = fmaf(a.w1[(long long)j * a.c_p + c], mean[c], s);
+        s = warp_sum(s);
+        if (lane == 0) hid[j] = apply_act(s + a.b1[j], EDE_ACT_SWISH);
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < a.c_p; c += blockDim.x) {
+        float s = 0.f;
+        if (c < a.c) {
+            s = a.b2[c];
+            for (int j = 0; j < a.csq; ++j) s = fmaf(a.w2[(long long)c * a.csq + j], hid[j], s);
+        }
+        a.gate[(long long)n * a.c_p + c] = c < a.c ? apply_act(s, EDE_ACT_SIGMOID) : 0.f;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) se_scale_kernel(const EdeSeScale a) {
+    const int cg = a.c_p >> 3;
+    const long long total = (long long)a.n * a.hw * cg;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cg) << 3;
+        const long long pix = i / cg;
+        const int n = (int)(pix / a.hw);
+        float v[8], g[8];
+        load8<T>(reinterpret_cast<const T*>(a.x) + pix * a.x_cs + a.x_co + c, v);
+        load8<float>(a.gate + (long long)n * a.c_p + c, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] *= g[j];
+        store8<T>(reinterpret_cast<T*>(a.y) + pix * a.y_cs + a.y_co + c, v);
+    }
+}
+
+// ------------------------------------------------------------------ bilinear resize, align_corners=True
+template <typename TX, typename TY>
+__global__ void __launch_bounds__(256) resize_kernel(const EdeResize a, float scale_h, float scale_w) {
+    const int cg = a.c_p >> 3;
+    const long long total = (long long)a.n * a.oh * a.ow * cg;
+    const TX* __restrict__ x = reinterpret_cast<const TX*>(a.x);
+    TY* __restrict__ y = reinterpret_cast<TY*>(a.y);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cg) << 3;
+        long long pix = i / cg;
+        const int ow = (int)(pix % a.ow);
+        pix /= a.ow;
+        const int oh = (int)(pix % a.oh);
+        const int n = (int)(pix / a.oh);
+        // ATen upsample_bilinear2d (align_corners): src = scale * dst, lambda in fp32
+        const float sy = scale_h * oh, sx = scale_w * ow;
+        const int y0 = (int)sy, x0 = (int)sx;
+        const int y1 = y0 + (y0 < a.h - 1 ? 1 : 0), x1 = x0 + (x0 < a.w - 1 ? 1 : 0);
+        const float ly = sy - y0, lx = sx - x0;
+        const float hy = 1.f - ly, hx = 1.f - lx;
+        const long long base = (long long)n * a.h;
+        float v00[8], v01[8], v10[8], v11[8], o[8];
+        load8<TX>(x + ((base + y0) * a.w + x0) * a.x_cs + a.x_co + c, v00);
+        load8<TX>(x + ((base + y0) * a.w + x1) * a.x_cs + a.x_co + c, v01);
+        load8<TX>(x + ((base + y1) * a.w + x0) * a.x_cs + a.x_co + c, v10);
+        load8<TX>(x + ((base + y1) * a.w + x1) * a.x_cs + a.x_co + c, v11);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            o[j] = hy * (hx * v00[j] + lx * v01[j]) + ly * (hx * v10[j] + lx * v11[j]);
+        store8<TY>(y + (((long long)n * a.oh + oh) * a.ow + ow) * a.y_cs + a.y_co + c, o);
+    }
+}
+
+// fp32 planes ([planes][h][w], i.e. NCHW with any C): the post-forward depth-map resize
+__global__ void __launch_bounds__(256) resize_planes_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                            long long planes, int h, int w, int oh, int ow,
+                                                            float scale_h, float scale_w) {
+    const long long total = planes * oh * ow;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int ox = (int)(i % ow);
+        const long long r = i / ow;
+        const int oy = (int)(r % oh);
+        const long long pl = r / oh;
+        const float sy = scale_h * oy, sx = scale_w * ox;
+        const int y0 = (int)sy, x0 = (int)sx;
+        const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
+        const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
+        const float* p = x + pl * h * w;
+        y[i] = hy * (hx * p[(long long)y0 * w + x0] + lx * p[(long long)y0 * w + x1]) +
+               ly * (hx * p[(long long)y1 * w + x0] + lx * p[(long long)y1 * w + x1]);
+    }
+}
+
+// ------------------------------------------------------------------ 3x3 s2 p1 max pooling
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool_kernel(const EdeMaxPool a) {
+    const int cg = a.c_p >> 3;
+    const long long total = (long long)a.n * a.oh * a.ow * cg;
+    const T* __restrict__ x = reinterpret_cast<const T*>(a.x);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cg) << 3;
+        long long pix = i / cg;
+        const int ow = (int)(pix % a.ow);
+        pix /= a.ow;
+        const int oh = (int)(pix % a.oh);
+        const int n = (int)(pix / a.oh);
+        float m[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = -INFINITY;
+        for (int ky = 0; ky < 3; ++ky) {
+            const int ih = oh * 2 - 1 + ky;
+            if (ih < 0 || ih >= a.h) continue;
+            for (int kx = 0; kx < 3; ++kx) {
+                const int iw = ow * 2 - 1 + kx;
+                if (iw < 0 || iw >= a.w) continue;
+                float v[8];
+                load8<T>(x + (((long long)n * a.h + ih) * a.w + iw) * a.x_cs + a.x_co + c, v);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) m[j] = fmaxf(m[j], v[j]);
+            }
+        }
+        store8<T>(reinterpret_cast<T*>(a.y) + (((long long)n * a.oh + oh) * a.ow + ow) * a.y_cs + a.y_co + c, m);
+    }
+}
+
+// ------------------------------------------------------------------ elementwise act(x) (+ x2)
+template <typename T>
+__global__ void __launch_bounds__(256) eltwise_kernel(const EdeEltwise a) {
+    const int cg = a.c_p >> 3;
+    const long long total = (long long)a.n_pix * cg;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % cg) << 3;
+        const long long pix = i / cg;
+        float v[8];
+        load8<T>(reinterpret_cast<const T*>(a.x) + pix * a.x_cs + a.x_co + c, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], a.act);
+        if (a.x2) {
+            float w[8];
+            load8<T>(reinterpret_cast<const T*>(a.x2) + pix * a.x2_cs + a.x2_co + c, w);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] += w[j];
+        }
+        store8<T>(reinterpret_cast<T*>(a.y) + pix * a.y_cs + a.y_co + c, v);
+    }
+}
+
+// ------------------------------------------------------------------ layout changes at the model boundary
+template <typename T>
+__global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const EdeLayout a) {
+    const int cg = a.c_p >> 3;
+    const long long hw = (long long)a.h * a.w;
+    const long long total = (long long)a.n * hw * cg;
+    const float* __restrict__ src = reinterpret_cast<const float*>(a.src);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        // pixel fastest so that the per-channel plane reads coalesce
+        const long long pix = i % ((long long)a.n * hw);
+        const int c = (int)(i / ((long long)a.n * hw)) << 3;
+        const int n = (int)(pix / hw);
+        const long long p = pix - (long long)n * hw;
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = (c + j < a.c) ? src[((long long)n * a.c + c + j) * hw + p] : 0.f;
+        store8<T>(reinterpret_cast<T*>(a.dst) + pix * a.cs + a.co + c, v);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) nhwc_to_nchw_kernel(const EdeLayout a) {
+    const long long hw = (long long)a.h * a.w;
+    const long long total = (long long)a.n * a.c * hw;
+    const T* __restrict__ src = reinterpret_cast<const T*>(a.src);
+    float* __restrict__ dst = reinterpret_cast<float*>(a.dst);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long p = i % hw;
+        const long long r = i / hw;
+        const int c = (int)(r % a.c);
+        const long long n = r / a.c;
+        dst[i] = Elt<T>::ld(src + (n * hw + p) * a.cs + a.co + c);
+    }
+}
+
+}  // namespace ede
+
+using namespace ede;
+
+extern "C" {
+
+int ede_dwconv2d(const EdeDwConv* a, void* stream) {
+    EDE_REQUIRE(a && a->x && a->y && a->w && a->scale && a->shift, "ede_dwconv2d: null argument");
+    EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_dwconv2d: channel counts must be multiples of 8");
+    EDE_REQUIRE(a->n > 0 && a->oh > 0 && a->ow > 0 && a->k > 0 && a->s > 0, "ede_dwconv2d: bad shape");
+    const long long per_img = (long long)a->oh * a->ow * (a->c_p >> 3);
+    long long gx = (per_img + 256 * 4 - 1) / (256 * 4);
+    if (gx < 1) gx = 1;
+    if (gx > 2048) gx = 2048;
+    dim3 grid((unsigned)gx, (unsigned)a->n);
+    const size_t smem = a->pool_sum ? (size_t)a->c_p * sizeof(float) : 0;
+    EDE_DISPATCH_DTYPE(a->dtype, T, (dwconv_kernel<T><<<grid, 256, smem, (cudaStream_t)stream>>>(*a)));
+    EDE_LAUNCH_CHECK("dwconv_kernel");
+    return EDE_OK;
+}
+
+int ede_se_fc(const EdeSeFc* a, void* stream) {
+    EDE_REQUIRE(a && a->pool_sum && a->w1 && a->b1 && a->w2 && a->b2 && a->gate, "ede_se_fc: null argument");
+    EDE_REQUIRE(a->n > 0 && a->c > 0 && a->c <= a->c_p && a->csq > 0, "ede_se_fc: bad shape");
+    const size_t smem = (size_t)(a->c_p + a->csq) * sizeof(float);
+    EDE_REQUIRE(smem <= 48 * 1024, "ede_se_fc: too many channels (%d)", a->c_p);
+    se_fc_kernel<<<a->n, 256, smem, (cudaStream_t)stream>>>(*a);
+    EDE_LAUNCH_CHECK("se_fc_kernel");
+    return EDE_OK;
+}
+
+int ede_se_scale(const EdeSeScale* a, void* stream) {
+    EDE_REQUIRE(a && a->x && a->y && a->gate, "ede_se_scale: null argument");
+    EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_se_scale: channel counts must be multiples of 8");
+    const long long total = (long long)a->n * a->hw * (a->c_p >> 3);
+    EDE_DISPATCH_DTYPE(a->dtype, T, (se_scale_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*a)));
+    EDE_LAUNCH_CHECK("se_scale_kernel");
+    return EDE_OK;
+}
+
+int ede_resize_bilinear_ac(const EdeResize* a, void* stream) {
+    EDE_REQUIRE(a && a->x && a->y, "ede_resize_bilinear_ac: null argument");
+    EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_resize_bilinear_ac: channel counts must be multiples of 8");
+    EDE_REQUIRE(a->n > 0 && a->h > 0 && a->w > 0 && a->oh > 0 && a->ow > 0, "ede_resize_bilinear_ac: bad shape");
+    const float sh = a->oh > 1 ? (float)(a->h - 1) / (float)(a->oh - 1) : 0.f;
+    const float sw = a->ow > 1 ? (float)(a->w - 1) / (float)(a->ow - 1) : 0.f;
+    const long long total = (long long)a->n * a->oh * a->ow * (a->c_p >> 3);
+    const unsigned g = grid_for(total, 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (a->x_dtype == EDE_BF16 && a->y_dtype == EDE_BF16) resize_kernel<__nv_bfloat16, __nv_bfloat16><<<g, 256, 0, st>>>(*a, sh, sw);
+    else if (a->x_dtype == EDE_BF16) resize_kernel<__nv_bfloat16, float><<<g, 256, 0, st>>>(*a, sh, sw);
+    else if (a->y_dtype == EDE_BF16) resize_kernel<float, __nv_bfloat16><<<g, 256, 0, st>>>(*a, sh, sw);
+    else resize_kernel<float, float><<<g, 256, 0, st>>>(*a, sh, sw);
+    EDE_LAUNCH_CHECK("resize_kernel");
+    return EDE_OK;
+}
+
+int ede_resize_planes_f32(const float* x, float* y, int64_t planes, int32_t h, int32_t w, int32_t oh, int32_t ow,
+                          void* stream) {
+    EDE_REQUIRE(x && y && planes > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "ede_resize_planes_f32: bad arguments");
+    const float sh = oh > 1 ? (float)(h - 1) / (float)(oh - 1) : 0.f;
+    const float sw = ow > 1 ? (float)(w - 1) / (float)(ow - 1) : 0.f;
+    resize_planes_kernel<<<grid_for(planes * oh * ow, 256), 256, 0, (cudaStream_t)stream>>>(x, y, planes, h, w, oh, ow,
+                                                                                            sh, sw);
+    EDE_LAUNCH_CHECK("resize_planes_kernel");
+    return EDE_OK;
+}
+
+int ede_maxpool3x3s2(const EdeMaxPool* a, void* stream) {
+    EDE_REQUIRE(a && a->x && a->y, "ede_maxpool3x3s2: null argument");
+    EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_maxpool3x3s2: channel counts must be multiples of 8");
+    const long long total = (long long)a->n * a->oh * a->ow * (a->c_p >> 3);
+    EDE_DISPATCH_DTYPE(a->dtype, T, (maxpool_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*a)));
+    EDE_LAUNCH_CHECK("maxpool_kernel");
+    return EDE_OK;
+}
+
+int ede_eltwise(const EdeEltwise* a, void* stream) {
+    EDE_REQUIRE(a && a->x && a->y, "ede_eltwise: null argument");
+    EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co | a->x2_cs | a->x2_co) & 7) == 0, "ede_eltwise: channel counts must be multiples of 8");
+    const long long total = (long long)a->n_pix * (a->c_p >> 3);
+    EDE_DISPATCH_DTYPE(a->dtype, T, (eltwise_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*a)));
+    EDE_LAUNCH_CHECK("eltwise_kernel");
+    return EDE_OK;
+}
+
+int ede_nchw_to_nhwc(const EdeLayout* a, void* stream) {
+    EDE_REQUIRE(a && a->src && a->dst, "ede_nchw_to_nhwc: null argument");
+    EDE_REQUIRE(((a->c_p | a->cs | a->co) & 7) == 0 && a->c <= a->c_p, "ede_nchw_to_nhwc: bad channel layout");
+    const long long total = (long long)a->n * a->h * a->w * (a->c_p >> 3);
+    EDE_DISPATCH_DTYPE(a->dtype, T, (nchw_to_nhwc_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*a)));
+    EDE_LAUNCH_CHECK("nchw_to_nhwc_kernel");
+    return EDE_OK;
+}
+
+int ede_nhwc_to_nchw(const EdeLayout* a, void* stream) {
+    EDE_REQUIRE(a && a->src && a->dst, "ede_nhwc_to_nchw: null argument");
+    const long long total = (long long)a->n * a->c * a->h * a->w;
+    EDE_DISPATCH_DTYPE(a->dtype, T, (nhwc_to_nchw_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*a)));
+    EDE_LAUNCH_CHECK("nhwc_to_nchw_kernel");
+    return EDE_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,109 @@
+// common.cuh -- shared device/host helpers for libede_sm100.so (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/ede.h"
+
+namespace ede {
+
+// ---------------------------------------------------------------- error plumbing (api.cu)
+void set_error(const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what);
+void count_launch(int n = 1);
+
+#define EDE_REQUIRE(cond, ...)                                   \
+    do {                                                         \
+        if (!(cond)) {                                           \
+            ::ede::set_error(__VA_ARGS__);                       \
+            return EDE_E_ARG;                                    \
+        }                                                        \
+    } while (0)
+
+#define EDE_LAUNCH_CHECK(what)                                                  \
+    do {                                                                        \
+        ::ede::count_launch();                                                  \
+        int _rc = ::ede::check_cuda(cudaGetLastError(), what);                  \
+        if (_rc) return _rc;                                                    \
+    } while (0)
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline int round_up(int a, int b) { return ceil_div(a, b) * b; }
+static inline size_t dtype_size(int dt) { return dt == EDE_BF16 ? 2 : 4; }
+
+// ---------------------------------------------------------------- typed element access
+template <typename T> struct Elt;
+template <> struct Elt<float> {
+    static __device__ __forceinline__ float ld(const float* p) { return *p; }
+    static __device__ __forceinline__ void st(float* p, float v) { *p = v; }
+};
+template <> struct Elt<__nv_bfloat16> {
+    static __device__ __forceinline__ float ld(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+    static __device__ __forceinline__ void st(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+};
+
+// 8 consecutive channels (one 16-byte bf16 vector / two float4) <-> 8 floats
+template <typename T> __device__ __forceinline__ void load8(const T* p, float (&v)[8]);
+template <> __device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
+    float4 a = *reinterpret_cast<const float4*>(p);
+    float4 b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+    uint4 u = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float2 f = __bfloat1622float2(h[i]);
+        v[2 * i] = f.x; v[2 * i + 1] = f.y;
+    }
+}
+template <typename T> __device__ __forceinline__ void store8(T* p, const float (&v)[8]);
+template <> __device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
+    uint4 u;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = u;
+}
+
+template <typename T> __device__ __forceinline__ float round_as(float v);
+template <> __device__ __forceinline__ float round_as<float>(float v) { return v; }
+template <> __device__ __forceinline__ float round_as<__nv_bfloat16>(float v) {
+    return __bfloat162float(__float2bfloat16_rn(v));
+}
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    switch (act) {
+        case EDE_ACT_RELU: return fmaxf(v, 0.f);
+        case EDE_ACT_SWISH: return v / (1.f + __expf(-v));
+        case EDE_ACT_SIGMOID: return 1.f / (1.f + __expf(-v));
+        default: return v;
+    }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// dispatch helper: call f.template operator()<T>() for the dtype
+#define EDE_DISPATCH_DTYPE(dt, T, ...)                       \
+    do {                                                     \
+        if ((dt) == EDE_BF16) { using T = __nv_bfloat16; __VA_ARGS__; } \
+        else { using T = float; __VA_ARGS__; }              \
+    } while (0)
+
+}  // namespace ede

@@ -1,0 +1,186 @@
+/* ede.h -- C ABI of libede_sm100.so: the B200 (sm_100a) kernels behind the ReSIDE
+ * depth-estimation forward path.
+ *
+ * The reference (AnthonyDickson/EfficientDepthEstimation) has no FFI of its own: its
+ * hot path is a tree of torch.nn modules whose arithmetic is executed by ATen/cuDNN
+ * (SURVEY.md 2.1).  Each entry point below therefore replaces ONE library operator as
+ * the reference calls it; the citation after "replaces:" is the reference call site
+ * (paths relative to the reference repository root).
+ *
+ * Conventions: plain C, raw DEVICE pointers, explicit shapes, caller-provided
+ * cudaStream_t passed as void*; every call is asynchronous on that stream, allocates
+ * nothing, never synchronises, never throws.  Return 0 on success, negative EDE_E_* on
+ * error (text via ede_last_error(), thread-local).  Activations are NHWC ("pixel-major"):
+ * element (n,h,w,c) of a view lives at base[((n*H+h)*W+w)*cs + co + c]; cs (channel
+ * stride) and co (channel offset) are multiples of 8 elements so that every pixel slice
+ * is 16-byte aligned, lanes between the real channel count and the next multiple of 8
+ * hold zeros.  dtype: EDE_F32 or EDE_BF16.
+ */
+#ifndef EDE_H_
+#define EDE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EDE_ABI_VERSION 1
+
+enum { EDE_F32 = 0, EDE_BF16 = 1 };
+enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
+enum { EDE_OK = 0, EDE_E_ARG = -1, EDE_E_CUDA = -2, EDE_E_UNSUPPORTED = -3, EDE_E_DRIVER = -4 };
+enum { EDE_NHWC = 0, EDE_NCHW = 1 };
+
+/* One dense convolution + folded BatchNorm + activation (+ residual).
+ * replaces: nn.Conv2d -> nn.BatchNorm2d(eval) -> ReLU/swish -> `out += residual`
+ *   ReSIDE/models/resnet.py:78-93 (Bottleneck), ReSIDE/models/modules.py:35-39 (_UpProjection),
+ *   modules.py:229,265-266,288-296 (D.conv, MFF.conv, R.*), ReSIDE/models/lasinger2019.py:153-161,
+ *   288-293, and MBConv expand/project 1x1 of efficientnet-pytorch 0.6.3.
+ *   y[n,oh,ow,k] = act_k( scale[k] * sum_{r,s,c} x[n, oh*sh-pt+r, ow*sw-pl+s, c] * w[k,c,r,s]
+ *                         + shift[k] + res[n,oh,ow,k] ),  act applied to channels k < act_c_end. */
+typedef struct EdeConv {
+    const void* x;          /* input view base (dtype x_dtype)                                  */
+    void* y;                /* output view base (dtype y_dtype)                                 */
+    const void* res;        /* optional residual view (dtype y_dtype), NULL if none             */
+    const float* scale;     /* [cout_p] fp32, folded BN gamma/sqrt(var+eps) (1 if no BN)        */
+    const float* shift;     /* [cout_p] fp32, folded BN beta-mean*scale (+ conv bias)           */
+    const void* w_umma;     /* bf16 [kh*kw][cout_p16][cin_p64] K-major packed weights, or NULL   */
+    const float* w_direct;  /* fp32 [kh*kw][cin_p][cout_p] packed weights (always present)       */
+    int32_t n, h, w, cin_p, x_cs, x_co;          /* cin_p: visible input lanes (multiple of 8)   */
+    int32_t oh, ow, cout_p, y_cs, y_co;          /* cout_p: written output lanes (multiple of 8) */
+    int32_t res_cs, res_co;
+    int32_t kh, kw, sh, sw, pt, pl;              /* bottom/right padding is implied by oh/ow     */
+    int32_t act, act_c_end;
+    int32_t x_dtype, y_dtype;
+    int32_t x_layout;       /* EDE_NCHW only for a 3-channel fp32 network input (stem convs)     */
+    int32_t relu_in;        /* apply ReLU to x while loading (lasinger2019.py:153), direct path  */
+    int32_t w_umma_cout_p, w_umma_cin_p;         /* padded dims of w_umma                        */
+    int32_t force_direct;   /* 1: never take the tcgen05 path (fp32 parity mode / debugging)     */
+} EdeConv;
+int ede_conv2d(const EdeConv* a, void* stream);
+
+/* Tile configuration the tcgen05 path would use for `a` (pure host function, no GPU). */
+typedef struct EdeUmmaCfg {
+    int32_t eligible;       /* 0: ede_conv2d would take the direct path                          */
+    int32_t a_mode;         /* 0: halo tile resident in smem, taps = shifted UMMA windows;
+                               1: one TMA box per (tap, channel chunk)                            */
+    int32_t ck, swizzle;    /* channels per K chunk (16/32/64) and smem swizzle bytes            */
+    int32_t bh, bw, pitch, box_rows;             /* output tile, smem pixel pitch, input rows    */
+    int32_t m_tiles, n_pad, n_tiles;             /* UMMA M=128 tiles per CTA, UMMA N, grid.y      */
+    int32_t a_stages, b_stages, a_stage_bytes, b_stage_bytes, smem_bytes, tmem_cols;
+    int32_t tiles_w, tiles_h, flat;              /* flat: N*H*W folded into one pixel axis (1x1)  */
+    double useful_frac;     /* real MACs / issued tensor MACs                                    */
+} EdeUmmaCfg;
+int ede_conv2d_umma_config(const EdeConv* a, EdeUmmaCfg* out);
+
+/* Depthwise convolution + folded BN + swish, accumulating per-(n,c) sums for squeeze-excite.
+ * replaces: MBConvBlock._depthwise_conv (Conv2dStaticSamePadding, groups=C) -> _bn1 -> swish and
+ *   F.adaptive_avg_pool2d(x, 1) of efficientnet-pytorch 0.6.3, reached
+ *   from ReSIDE/models/modules.py:157-159.  w: fp32 [kh*kw][c_p].  pool_sum: fp32 [n][c_p],
+ *   must be zeroed by the caller (ede_fill_zero) before the call; NULL to skip. */
+typedef struct EdeDwConv {
+    const void* x; void* y; const float* w; const float* scale; const float* shift; float* pool_sum;
+    int32_t n, h, w_, c_p, x_cs, x_co, oh, ow, y_cs, y_co;
+    int32_t k, s, pt, pl, act, dtype;
+} EdeDwConv;
+int ede_dwconv2d(const EdeDwConv* a, void* stream);
+
+/* Squeeze-excite gate: gate[n,c] = sigmoid(W2 . swish(W1 . (pool_sum[n,:]/hw) + b1) + b2).
+ * replaces: _se_reduce -> swish -> _se_expand -> sigmoid (App. A.3).  w1: fp32 [csq][c_p],
+ *   w2: fp32 [c_p][csq] (rows >= c hold zeros), gate: fp32 [n][c_p]. */
+typedef struct EdeSeFc {
+    const float* pool_sum; const float* w1; const float* b1; const float* w2; const float* b2; float* gate;
+    int32_t n, c, c_p, csq; float inv_hw;
+} EdeSeFc;
+int ede_se_fc(const EdeSeFc* a, void* stream);
+
+/* y[n,h,w,c] = x[n,h,w,c] * gate[n,c]  (the `torch.sigmoid(s) * x` of App. A.3). */
+typedef struct EdeSeScale {
+    const void* x; void* y; const float* gate;
+    int32_t n, hw, c_p, x_cs, x_co, y_cs, y_co, dtype;
+} EdeSeScale;
+int ede_se_scale(const EdeSeScale* a, void* stream);
+
+/* Bilinear resize, align_corners=True, into a channel slice of the destination.
+ * replaces: F.interpolate(x, size, mode='bilinear', align_corners=True) at
+ *   ReSIDE/models/modules.py:34, ReSIDE/models/lasinger2019.py:244,289, ReSIDE/train.py:273-276. */
+typedef struct EdeResize {
+    const void* x; void* y;
+    int32_t n, h, w, c_p, x_cs, x_co, oh, ow, y_cs, y_co, x_dtype, y_dtype;
+} EdeResize;
+int ede_resize_bilinear_ac(const EdeResize* a, void* stream);
+
+/* Same resize on fp32 planes ([planes][h][w] == NCHW): the post-forward depth-map resize of
+ * ReSIDE/train.py:273-276, test.py:49-52, test_nyu.py:85, inference_benchmark.py:162. */
+int ede_resize_planes_f32(const float* x, float* y, int64_t planes, int32_t h, int32_t w, int32_t oh, int32_t ow,
+                          void* stream);
+
+/* 3x3 stride-2 pad-1 max pooling. replaces: nn.MaxPool2d(3,2,1), ReSIDE/models/resnet.py:107. */
+typedef struct EdeMaxPool {
+    const void* x; void* y;
+    int32_t n, h, w, c_p, x_cs, x_co, oh, ow, y_cs, y_co, dtype;
+} EdeMaxPool;
+int ede_maxpool3x3s2(const EdeMaxPool* a, void* stream);
+
+/* Elementwise y = act(x) (+ x2): the pre-activation ReLU of lasinger2019.py:153 and the
+ * `input_from_decoder + res_block1(...)` add of lasinger2019.py:241. x2 may be NULL. */
+typedef struct EdeEltwise {
+    const void* x; const void* x2; void* y;
+    int32_t n_pix, c_p, x_cs, x_co, x2_cs, x2_co, y_cs, y_co, act, dtype;
+} EdeEltwise;
+int ede_eltwise(const EdeEltwise* a, void* stream);
+
+/* Layout changes at the model boundary (the reference is NCHW fp32 end to end).
+ * nchw_to_nhwc: src fp32 [n][c][h][w] -> dst view (dst_dtype), lanes c..c_p-1 zeroed.
+ * nhwc_to_nchw: src view -> dst fp32 [n][c][h][w] contiguous. */
+typedef struct EdeLayout {
+    const void* src; void* dst;
+    int32_t n, c, h, w, c_p, cs, co, dtype;
+} EdeLayout;
+int ede_nchw_to_nhwc(const EdeLayout* a, void* stream);
+int ede_nhwc_to_nchw(const EdeLayout* a, void* stream);
+
+int ede_fill_zero(void* p, int64_t bytes, void* stream);
+
+/* Sobel gradients. replaces: Sobel.forward, ReSIDE/sobel.py:19-23 ([n,1,h,w] -> [n,2,h,w], fp32 NCHW). */
+int ede_sobel(const float* x, float* y, int32_t n, int32_t h, int32_t w, void* stream);
+
+/* Fused Sobel depth/gradient/normal loss + depth metrics: ONE pass over (pred, label).
+ * replaces: ReSIDE/train.py:216-236 (loss) and MetricsTracker.update, ReSIDE/util.py:39-92.
+ * pred/label: fp32 [n,1,h,w].  out: 16 doubles, ACCUMULATED (zero it first):
+ *  [0] sum log(|o-d|+.5)  [1] sum |1-cos|  [2] sum log(|odx-ddx|+.5)  [3] sum log(|ody-ddy|+.5)
+ *  [4] sum |o-d|  [5] sum (o-d)^2  [6] sum rel (masked)  [7] sum |log10 o - log10 d| (masked)
+ *  [8..10] #(max(o/d,d/o) <= 1.25^k)  [11] #non-NaN labels  [12] #pixels  [13] #images [14..15] 0 */
+int ede_sobel_loss_metrics(const float* pred, const float* label, int32_t n, int32_t h, int32_t w,
+                           double* out16, void* stream);
+
+/* Edge-detection counts of ReSIDE/test.py:56-76,94-102: sqrt(gx^2+gy^2) > thr for both maps.
+ * out: 4 doubles accumulated: [0] #pred edges [1] #label edges [2] #both [3] #equal. */
+int ede_edge_counts(const float* pred, const float* label, int32_t n, int32_t h, int32_t w,
+                    float thr, double* out4, void* stream);
+
+/* Run a pre-built operator list ("forward plan") back to back on one stream. */
+enum { EDE_OP_CONV = 1, EDE_OP_DWCONV = 2, EDE_OP_SE_FC = 3, EDE_OP_SE_SCALE = 4, EDE_OP_RESIZE = 5,
+       EDE_OP_MAXPOOL = 6, EDE_OP_ELTWISE = 7, EDE_OP_TO_NHWC = 8, EDE_OP_TO_NCHW = 9, EDE_OP_ZERO = 10 };
+typedef struct EdeOp {
+    int32_t kind; int32_t _pad;
+    union {
+        EdeConv conv; EdeDwConv dw; EdeSeFc se_fc; EdeSeScale se_scale; EdeResize resize;
+        EdeMaxPool maxpool; EdeEltwise eltwise; EdeLayout layout;
+        struct { void* p; int64_t bytes; } zero;
+    } u;
+} EdeOp;
+int ede_plan_run(const EdeOp* ops, int32_t n_ops, void* stream);
+/* number of kernel launches issued by this library on the calling thread since the last reset */
+int64_t ede_launch_count(int32_t reset);
+
+int ede_version(void);
+const char* ede_last_error(void);
+/* 1 when the tcgen05/TMA path is usable (driver entry point for tensor maps resolved, sm_100). */
+int ede_umma_available(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EDE_H_ */
