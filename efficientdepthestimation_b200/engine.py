@@ -1,0 +1,609 @@
+"""Forward-plan compiler and runner (host logic of the B200 path).
+
+A product module (``ReSIDE/models/*.py`` in this package) never executes torch ops in
+``forward``.  Instead it *emits* its operators into a :class:`Graph` -- an ordered list of
+``EdeOp`` records (include/ede.h) over NHWC activation buffers carved out of ONE arena --
+which is compiled once per (module, input shapes, precision, device) and then replayed with
+a single ``ede_plan_run`` call per forward.  There is NO fallback: without the CUDA library
+or with a CPU tensor, ``forward`` raises.
+
+Layout rules (include/ede.h): every activation view has a multiple-of-8 lane count; a
+``View`` records which logical channel each lane carries (``-1`` = zero lane), so channel
+concatenation (``torch.cat`` at ReSIDE/models/net.py:30, modules.py:265 of the reference) is
+two producers writing adjacent slices of the same buffer, and the consumer's weights are
+scattered to the lane order once at prepack time.
+"""
+import ctypes as C
+import os
+import threading
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _cabi as A
+from . import prepack as P
+
+_PRECISION = os.environ.get("EDE_PRECISION", "bf16")
+_ELT = {A.F32: 4, A.BF16: 2}
+_ALIGN = 1024
+
+
+def set_precision(mode: str) -> None:
+    """'bf16' (tcgen05 path, bf16 activations, fp32 accumulate) or 'fp32' (exact SIMT path)."""
+    global _PRECISION
+    if mode not in ("bf16", "fp32"):
+        raise ValueError(f"unknown precision mode '{mode}' (expected 'bf16' or 'fp32')")
+    _PRECISION = mode
+
+
+def get_precision() -> str:
+    return _PRECISION
+
+
+class Buf:
+    """One NHWC activation buffer ([n][h][w][cs] elements of `dtype`) inside the plan arena."""
+
+    def __init__(self, n, h, w, cs, dtype):
+        self.n, self.h, self.w, self.cs, self.dtype = n, h, w, cs, dtype
+        self.first = self.last = -1
+        self.offset = -1
+
+    @property
+    def nbytes(self):
+        return self.n * self.h * self.w * self.cs * _ELT[self.dtype]
+
+
+class View:
+    """Channel slice [co, co+len(lanes)) of a buffer; lanes[j] = logical channel or -1 (zero)."""
+
+    def __init__(self, buf: Buf, co: int, lanes: Sequence[int]):
+        assert co % 8 == 0 and len(lanes) % 8 == 0
+        self.buf, self.co, self.lanes = buf, co, list(lanes)
+
+    n = property(lambda s: s.buf.n)
+    h = property(lambda s: s.buf.h)
+    w = property(lambda s: s.buf.w)
+    c_p = property(lambda s: len(s.lanes))
+    c = property(lambda s: sum(1 for v in s.lanes if v >= 0))
+    dtype = property(lambda s: s.buf.dtype)
+
+    @property
+    def shape(self):          # logical NCHW shape, what the reference tensor would have
+        return (self.n, self.c, self.h, self.w)
+
+    def size(self, d):
+        return self.shape[d]
+
+    def slice(self, lo_p: int, n_p: int, relabel: bool = True) -> "View":
+        lanes = self.lanes[lo_p:lo_p + n_p]
+        if relabel:
+            base = min([v for v in lanes if v >= 0], default=0)
+            lanes = [v - base if v >= 0 else -1 for v in lanes]
+        return View(self.buf, self.co + lo_p, lanes)
+
+
+def cat_views(views: Sequence[View]) -> View:
+    """torch.cat(dim=1) of views that already sit side by side in one buffer."""
+    b, co, lanes, base = views[0].buf, views[0].co, [], 0
+    for v in views:
+        if v.buf is not b or v.co != co + len(lanes):
+            raise RuntimeError("cat_views: views are not adjacent slices of one buffer")
+        lanes += [base + x if x >= 0 else -1 for x in v.lanes]
+        base += v.c
+    return View(b, co, lanes)
+
+
+def _bn_dict(bn):
+    if bn is None:
+        return None
+    return dict(weight=bn.weight, bias=bn.bias, mean=bn.running_mean, var=bn.running_var, eps=bn.eps)
+
+
+def _pad4(conv) -> Tuple[int, int, int, int]:
+    """(top, left, bottom, right) zero padding of a conv module.  Conv2dStaticSamePadding of
+    the product efficientnet_pytorch carries `static_pad` = (left, right, top, bottom)."""
+    sp = getattr(conv, "static_pad", None)
+    if sp is not None:
+        l, r, t, b = sp
+        return t, l, b, r
+    ph, pw = conv.padding
+    return ph, pw, ph, pw
+
+
+class Graph:
+    """Records operators; `finalize()` lays out the arena and returns a runnable Plan."""
+
+    def __init__(self, device: torch.device, precision: Optional[str] = None):
+        self.device = device
+        self.precision = precision or _PRECISION
+        self.act_dtype = A.BF16 if self.precision == "bf16" else A.F32
+        self.dry = device.type != "cuda"          # host-only compile (tests without a GPU)
+        self.ops: List[tuple] = []                # (kind, struct, [(field, Buf)], tag)
+        self.bufs: List[Buf] = []
+        self.keep: List[torch.Tensor] = []        # prepacked weights etc.
+        self.inputs: List[tuple] = []             # (op index, shape)
+        self.outputs: List[tuple] = []            # (op index, shape)
+        self.flops = 0.0                          # algorithmic 2*MAC of the dense/depthwise convs
+        self.tags: List[str] = []
+
+    # ------------------------------------------------------------------ helpers
+    def new_buf(self, n, h, w, cs, dtype=None) -> Buf:
+        b = Buf(n, h, w, cs, self.act_dtype if dtype is None else dtype)
+        self.bufs.append(b)
+        return b
+
+    def new_view(self, n, h, w, c, dtype=None) -> View:
+        c_p = P.ceil8(c)
+        return View(self.new_buf(n, h, w, c_p, dtype), 0, P.identity_map(c, c_p))
+
+    def alloc_concat(self, n, h, w, channels: Sequence[int], dtype=None) -> List[View]:
+        """Destination slices for producers whose outputs the reference concatenates."""
+        cps = [P.ceil8(c) for c in channels]
+        b = self.new_buf(n, h, w, sum(cps), dtype)
+        out, co = [], 0
+        for c, cp in zip(channels, cps):
+            out.append(View(b, co, P.identity_map(c, cp)))
+            co += cp
+        return out
+
+    def _dev(self, t: torch.Tensor) -> torch.Tensor:
+        t = t.contiguous()
+        if not self.dry:
+            t = t.to(self.device)
+        self.keep.append(t)
+        return t
+
+    def _ptr(self, t: Optional[torch.Tensor]):
+        return None if t is None else (t.data_ptr() if not self.dry else 1)
+
+    def _add(self, kind, st, refs, tag):
+        i = len(self.ops)
+        for _, b in refs:
+            if b.first < 0:
+                b.first = i
+            b.last = i
+        self.ops.append((kind, st, refs, tag))
+        return i
+
+    # ------------------------------------------------------------------ operators
+    def input_nchw(self, shape) -> View:
+        """Network input: fp32 NCHW tensor supplied at run time -> NHWC view (EDE_OP_TO_NHWC)."""
+        n, c, h, w = (int(s) for s in shape)
+        v = self.new_view(n, h, w, c)
+        st = A.EdeLayout(src=None, dst=None, n=n, c=c, h=h, w=w, c_p=v.c_p, cs=v.buf.cs, co=v.co, dtype=v.dtype)
+        i = self._add(A.OP_TO_NHWC, st, [("dst", v.buf)], "to_nhwc")
+        self.inputs.append((i, (n, c, h, w)))
+        return v
+
+    def output_nchw(self, v: View) -> None:
+        """Module output: view -> fresh fp32 NCHW contiguous tensor (EDE_OP_TO_NCHW)."""
+        lanes = [x for x in v.lanes if x >= 0]
+        if lanes != list(range(len(lanes))) or v.lanes[:len(lanes)] != lanes:
+            raise RuntimeError("output_nchw: view must carry its channels contiguously from lane 0")
+        st = A.EdeLayout(src=None, dst=None, n=v.n, c=v.c, h=v.h, w=v.w, c_p=v.c_p, cs=v.buf.cs, co=v.co,
+                         dtype=v.dtype)
+        i = self._add(A.OP_TO_NCHW, st, [("src", v.buf)], "to_nchw")
+        self.outputs.append((i, (v.n, v.c, v.h, v.w)))
+
+    def conv(self, x: View, parts, stride=1, pad=(0, 0, 0, 0), act=A.ACT_NONE, res: Optional[View] = None,
+             out: Optional[View] = None, relu_in=False, out_dtype=None, tag="conv") -> View:
+        """Dense conv + folded BN + activation (+ residual).  `parts` is a list of
+        (weight OIHW, bn module|None, bias|None, activated: bool); the parts share the input and
+        their outputs are laid side by side (each padded to 8 lanes) -- used to run the two 5x5
+        convs of an _UpProjection (modules.py:35,37) as ONE GEMM with N = 2*Cout."""
+        if relu_in and self.precision == "bf16":
+            x = self.eltwise(x, act=A.ACT_RELU, tag=tag + ".relu_in")      # keeps the conv on the tcgen05 path
+            relu_in = False
+        kh, kw = int(parts[0][0].shape[2]), int(parts[0][0].shape[3])
+        pt, pl, pb, pr = pad
+        oh = (x.h + pt + pb - kh) // stride + 1
+        ow = (x.w + pl + pr - kw) // stride + 1
+        cin = x.c
+        out_lanes, fulls, scales, shifts, act_end = [], [], [], [], 0
+        seen_plain = False
+        for (wt, bn, bias, activated) in parts:
+            co = int(wt.shape[0])
+            if int(wt.shape[1]) != cin:
+                raise RuntimeError(f"{tag}: weight expects {int(wt.shape[1])} input channels, view has {cin}")
+            omap = P.identity_map(co)
+            fulls.append(P.scatter_weight(wt, x.lanes, omap))
+            sc, sf = P.fold_bn(co, _bn_dict(bn), bias, wt.device)
+            scales.append(P.place_lanes(sc, omap))
+            shifts.append(P.place_lanes(sf, omap))
+            base = sum(1 for v in out_lanes if v >= 0)
+            out_lanes += [base + v if v >= 0 else -1 for v in omap]
+            if activated and act != A.ACT_NONE:
+                if seen_plain:
+                    raise RuntimeError("conv: activated parts must precede plain ones")
+                act_end = len(out_lanes)
+            else:
+                seen_plain = True
+            self.flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
+        full = torch.cat(fulls, 0)
+        cout_p = len(out_lanes)
+        if out is None:
+            out = View(self.new_buf(x.n, oh, ow, cout_p, out_dtype), 0, out_lanes)
+        else:
+            if (out.n, out.h, out.w, out.c_p) != (x.n, oh, ow, cout_p):
+                raise RuntimeError(f"{tag}: destination slice {out.n, out.h, out.w, out.c_p} does not match "
+                                   f"conv output {x.n, oh, ow, cout_p}")
+        w_direct = self._dev(P.pack_direct(full))
+        w_umma, co16, ci64 = P.pack_umma(full)
+        w_umma = self._dev(w_umma)
+        scale = self._dev(torch.cat(scales))
+        shift = self._dev(torch.cat(shifts))
+        if res is not None and res.dtype != out.dtype:
+            raise RuntimeError(f"{tag}: residual dtype must equal output dtype")
+        st = A.EdeConv(x=None, y=None, res=None, scale=self._ptr(scale), shift=self._ptr(shift),
+                       w_umma=self._ptr(w_umma), w_direct=self._ptr(w_direct),
+                       n=x.n, h=x.h, w=x.w, cin_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
+                       oh=oh, ow=ow, cout_p=cout_p, y_cs=out.buf.cs, y_co=out.co,
+                       res_cs=res.buf.cs if res is not None else 0, res_co=res.co if res is not None else 0,
+                       kh=kh, kw=kw, sh=stride, sw=stride, pt=pt, pl=pl, act=act, act_c_end=act_end,
+                       x_dtype=x.dtype, y_dtype=out.dtype, x_layout=A.NHWC, relu_in=1 if relu_in else 0,
+                       w_umma_cout_p=co16, w_umma_cin_p=ci64, force_direct=1 if self.precision == "fp32" else 0)
+        refs = [("x", x.buf), ("y", out.buf)] + ([("res", res.buf)] if res is not None else [])
+        self._add(A.OP_CONV, st, refs, tag)
+        return out
+
+    def conv_bn_act(self, x: View, conv, bn=None, act=A.ACT_NONE, res=None, out=None, relu_in=False,
+                    out_dtype=None, tag="conv") -> View:
+        """nn.Conv2d (+ nn.BatchNorm2d) (+ activation) as one fused operator."""
+        if conv.groups != 1:
+            raise RuntimeError(f"{tag}: grouped convolution is not a dense conv")
+        return self.conv(x, [(conv.weight, bn, conv.bias, act != A.ACT_NONE)], conv.stride[0], _pad4(conv), act,
+                         res, out, relu_in, out_dtype, tag)
+
+    def dwconv_bn_act(self, x: View, conv, bn, act, pool: bool, tag="dwconv"):
+        """Depthwise conv + BN + activation; with pool=True also the per-(n,c) sums for SE."""
+        k, s = conv.kernel_size[0], conv.stride[0]
+        pt, pl, pb, pr = _pad4(conv)
+        oh, ow = (x.h + pt + pb - k) // s + 1, (x.w + pl + pr - k) // s + 1
+        c = x.c
+        if conv.groups != c or int(conv.weight.shape[0]) != c:
+            raise RuntimeError(f"{tag}: not a depthwise convolution over {c} channels")
+        out = View(self.new_buf(x.n, oh, ow, x.c_p), 0, x.lanes)
+        wt = conv.weight.detach().float().reshape(c, k * k).t()            # [k*k][c]
+        w = torch.zeros(k * k, x.c_p, dtype=torch.float32, device=wt.device)
+        idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0], device=wt.device)
+        src = torch.tensor([v for v in x.lanes if v >= 0], device=wt.device)
+        w[:, idx] = wt[:, src]
+        sc, sf = P.fold_bn(c, _bn_dict(bn), conv.bias, wt.device)
+        w, sc, sf = self._dev(w), self._dev(P.place_lanes(sc, x.lanes)), self._dev(P.place_lanes(sf, x.lanes))
+        pool_t = None
+        if pool:
+            pool_t = self._dev(torch.zeros(x.n, x.c_p, dtype=torch.float32))
+            self._add(A.OP_ZERO, A._Zero(p=self._ptr(pool_t), bytes=pool_t.numel() * 4), [], tag + ".zero")
+        st = A.EdeDwConv(x=None, y=None, w=self._ptr(w), scale=self._ptr(sc), shift=self._ptr(sf),
+                         pool_sum=self._ptr(pool_t), n=x.n, h=x.h, w_=x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
+                         oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype)
+        self._add(A.OP_DWCONV, st, [("x", x.buf), ("y", out.buf)], tag)
+        self.flops += 2.0 * x.n * oh * ow * c * k * k
+        return out, pool_t
+
+    def se_gate(self, x: View, pool_t, reduce_conv, expand_conv, tag="se") -> View:
+        """Squeeze-excite: gate = sigmoid(W2 swish(W1 mean + b1) + b2); returns x * gate."""
+        c, csq = x.c, int(reduce_conv.weight.shape[0])
+        dev = reduce_conv.weight.device
+        idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0], device=dev)
+        src = torch.tensor([v for v in x.lanes if v >= 0], device=dev)
+        if idx.tolist() != list(range(c)):
+            raise RuntimeError("se_gate: channels must occupy lanes 0..c-1")
+        w1 = torch.zeros(csq, x.c_p, dtype=torch.float32, device=dev)
+        w1[:, idx] = reduce_conv.weight.detach().float().reshape(csq, c)[:, src]
+        w2 = torch.zeros(x.c_p, csq, dtype=torch.float32, device=dev)
+        w2[idx] = expand_conv.weight.detach().float().reshape(c, csq)[src]
+        b2 = torch.zeros(x.c_p, dtype=torch.float32, device=dev)
+        b2[idx] = expand_conv.bias.detach().float()[src]
+        w1, w2, b2 = self._dev(w1), self._dev(w2), self._dev(b2)
+        b1 = self._dev(reduce_conv.bias.detach().float())
+        gate = self._dev(torch.zeros(x.n, x.c_p, dtype=torch.float32))
+        st = A.EdeSeFc(pool_sum=self._ptr(pool_t), w1=self._ptr(w1), b1=self._ptr(b1), w2=self._ptr(w2),
+                       b2=self._ptr(b2), gate=self._ptr(gate), n=x.n, c=c, c_p=x.c_p, csq=csq,
+                       inv_hw=1.0 / (x.h * x.w))
+        self._add(A.OP_SE_FC, st, [], tag + ".fc")
+        out = View(self.new_buf(x.n, x.h, x.w, x.c_p), 0, x.lanes)
+        st = A.EdeSeScale(x=None, y=None, gate=self._ptr(gate), n=x.n, hw=x.h * x.w, c_p=x.c_p,
+                          x_cs=x.buf.cs, x_co=x.co, y_cs=out.buf.cs, y_co=out.co, dtype=x.dtype)
+        self._add(A.OP_SE_SCALE, st, [("x", x.buf), ("y", out.buf)], tag + ".scale")
+        return out
+
+    def resize(self, x: View, size, out: Optional[View] = None, out_dtype=None, tag="resize") -> View:
+        """F.interpolate(x, size, mode='bilinear', align_corners=True)."""
+        oh, ow = int(size[0]), int(size[1])
+        if out is None:
+            if (oh, ow) == (x.h, x.w) and (out_dtype is None or out_dtype == x.dtype):
+                return x                                   # identity resample
+            out = View(self.new_buf(x.n, oh, ow, x.c_p, out_dtype), 0, x.lanes)
+        st = A.EdeResize(x=None, y=None, n=x.n, h=x.h, w=x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co, oh=oh, ow=ow,
+                         y_cs=out.buf.cs, y_co=out.co, x_dtype=x.dtype, y_dtype=out.dtype)
+        self._add(A.OP_RESIZE, st, [("x", x.buf), ("y", out.buf)], tag)
+        return out
+
+    def maxpool3x3s2(self, x: View, tag="maxpool") -> View:
+        oh, ow = (x.h + 2 - 3) // 2 + 1, (x.w + 2 - 3) // 2 + 1
+        out = View(self.new_buf(x.n, oh, ow, x.c_p), 0, x.lanes)
+        st = A.EdeMaxPool(x=None, y=None, n=x.n, h=x.h, w=x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co, oh=oh, ow=ow,
+                          y_cs=out.buf.cs, y_co=out.co, dtype=x.dtype)
+        self._add(A.OP_MAXPOOL, st, [("x", x.buf), ("y", out.buf)], tag)
+        return out
+
+    def eltwise(self, x: View, x2: Optional[View] = None, act=A.ACT_NONE, tag="eltwise") -> View:
+        """y = act(x) (+ x2)."""
+        if x2 is not None and (x2.lanes != x.lanes or x2.dtype != x.dtype):
+            raise RuntimeError("eltwise: operands must share lane layout and dtype")
+        out = View(self.new_buf(x.n, x.h, x.w, x.c_p), 0, x.lanes)
+        st = A.EdeEltwise(x=None, x2=None, y=None, n_pix=x.n * x.h * x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
+                          x2_cs=x2.buf.cs if x2 is not None else 0, x2_co=x2.co if x2 is not None else 0,
+                          y_cs=out.buf.cs, y_co=out.co, act=act, dtype=x.dtype)
+        refs = [("x", x.buf), ("y", out.buf)] + ([("x2", x2.buf)] if x2 is not None else [])
+        self._add(A.OP_ELTWISE, st, refs, tag)
+        return out
+
+    # ------------------------------------------------------------------ arena layout
+    def finalize(self) -> "Plan":
+        """Liveness-based first-fit placement of every buffer in one arena, then pointer patching."""
+        live: List[Buf] = []
+        top = 0
+        for b in sorted((b for b in self.bufs if b.first >= 0), key=lambda b: (b.first, -b.nbytes)):
+            live = [o for o in live if o.last >= b.first]
+            live.sort(key=lambda o: o.offset)
+            size = (b.nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+            pos = 0
+            for o in live:
+                o_size = (o.nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+                if pos + size <= o.offset:
+                    break
+                pos = max(pos, o.offset + o_size)
+            b.offset = pos
+            live.append(b)
+            top = max(top, pos + size)
+        return Plan(self, top)
+
+
+class Plan:
+    """A compiled forward: EdeOp array + arena + prepacked weights.  `run` is one C call."""
+
+    def __init__(self, g: Graph, arena_bytes: int):
+        self.device, self.precision, self.dry = g.device, g.precision, g.dry
+        self.arena_bytes = arena_bytes
+        self.keep = g.keep
+        self.flops = g.flops
+        self.tags = [t for (_, _, _, t) in g.ops]
+        self.kinds = [k for (k, _, _, _) in g.ops]
+        self.inputs, self.outputs = g.inputs, g.outputs
+        self.n_ops = len(g.ops)
+        self.arena = None
+        base = 0
+        if not self.dry:
+            self.arena = torch.empty(arena_bytes + _ALIGN, dtype=torch.uint8, device=self.device)
+            base = (self.arena.data_ptr() + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.ops = (A.EdeOp * max(1, self.n_ops))()
+        for i, (kind, st, refs, _) in enumerate(g.ops):
+            for field, b in refs:
+                setattr(st, field, base + b.offset if not self.dry else 1 + b.offset)
+            self.ops[i].kind = kind
+            setattr(self.ops[i].u, A.OP_FIELD[kind], st)
+        self.structs = [st for (_, st, _, _) in g.ops]      # host copies (introspection / tests)
+        self._graph = None
+        self._lock = threading.Lock()
+
+    def conv_configs(self):
+        """(tag, EdeConv, EdeUmmaCfg) of every dense conv -- which path each one takes."""
+        out = []
+        for k, st, tag in zip(self.kinds, self.structs, self.tags):
+            if k == A.OP_CONV:
+                out.append((tag, st, A.umma_config(st)))
+        return out
+
+    def launches_per_run(self) -> int:
+        return self.n_ops
+
+    def run(self, tensors: Sequence[torch.Tensor]) -> List[torch.Tensor]:
+        if self.dry:
+            raise RuntimeError("efficientdepthestimation_b200: this plan was compiled without a CUDA device; "
+                               "there is no CPU execution path")
+        if len(tensors) != len(self.inputs):
+            raise RuntimeError(f"plan expects {len(self.inputs)} input tensors, got {len(tensors)}")
+        outs = []
+        with self._lock, torch.cuda.device(self.device):
+            hold = []
+            for (i, shape), t in zip(self.inputs, tensors):
+                if tuple(t.shape) != shape:
+                    raise RuntimeError(f"plan compiled for input {shape}, got {tuple(t.shape)}")
+                if t.dtype != torch.float32 or not t.is_contiguous():
+                    t = t.float().contiguous()
+                hold.append(t)
+                self.ops[i].u.layout.src = t.data_ptr()
+            for (i, shape) in self.outputs:
+                o = torch.empty(shape, dtype=torch.float32, device=self.device)
+                self.ops[i].u.layout.dst = o.data_ptr()
+                outs.append(o)
+            st = torch.cuda.current_stream(self.device).cuda_stream
+            A.check(A.lib().ede_plan_run(self.ops, self.n_ops, st), "ede_plan_run")
+        return outs
+
+
+# ---------------------------------------------------------------------- module protocol
+def emit(module, g: Graph, *args, **kw):
+    """Emit `module` into `g`.  Product modules implement `_emit`; plain torch containers
+    (nn.Sequential of conv/bn/relu/maxpool/blocks, as the reference builds them at
+    modules.py:187-196 and lasinger2019.py:107-111) are pattern-matched here."""
+    from torch import nn
+    if hasattr(module, "_emit"):
+        return module._emit(g, *args, **kw)
+    if isinstance(module, nn.Sequential):
+        (x,) = args
+        mods = list(module.children())
+        i = 0
+        while i < len(mods):
+            m = mods[i]
+            if isinstance(m, nn.Conv2d):
+                bn = mods[i + 1] if i + 1 < len(mods) and isinstance(mods[i + 1], nn.BatchNorm2d) else None
+                j = i + (2 if bn is not None else 1)
+                relu = j < len(mods) and isinstance(mods[j], nn.ReLU)
+                x = g.conv_bn_act(x, m, bn, A.ACT_RELU if relu else A.ACT_NONE, tag=f"seq.{i}")
+                i = j + (1 if relu else 0)
+                continue
+            if isinstance(m, nn.MaxPool2d):
+                k = m.kernel_size if isinstance(m.kernel_size, int) else m.kernel_size[0]
+                s = m.stride if isinstance(m.stride, int) else m.stride[0]
+                p = m.padding if isinstance(m.padding, int) else m.padding[0]
+                if (k, s, p) != (3, 2, 1):
+                    raise RuntimeError(f"unsupported MaxPool2d{(k, s, p)} on the B200 path")
+                x = g.maxpool3x3s2(x)
+            elif isinstance(m, nn.ReLU):
+                x = g.eltwise(x, act=A.ACT_RELU)
+            elif isinstance(m, nn.Identity):
+                pass
+            else:
+                x = emit(m, g, x)
+            i += 1
+        return x
+    if all(hasattr(module, a) for a in ("conv1", "bn1", "conv2", "bn2", "conv3", "bn3", "downsample")):
+        return emit_bottleneck(module, g, *args)
+    raise RuntimeError(f"efficientdepthestimation_b200: no B200 operator mapping for {type(module).__name__}")
+
+
+def emit_bottleneck(m, g: Graph, x: View, tag="bottleneck") -> View:
+    """ResNet bottleneck (ReSIDE/models/resnet.py:75-95; same attribute layout as torchvision's):
+    1x1+BN+ReLU -> 3x3(stride)+BN+ReLU -> 1x1+BN (+ downsample 1x1(stride)+BN) -> add -> ReLU,
+    the add and the final ReLU fused into the last conv's epilogue."""
+    out = g.conv_bn_act(x, m.conv1, m.bn1, A.ACT_RELU, tag=tag + ".conv1")
+    out = g.conv_bn_act(out, m.conv2, m.bn2, A.ACT_RELU, tag=tag + ".conv2")
+    res = x
+    if m.downsample is not None:
+        ds = list(m.downsample.children())
+        res = g.conv_bn_act(x, ds[0], ds[1], A.ACT_NONE, tag=tag + ".downsample")
+    return g.conv_bn_act(out, m.conv3, m.bn3, A.ACT_RELU, res=res, tag=tag + ".conv3")
+
+
+def _flatten(obj, tensors, spec):
+    if isinstance(obj, torch.Tensor):
+        tensors.append(obj)
+        spec.append(("T", tuple(obj.shape)))
+    elif isinstance(obj, (list, tuple)) and any(isinstance(o, torch.Tensor) for o in obj):
+        spec.append(("L", len(obj)))
+        for o in obj:
+            _flatten(o, tensors, spec)
+    else:
+        spec.append(("V", tuple(int(v) for v in obj) if isinstance(obj, (list, tuple, torch.Size)) else obj))
+
+
+def _rebuild(spec, it, views):
+    kind, val = next(it)
+    if kind == "T":
+        return next(views)
+    if kind == "L":
+        return [_rebuild(spec, it, views) for _ in range(val)]
+    return val
+
+
+def _flatten_out(obj, out):
+    if isinstance(obj, View):
+        out.append(obj)
+        return ("T",)
+    return ("L", [_flatten_out(o, out) for o in obj], type(obj))
+
+
+def _rebuild_out(s, it):
+    if s[0] == "T":
+        return next(it)
+    items = [_rebuild_out(x, it) for x in s[1]]
+    return tuple(items) if s[2] is tuple else items
+
+
+def compile_module(module, args, device: torch.device, precision: Optional[str] = None):
+    """Build the plan of `module(*args)`; tensors in `args` may be real or meta/CPU (dry)."""
+    tensors, spec = [], []
+    for a in args:
+        _flatten(a, tensors, spec)
+    g = Graph(device, precision)
+    views = iter([g.input_nchw(t.shape) for t in tensors])
+    it = iter(spec)
+    call_args = [_rebuild(spec, it, views) for _ in args]
+    with torch.no_grad():
+        result = emit(module, g, *call_args)
+        outs: List[View] = []
+        out_spec = _flatten_out(result, outs)
+        for v in outs:
+            g.output_nchw(v)
+    return g.finalize(), out_spec, tuple(spec)
+
+
+class EdeModule:
+    """Mixin giving an nn.Module the B200 `forward`: compile once per signature, then replay.
+
+    Mirrors the reference's calling convention (fp32 NCHW in, fp32 NCHW out, eval mode).
+    training=True, CPU tensors or a missing CUDA library raise -- there is no fallback."""
+
+    def _ede_cache(self) -> dict:
+        c = self.__dict__.get("_ede_plans")
+        if c is None:
+            c = {}
+            self.__dict__["_ede_plans"] = c
+        return c
+
+    def invalidate_plans(self) -> None:
+        """Drop compiled plans (weights changed: load_state_dict, .to(), .train())."""
+        from torch import nn
+        for m in self.modules() if isinstance(self, nn.Module) else [self]:
+            if "_ede_plans" in m.__dict__:
+                m.__dict__["_ede_plans"] = {}
+
+    def _apply(self, fn, *a, **kw):
+        r = super()._apply(fn, *a, **kw)
+        self.invalidate_plans()
+        return r
+
+    def load_state_dict(self, *a, **kw):
+        r = super().load_state_dict(*a, **kw)
+        self.invalidate_plans()
+        return r
+
+    def train(self, mode: bool = True):
+        r = super().train(mode)
+        if mode:
+            self.invalidate_plans()
+        return r
+
+    def __deepcopy__(self, memo):           # plans hold raw device pointers: never copy them
+        import copy
+        cls = self.__class__
+        new = cls.__new__(cls)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            new.__dict__[k] = {} if k == "_ede_plans" else copy.deepcopy(v, memo)
+        return new
+
+    def plan_for(self, *args, precision: Optional[str] = None) -> "Plan":
+        tensors, spec = [], []
+        for a in args:
+            _flatten(a, tensors, spec)
+        if not tensors:
+            raise RuntimeError(f"{type(self).__name__}.forward needs at least one tensor argument")
+        dev = tensors[0].device
+        key = (tuple(spec), precision or _PRECISION, str(dev))
+        cache = self._ede_cache()
+        hit = cache.get(key)
+        if hit is None:
+            hit = compile_module(self, args, dev, precision)
+            cache[key] = hit
+        return hit
+
+    def forward(self, *args):
+        if self.training:
+            raise RuntimeError(
+                f"{type(self).__name__}: the B200 path implements the inference forward only "
+                "(call .eval() first); there is no training-mode or CPU fallback")
+        tensors, spec = [], []
+        for a in args:
+            _flatten(a, tensors, spec)
+        for t in tensors:
+            if t.device.type != "cuda":
+                raise RuntimeError(
+                    f"{type(self).__name__}.forward got a {t.device.type} tensor: efficientdepthestimation_b200 "
+                    "runs on CUDA (sm_100a) only and has no CPU fallback")
+        plan, out_spec, _ = self.plan_for(*args)
+        outs = plan.run(tensors)
+        return _rebuild_out(out_spec, iter(outs))

@@ -1,0 +1,75 @@
+"""Fused Sobel depth/gradient/normal loss + depth metrics (host side of ede_sobel_loss_metrics).
+
+Replaces the ~25 small kernels of the loss expression (ReSIDE/train.py:216-236) and the 9 host
+syncs of MetricsTracker.update (ReSIDE/util.py:39-92) by ONE pass over (pred, label) producing a
+16-double vector of partial sums on the device; every reported quantity is recovered from those
+sums, so a multi-GPU run only has to all-reduce 128 bytes (parallel.py).
+"""
+import math
+from typing import Dict
+
+import torch
+
+from . import _cabi as A
+
+SUM_NAMES = ("log_depth", "normal", "log_dx", "log_dy", "abs", "sq", "rel", "log10", "d1", "d2", "d3",
+             "num_valid", "num_pixels", "num_images", "_14", "_15")
+
+
+def _check_pair(pred: torch.Tensor, label: torch.Tensor):
+    if pred.device.type != "cuda" or label.device.type != "cuda":
+        raise RuntimeError("efficientdepthestimation_b200.loss: CUDA tensors required (no CPU fallback)")
+    if pred.dim() != 4 or pred.size(1) != 1 or pred.shape != label.shape:
+        raise RuntimeError(f"expected pred/label of identical shape [N,1,H,W], got {tuple(pred.shape)} / {tuple(label.shape)}")
+    return pred.detach().float().contiguous(), label.detach().float().contiguous()
+
+
+def loss_metric_sums(pred: torch.Tensor, label: torch.Tensor, out: torch.Tensor = None) -> torch.Tensor:
+    """16 fp64 partial sums (layout in include/ede.h) ACCUMULATED into `out` (device tensor); async."""
+    pred, label = _check_pair(pred, label)
+    if out is None:
+        out = torch.zeros(16, dtype=torch.float64, device=pred.device)
+    n, _, h, w = pred.shape
+    with torch.cuda.device(pred.device):
+        A.check(A.lib().ede_sobel_loss_metrics(pred.data_ptr(), label.data_ptr(), n, h, w, out.data_ptr(),
+                                               torch.cuda.current_stream(pred.device).cuda_stream),
+                "ede_sobel_loss_metrics")
+    return out
+
+
+def edge_counts(pred: torch.Tensor, label: torch.Tensor, threshold: float = 0.25, out: torch.Tensor = None):
+    """[#pred edges, #label edges, #both, #equal] of ReSIDE/test.py:56-76,94-102 as 4 fp64 on device."""
+    pred, label = _check_pair(pred, label)
+    if out is None:
+        out = torch.zeros(4, dtype=torch.float64, device=pred.device)
+    n, _, h, w = pred.shape
+    with torch.cuda.device(pred.device):
+        A.check(A.lib().ede_edge_counts(pred.data_ptr(), label.data_ptr(), n, h, w, float(threshold), out.data_ptr(),
+                                        torch.cuda.current_stream(pred.device).cuda_stream), "ede_edge_counts")
+    return out
+
+
+def loss_from_sums(s) -> Dict[str, float]:
+    """train.py:231-236 from global sums: every term is a mean over N*H*W pixels."""
+    s = [float(v) for v in s]
+    px = s[12]
+    t = {"depth": s[0] / px, "normal": s[1] / px, "dx": s[2] / px, "dy": s[3] / px}
+    t["loss"] = t["depth"] + t["normal"] + (t["dx"] + t["dy"])
+    return t
+
+
+def metrics_from_sums(s) -> Dict[str, float]:
+    """One MetricsTracker.update + read-out (util.py:54-83) from sums, INCLUDING the reference's quirk
+    that log10 lacks the batch_size factor (util.py:68)."""
+    s = [float(v) for v in s]
+    nv, b = s[11], s[13]
+    mse = s[5] / nv
+    return {"mae": s[4] / nv, "mse": mse, "rmse": math.sqrt(mse) if mse == mse and mse >= 0 else float("nan"),
+            "abs_rel": s[6] / nv, "log10": s[7] / nv / b, "delta1": s[8] / nv, "delta2": s[9] / nv,
+            "delta3": s[10] / nv}
+
+
+def sobel_loss(output: torch.Tensor, depth: torch.Tensor) -> torch.Tensor:
+    """The scalar loss of train.py:236 as a 0-dim device tensor (forward value only)."""
+    s = loss_metric_sums(output, depth)
+    return ((s[0] + s[1] + s[2] + s[3]) / s[12]).float()
