@@ -59,9 +59,10 @@ class Encoder(EdeModule, nn.Module):
 
     def _emit(self, g, x):
         outs = []
-        for block in self.blocks:
-            x = emit(block, g, x)
-            outs.append(x)
+        with g.encoder_scope():
+            for block in self.blocks:
+                x = emit(block, g, x)
+                outs.append(x)
         return outs
 
 

@@ -43,12 +43,13 @@ class E_resnet(EdeModule, nn.Module):
             setattr(self, name, getattr(original_model, name))
 
     def _emit(self, g, x):
-        x = g.conv_bn_act(x, self.conv1, self.bn1, A.ACT_RELU, tag="E.conv1")
-        x = g.maxpool3x3s2(x, tag="E.maxpool")
-        feats = []
-        for layer in (self.layer1, self.layer2, self.layer3, self.layer4):
-            x = emit(layer, g, x)
-            feats.append(x)
+        with g.encoder_scope():
+            x = g.conv_bn_act(x, self.conv1, self.bn1, A.ACT_RELU, tag="E.conv1")
+            x = g.maxpool3x3s2(x, tag="E.maxpool")
+            feats = []
+            for layer in (self.layer1, self.layer2, self.layer3, self.layer4):
+                x = emit(layer, g, x)
+                feats.append(x)
         return tuple(feats)
 
 
@@ -94,9 +95,10 @@ class E_efficientnet(EdeModule, nn.Module):
 
     def _emit(self, g, x):
         outs = []
-        for block in self.blocks:
-            x = emit(block, g, x)
-            outs.append(x)
+        with g.encoder_scope():
+            for block in self.blocks:
+                x = emit(block, g, x)
+                outs.append(x)
         return outs
 
 

@@ -11,7 +11,7 @@ from ctypes import POINTER, Structure, Union, c_double, c_float, c_int32, c_int6
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libede_sm100.so")
 
-F32, BF16 = 0, 1
+F32, BF16, BF16X2 = 0, 1, 2
 ACT_NONE, ACT_RELU, ACT_SWISH, ACT_SIGMOID = 0, 1, 2, 3
 NHWC, NCHW = 0, 1
 (OP_CONV, OP_DWCONV, OP_SE_FC, OP_SE_SCALE, OP_RESIZE, OP_MAXPOOL, OP_ELTWISE, OP_TO_NHWC, OP_TO_NCHW,
@@ -27,7 +27,7 @@ class EdeConv(Structure):
                 ("w_umma", c_void_p), ("w_direct", c_void_p)] + _ints(
         "n", "h", "w", "cin_p", "x_cs", "x_co", "oh", "ow", "cout_p", "y_cs", "y_co", "res_cs", "res_co",
         "kh", "kw", "sh", "sw", "pt", "pl", "act", "act_c_end", "x_dtype", "y_dtype", "x_layout", "relu_in",
-        "w_umma_cout_p", "w_umma_cin_p", "force_direct")
+        "w_umma_cout_p", "w_umma_cin_p", "force_direct", "w_passes")
 
 
 class EdeUmmaCfg(Structure):

@@ -312,10 +312,8 @@ int ede_resize_bilinear_ac(const EdeResize* a, void* stream) {
     const long long total = (long long)a->n * a->oh * a->ow * (a->c_p >> 3);
     const unsigned g = grid_for(total, 256);
     cudaStream_t st = (cudaStream_t)stream;
-    if (a->x_dtype == EDE_BF16 && a->y_dtype == EDE_BF16) resize_kernel<__nv_bfloat16, __nv_bfloat16><<<g, 256, 0, st>>>(*a, sh, sw);
-    else if (a->x_dtype == EDE_BF16) resize_kernel<__nv_bfloat16, float><<<g, 256, 0, st>>>(*a, sh, sw);
-    else if (a->y_dtype == EDE_BF16) resize_kernel<float, __nv_bfloat16><<<g, 256, 0, st>>>(*a, sh, sw);
-    else resize_kernel<float, float><<<g, 256, 0, st>>>(*a, sh, sw);
+    EDE_DISPATCH_DTYPE(a->x_dtype, TX,
+                       EDE_DISPATCH_DTYPE(a->y_dtype, TY, (resize_kernel<TX, TY><<<g, 256, 0, st>>>(*a, sh, sw))));
     EDE_LAUNCH_CHECK("resize_kernel");
     return EDE_OK;
 }

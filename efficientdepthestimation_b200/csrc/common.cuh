@@ -33,6 +33,12 @@ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int round_up(int a, int b) { return ceil_div(a, b) * b; }
 static inline size_t dtype_size(int dt) { return dt == EDE_BF16 ? 2 : 4; }
 
+// EDE_BF16X2 ("split bf16"): one logical lane = 4 bytes; every group of 8 logical lanes is stored as
+// [8 x bf16 hi][8 x bf16 lo] (32 bytes) with value = hi + lo (16 mantissa bits).  Seen as a plain bf16
+// tensor with twice the lanes it feeds the tensor cores directly: weights laid out [w,w] make one
+// K=16 MMA compute (hi+lo).w, so the same TMA/UMMA path runs at near-fp32 operand accuracy.
+struct bf16x2_t { __nv_bfloat16 hi, lo; };
+
 // ---------------------------------------------------------------- typed element access
 template <typename T> struct Elt;
 template <> struct Elt<float> {
@@ -42,6 +48,25 @@ template <> struct Elt<float> {
 template <> struct Elt<__nv_bfloat16> {
     static __device__ __forceinline__ float ld(const __nv_bfloat16* p) { return __bfloat162float(*p); }
     static __device__ __forceinline__ void st(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+};
+
+template <> struct Elt<bf16x2_t> {
+    // scalar access to logical lane c of a row: p points at the lane's 4-byte slot index (row base + c)
+    static __device__ __forceinline__ float ld(const bf16x2_t* p) {
+        // slot index -> group/offset relative to the 32-byte aligned group start
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        const __nv_bfloat16* g = reinterpret_cast<const __nv_bfloat16*>(a & ~uintptr_t(31));
+        const int j = (int)((a & 31) >> 2);
+        return __bfloat162float(g[j]) + __bfloat162float(g[8 + j]);
+    }
+    static __device__ __forceinline__ void st(bf16x2_t* p, float v) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        __nv_bfloat16* g = reinterpret_cast<__nv_bfloat16*>(a & ~uintptr_t(31));
+        const int j = (int)((a & 31) >> 2);
+        const __nv_bfloat16 h = __float2bfloat16_rn(v);
+        g[j] = h;
+        g[8 + j] = __float2bfloat16_rn(v - __bfloat162float(h));
+    }
 };
 
 // 8 consecutive channels (one 16-byte bf16 vector / two float4) <-> 8 floats
@@ -60,6 +85,17 @@ template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bflo
         v[2 * i] = f.x; v[2 * i + 1] = f.y;
     }
 }
+template <> __device__ __forceinline__ void load8<bf16x2_t>(const bf16x2_t* p, float (&v)[8]) {
+    const uint4 uh = *reinterpret_cast<const uint4*>(p);
+    const uint4 ul = *(reinterpret_cast<const uint4*>(p) + 1);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&uh);
+    const __nv_bfloat162* l = reinterpret_cast<const __nv_bfloat162*>(&ul);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float2 a = __bfloat1622float2(h[i]), b = __bfloat1622float2(l[i]);
+        v[2 * i] = a.x + b.x; v[2 * i + 1] = a.y + b.y;
+    }
+}
 template <typename T> __device__ __forceinline__ void store8(T* p, const float (&v)[8]);
 template <> __device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
     *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
@@ -73,10 +109,29 @@ template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16*
     *reinterpret_cast<uint4*>(p) = u;
 }
 
+template <> __device__ __forceinline__ void store8<bf16x2_t>(bf16x2_t* p, const float (&v)[8]) {
+    uint4 uh, ul;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&uh);
+    __nv_bfloat162* l = reinterpret_cast<__nv_bfloat162*>(&ul);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        const float2 r = __bfloat1622float2(h[i]);
+        l[i] = __floats2bfloat162_rn(v[2 * i] - r.x, v[2 * i + 1] - r.y);
+    }
+    *reinterpret_cast<uint4*>(p) = uh;
+    *(reinterpret_cast<uint4*>(p) + 1) = ul;
+}
+
 template <typename T> __device__ __forceinline__ float round_as(float v);
 template <> __device__ __forceinline__ float round_as<float>(float v) { return v; }
 template <> __device__ __forceinline__ float round_as<__nv_bfloat16>(float v) {
     return __bfloat162float(__float2bfloat16_rn(v));
+}
+
+template <> __device__ __forceinline__ float round_as<bf16x2_t>(float v) {
+    const float h = __bfloat162float(__float2bfloat16_rn(v));
+    return h + __bfloat162float(__float2bfloat16_rn(v - h));
 }
 
 __device__ __forceinline__ float apply_act(float v, int act) {
@@ -103,6 +158,7 @@ __device__ __forceinline__ double warp_sum(double v) {
 #define EDE_DISPATCH_DTYPE(dt, T, ...)                       \
     do {                                                     \
         if ((dt) == EDE_BF16) { using T = __nv_bfloat16; __VA_ARGS__; } \
+        else if ((dt) == EDE_BF16X2) { using T = ::ede::bf16x2_t; __VA_ARGS__; } \
         else { using T = float; __VA_ARGS__; }              \
     } while (0)
 

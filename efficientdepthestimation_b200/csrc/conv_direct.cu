@@ -112,14 +112,8 @@ int conv_direct_launch(const EdeConv& a, cudaStream_t st) {
     EDE_REQUIRE(a.w_direct != nullptr, "ede_conv2d: direct path needs w_direct");
     const long long m_total = (long long)a.n * a.oh * a.ow;
     dim3 grid((unsigned)((m_total + DBM - 1) / DBM), (unsigned)ceil_div(a.cout_p, DBN));
-    if (a.x_dtype == EDE_F32 && a.y_dtype == EDE_F32)
-        conv_direct_kernel<float, float><<<grid, 256, 0, st>>>(a);
-    else if (a.x_dtype == EDE_F32 && a.y_dtype == EDE_BF16)
-        conv_direct_kernel<float, __nv_bfloat16><<<grid, 256, 0, st>>>(a);
-    else if (a.x_dtype == EDE_BF16 && a.y_dtype == EDE_BF16)
-        conv_direct_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, st>>>(a);
-    else
-        conv_direct_kernel<__nv_bfloat16, float><<<grid, 256, 0, st>>>(a);
+    EDE_DISPATCH_DTYPE(a.x_dtype, TX,
+                       EDE_DISPATCH_DTYPE(a.y_dtype, TY, (conv_direct_kernel<TX, TY><<<grid, 256, 0, st>>>(a))));
     EDE_LAUNCH_CHECK("conv_direct_kernel");
     return EDE_OK;
 }

@@ -101,7 +101,7 @@ struct alignas(64) UmmaParams {
     CUtensorMap tm_a;     // activations: (C, W, H, N) bf16
     CUtensorMap tm_b;     // weights: (Cin_p, Cout_p, taps) bf16
     int oh, ow, tiles_w, tiles_h;
-    int a_mode, ck_bytes, n_chunks, kh, kw, sh, sw, pt, pl;
+    int a_mode, ck_bytes, n_chunks, kh, kw, sh, sw, pt, pl, w_passes;
     int bw, bh, pitch, box_bytes;
     int m_tiles, n_pad;
     int a_stages, b_stages, a_stage_bytes, b_stage_bytes, b_tx_bytes;
@@ -169,7 +169,8 @@ __global__ void __launch_bounds__(192) conv_umma_kernel(const __grid_constant__ 
     const int t_in = blockIdx.x - img * tiles_per_img;
     const int th = t_in / p.tiles_w, tw = t_in - th * p.tiles_w;
     const int ntile = blockIdx.y;
-    const int taps = p.kh * p.kw;
+    const int sp_taps = p.kh * p.kw;              // spatial taps
+    const int taps = sp_taps * p.w_passes;        // weight tiles per channel chunk ([w_hi taps ; w_lo taps])
     const int tile_w_pix = p.a_mode == 0 ? p.bw : p.bw * p.m_tiles;   // output columns covered by this CTA
     const int ow0 = tw * tile_w_pix, oh0 = th * p.bh;
 
@@ -208,7 +209,8 @@ __global__ void __launch_bounds__(192) conv_umma_kernel(const __grid_constant__ 
                 }
                 for (int tap = 0; tap < taps; ++tap) {
                     if (p.a_mode != 0) {
-                        const int ky = tap / p.kw, kx = tap - ky * p.kw;
+                        const int stap = tap >= sp_taps ? tap - sp_taps : tap;
+                        const int ky = stap / p.kw, kx = stap - ky * p.kw;
                         mbar_wait(a_empty(a_st), a_ph ^ 1);
                         mbar_expect_tx(a_full(a_st), (uint32_t)(p.m_tiles * 128 * p.ck_bytes));
                         for (int m = 0; m < p.m_tiles; ++m)
@@ -239,7 +241,8 @@ __global__ void __launch_bounds__(192) conv_umma_kernel(const __grid_constant__ 
                     tc_fence_after();
                     int shift_rows = 0;
                     if (p.a_mode == 0) {
-                        const int ky = tap / p.kw, kx = tap - ky * p.kw;
+                        const int stap = tap >= sp_taps ? tap - sp_taps : tap;
+                        const int ky = stap / p.kw, kx = stap - ky * p.kw;
                         shift_rows = ky * p.pitch + kx;
                     }
                     const uint32_t a_addr = a_base + a_st * p.a_stage_bytes + shift_rows * p.ck_bytes;
@@ -300,6 +303,9 @@ __global__ void __launch_bounds__(192) conv_umma_kernel(const __grid_constant__ 
                     if (p.y_dtype == EDE_BF16) {
                         if (c < p.cout_p) epilogue_store8<__nv_bfloat16>(p, pix, c, acc);
                         if (c + 8 < p.cout_p) epilogue_store8<__nv_bfloat16>(p, pix, c + 8, acc + 8);
+                    } else if (p.y_dtype == EDE_BF16X2) {
+                        if (c < p.cout_p) epilogue_store8<bf16x2_t>(p, pix, c, acc);
+                        if (c + 8 < p.cout_p) epilogue_store8<bf16x2_t>(p, pix, c + 8, acc + 8);
                     } else {
                         if (c < p.cout_p) epilogue_store8<float>(p, pix, c, acc);
                         if (c + 8 < p.cout_p) epilogue_store8<float>(p, pix, c + 8, acc + 8);
@@ -352,6 +358,7 @@ static bool umma_eligible(const EdeConv& a) {
     if (a.x_dtype != EDE_BF16 || a.x_layout != EDE_NHWC || a.relu_in) return false;
     if (a.sh != a.sw || (a.sh != 1 && a.sh != 2)) return false;
     if (a.kh * a.kw > 64 || a.kh > 8 || a.kw > 8) return false;
+    if (a.w_passes != 1 && a.w_passes != 2) return false;
     if ((a.x_cs | a.x_co | a.y_cs | a.y_co | a.cin_p | a.cout_p) & 7) return false;
     if (a.res && ((a.res_cs | a.res_co) & 7)) return false;
     if (a.w_umma_cin_p & 7) return false;
@@ -521,7 +528,8 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     }
     // ---- weights
     {
-        cuuint64_t dims[3] = {(cuuint64_t)a.w_umma_cin_p, (cuuint64_t)a.w_umma_cout_p, (cuuint64_t)(a.kh * a.kw)};
+        cuuint64_t dims[3] = {(cuuint64_t)a.w_umma_cin_p, (cuuint64_t)a.w_umma_cout_p,
+                              (cuuint64_t)(a.kh * a.kw * a.w_passes)};
         cuuint64_t strides[2] = {(cuuint64_t)a.w_umma_cin_p * 2, (cuuint64_t)a.w_umma_cin_p * 2 * a.w_umma_cout_p};
         cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)c.n_pad, 1};
         cuuint32_t es[3] = {1, 1, 1};
@@ -537,6 +545,7 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     p.ow = c.flat ? a.n * a.h * a.w : a.ow;
     p.tiles_w = c.tiles_w; p.tiles_h = c.tiles_h;
     p.a_mode = c.a_mode; p.ck_bytes = c.ck * 2; p.n_chunks = ceil_div(a.cin_p, c.ck);
+    p.w_passes = a.w_passes;
     p.kh = a.kh; p.kw = a.kw; p.sh = a.sh; p.sw = a.sw; p.pt = a.pt; p.pl = a.pl;
     p.bw = c.bw; p.bh = c.bh; p.pitch = c.pitch; p.box_bytes = c.pitch * c.box_rows * c.ck * 2;
     p.m_tiles = c.m_tiles; p.n_pad = c.n_pad;
@@ -577,7 +586,9 @@ int ede_umma_available(void) { return ede::get_encode_fn() != nullptr ? 1 : 0; }
 
 int ede_conv2d_umma_config(const EdeConv* a, EdeUmmaCfg* out) {
     EDE_REQUIRE(a != nullptr && out != nullptr, "ede_conv2d_umma_config: null argument");
-    ede::umma_config(*a, *out);
+    EdeConv b = *a;
+    if (b.w_passes == 0) b.w_passes = 1;
+    ede::umma_config(b, *out);
     return EDE_OK;
 }
 
@@ -591,10 +602,12 @@ int ede_conv2d(const EdeConv* a, void* stream) {
                 "ede_conv2d: output size inconsistent with input size");
     EDE_REQUIRE(a->x_layout == EDE_NHWC || (a->x_dtype == EDE_F32 && a->x_layout == EDE_NCHW),
                 "ede_conv2d: NCHW input must be fp32");
+    EdeConv b = *a;
+    if (b.w_passes == 0) b.w_passes = 1;
     EdeUmmaCfg cfg;
-    ede::umma_config(*a, cfg);
-    if (cfg.eligible) return ede::conv_umma_launch(*a, cfg, (cudaStream_t)stream);
-    return ede::conv_direct_launch(*a, (cudaStream_t)stream);
+    ede::umma_config(b, cfg);
+    if (cfg.eligible) return ede::conv_umma_launch(b, cfg, (cudaStream_t)stream);
+    return ede::conv_direct_launch(b, (cudaStream_t)stream);
 }
 
 }  // extern "C"

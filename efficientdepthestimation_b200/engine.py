@@ -24,16 +24,32 @@ from . import _cabi as A
 from . import prepack as P
 
 _PRECISION = os.environ.get("EDE_PRECISION", "bf16")
-_ELT = {A.F32: 4, A.BF16: 2}
+_ENCODER_PRECISION = os.environ.get("EDE_ENCODER_PRECISION", "bf16x2")
+_ELT = {A.F32: 4, A.BF16: 2, A.BF16X2: 4}
 _ALIGN = 1024
 
 
-def set_precision(mode: str) -> None:
-    """'bf16' (tcgen05 path, bf16 activations, fp32 accumulate) or 'fp32' (exact SIMT path)."""
-    global _PRECISION
+def set_precision(mode: str, encoder: Optional[str] = None) -> None:
+    """Precision of the forward plans compiled from now on.
+
+    mode 'bf16': tcgen05 tensor-core path, fp32 accumulation, bf16 activations in the decoders.
+        The ENCODER stage runs at `encoder` precision: 'bf16x2' (default; activations stored as split
+        bf16 hi+lo pairs = 16 mantissa bits, weights as w_hi+w_lo, 4 MMAs per plain-bf16 MMA -- needed
+        because randomly initialised BN+ReLU encoders amplify operand rounding ~100x)
+        or 'bf16' (plain bf16 everywhere, fastest, ~3e-2 / 2e-1 relative L1 on ENB0-/RN50-HU).
+    mode 'fp32': exact fp32 SIMT path for every operator (parity mode, 1e-3 tolerance)."""
+    global _PRECISION, _ENCODER_PRECISION
     if mode not in ("bf16", "fp32"):
         raise ValueError(f"unknown precision mode '{mode}' (expected 'bf16' or 'fp32')")
+    if encoder is not None:
+        if encoder not in ("bf16x2", "bf16"):
+            raise ValueError(f"unknown encoder precision '{encoder}' (expected 'bf16x2' or 'bf16')")
+        _ENCODER_PRECISION = encoder
     _PRECISION = mode
+
+
+def get_encoder_precision() -> str:
+    return _ENCODER_PRECISION
 
 
 def get_precision() -> str:
@@ -116,7 +132,13 @@ class Graph:
     def __init__(self, device: torch.device, precision: Optional[str] = None):
         self.device = device
         self.precision = precision or _PRECISION
-        self.act_dtype = A.BF16 if self.precision == "bf16" else A.F32
+        self.encoder_precision = _ENCODER_PRECISION
+        if self.precision == "fp32":
+            self.decoder_dtype = self.encoder_dtype = A.F32
+        else:
+            self.decoder_dtype = A.BF16
+            self.encoder_dtype = A.BF16X2 if self.encoder_precision == "bf16x2" else A.BF16
+        self.act_dtype = self.decoder_dtype       # dtype of newly created activations (see encoder_scope)
         self.dry = device.type != "cuda"          # host-only compile (tests without a GPU)
         self.ops: List[tuple] = []                # (kind, struct, [(field, Buf)], tag)
         self.bufs: List[Buf] = []
@@ -127,6 +149,19 @@ class Graph:
         self.tags: List[str] = []
 
     # ------------------------------------------------------------------ helpers
+    def encoder_scope(self):
+        """Context manager: operators emitted inside run at the encoder precision."""
+        g = self
+
+        class _Scope:
+            def __enter__(self_):
+                self_.prev = g.act_dtype
+                g.act_dtype = g.encoder_dtype
+
+            def __exit__(self_, *exc):
+                g.act_dtype = self_.prev
+        return _Scope()
+
     def new_buf(self, n, h, w, cs, dtype=None) -> Buf:
         b = Buf(n, h, w, cs, self.act_dtype if dtype is None else dtype)
         self.bufs.append(b)
@@ -169,7 +204,7 @@ class Graph:
     def input_nchw(self, shape) -> View:
         """Network input: fp32 NCHW tensor supplied at run time -> NHWC view (EDE_OP_TO_NHWC)."""
         n, c, h, w = (int(s) for s in shape)
-        v = self.new_view(n, h, w, c)
+        v = self.new_view(n, h, w, c, self.encoder_dtype)     # inputs keep 16 mantissa bits (4 B/lane)
         st = A.EdeLayout(src=None, dst=None, n=n, c=c, h=h, w=w, c_p=v.c_p, cs=v.buf.cs, co=v.co, dtype=v.dtype)
         i = self._add(A.OP_TO_NHWC, st, [("dst", v.buf)], "to_nhwc")
         self.inputs.append((i, (n, c, h, w)))
@@ -199,6 +234,12 @@ class Graph:
         oh = (x.h + pt + pb - kh) // stride + 1
         ow = (x.w + pl + pr - kw) // stride + 1
         cin = x.c
+        # a split-bf16 input is consumed as a plain bf16 tensor with twice the lanes (include/ede.h)
+        split_in = x.dtype == A.BF16X2
+        in_lanes = x.lanes
+        if split_in:
+            in_lanes = [v for g8 in range(0, x.c_p, 8) for v in x.lanes[g8:g8 + 8] * 2]
+        mul = 2 if split_in else 1
         out_lanes, fulls, scales, shifts, act_end = [], [], [], [], 0
         seen_plain = False
         for (wt, bn, bias, activated) in parts:
@@ -206,7 +247,7 @@ class Graph:
             if int(wt.shape[1]) != cin:
                 raise RuntimeError(f"{tag}: weight expects {int(wt.shape[1])} input channels, view has {cin}")
             omap = P.identity_map(co)
-            fulls.append(P.scatter_weight(wt, x.lanes, omap))
+            fulls.append(P.scatter_weight(wt, in_lanes, omap))
             sc, sf = P.fold_bn(co, _bn_dict(bn), bias, wt.device)
             scales.append(P.place_lanes(sc, omap))
             shifts.append(P.place_lanes(sf, omap))
@@ -227,21 +268,24 @@ class Graph:
             if (out.n, out.h, out.w, out.c_p) != (x.n, oh, ow, cout_p):
                 raise RuntimeError(f"{tag}: destination slice {out.n, out.h, out.w, out.c_p} does not match "
                                    f"conv output {x.n, oh, ow, cout_p}")
+        # hi+lo weights whenever the OUTPUT is kept at split precision (the accurate encoder path)
+        passes = 2 if (out.dtype == A.BF16X2 and self.precision != "fp32") else 1
         w_direct = self._dev(P.pack_direct(full))
-        w_umma, co16, ci64 = P.pack_umma(full)
+        w_umma, co16, ci64 = P.pack_umma(full, passes)
         w_umma = self._dev(w_umma)
         scale = self._dev(torch.cat(scales))
         shift = self._dev(torch.cat(shifts))
         if res is not None and res.dtype != out.dtype:
-            raise RuntimeError(f"{tag}: residual dtype must equal output dtype")
+            res = self.resize(res, (res.h, res.w), out_dtype=out.dtype, force=True, tag=tag + ".res_cast")
         st = A.EdeConv(x=None, y=None, res=None, scale=self._ptr(scale), shift=self._ptr(shift),
                        w_umma=self._ptr(w_umma), w_direct=self._ptr(w_direct),
-                       n=x.n, h=x.h, w=x.w, cin_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
+                       n=x.n, h=x.h, w=x.w, cin_p=x.c_p * mul, x_cs=x.buf.cs * mul, x_co=x.co * mul,
                        oh=oh, ow=ow, cout_p=cout_p, y_cs=out.buf.cs, y_co=out.co,
                        res_cs=res.buf.cs if res is not None else 0, res_co=res.co if res is not None else 0,
                        kh=kh, kw=kw, sh=stride, sw=stride, pt=pt, pl=pl, act=act, act_c_end=act_end,
-                       x_dtype=x.dtype, y_dtype=out.dtype, x_layout=A.NHWC, relu_in=1 if relu_in else 0,
-                       w_umma_cout_p=co16, w_umma_cin_p=ci64, force_direct=1 if self.precision == "fp32" else 0)
+                       x_dtype=A.BF16 if split_in else x.dtype, y_dtype=out.dtype, x_layout=A.NHWC,
+                       relu_in=1 if relu_in else 0, w_umma_cout_p=co16, w_umma_cin_p=ci64,
+                       force_direct=1 if self.precision == "fp32" else 0, w_passes=passes)
         refs = [("x", x.buf), ("y", out.buf)] + ([("res", res.buf)] if res is not None else [])
         self._add(A.OP_CONV, st, refs, tag)
         return out
@@ -262,7 +306,7 @@ class Graph:
         c = x.c
         if conv.groups != c or int(conv.weight.shape[0]) != c:
             raise RuntimeError(f"{tag}: not a depthwise convolution over {c} channels")
-        out = View(self.new_buf(x.n, oh, ow, x.c_p), 0, x.lanes)
+        out = View(self.new_buf(x.n, oh, ow, x.c_p, x.dtype), 0, x.lanes)
         wt = conv.weight.detach().float().reshape(c, k * k).t()            # [k*k][c]
         w = torch.zeros(k * k, x.c_p, dtype=torch.float32, device=wt.device)
         idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0], device=wt.device)
@@ -302,17 +346,17 @@ class Graph:
                        b2=self._ptr(b2), gate=self._ptr(gate), n=x.n, c=c, c_p=x.c_p, csq=csq,
                        inv_hw=1.0 / (x.h * x.w))
         self._add(A.OP_SE_FC, st, [], tag + ".fc")
-        out = View(self.new_buf(x.n, x.h, x.w, x.c_p), 0, x.lanes)
+        out = View(self.new_buf(x.n, x.h, x.w, x.c_p, x.dtype), 0, x.lanes)
         st = A.EdeSeScale(x=None, y=None, gate=self._ptr(gate), n=x.n, hw=x.h * x.w, c_p=x.c_p,
                           x_cs=x.buf.cs, x_co=x.co, y_cs=out.buf.cs, y_co=out.co, dtype=x.dtype)
         self._add(A.OP_SE_SCALE, st, [("x", x.buf), ("y", out.buf)], tag + ".scale")
         return out
 
-    def resize(self, x: View, size, out: Optional[View] = None, out_dtype=None, tag="resize") -> View:
-        """F.interpolate(x, size, mode='bilinear', align_corners=True)."""
+    def resize(self, x: View, size, out: Optional[View] = None, out_dtype=None, force=False, tag="resize") -> View:
+        """F.interpolate(x, size, mode='bilinear', align_corners=True) (identity size = exact copy/cast)."""
         oh, ow = int(size[0]), int(size[1])
         if out is None:
-            if (oh, ow) == (x.h, x.w) and (out_dtype is None or out_dtype == x.dtype):
+            if (oh, ow) == (x.h, x.w) and not force and (out_dtype is None or out_dtype == x.dtype):
                 return x                                   # identity resample
             out = View(self.new_buf(x.n, oh, ow, x.c_p, out_dtype), 0, x.lanes)
         st = A.EdeResize(x=None, y=None, n=x.n, h=x.h, w=x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co, oh=oh, ow=ow,
@@ -322,7 +366,7 @@ class Graph:
 
     def maxpool3x3s2(self, x: View, tag="maxpool") -> View:
         oh, ow = (x.h + 2 - 3) // 2 + 1, (x.w + 2 - 3) // 2 + 1
-        out = View(self.new_buf(x.n, oh, ow, x.c_p), 0, x.lanes)
+        out = View(self.new_buf(x.n, oh, ow, x.c_p, x.dtype), 0, x.lanes)
         st = A.EdeMaxPool(x=None, y=None, n=x.n, h=x.h, w=x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co, oh=oh, ow=ow,
                           y_cs=out.buf.cs, y_co=out.co, dtype=x.dtype)
         self._add(A.OP_MAXPOOL, st, [("x", x.buf), ("y", out.buf)], tag)
@@ -332,7 +376,7 @@ class Graph:
         """y = act(x) (+ x2)."""
         if x2 is not None and (x2.lanes != x.lanes or x2.dtype != x.dtype):
             raise RuntimeError("eltwise: operands must share lane layout and dtype")
-        out = View(self.new_buf(x.n, x.h, x.w, x.c_p), 0, x.lanes)
+        out = View(self.new_buf(x.n, x.h, x.w, x.c_p, x.dtype), 0, x.lanes)
         st = A.EdeEltwise(x=None, x2=None, y=None, n_pix=x.n * x.h * x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
                           x2_cs=x2.buf.cs if x2 is not None else 0, x2_co=x2.co if x2 is not None else 0,
                           y_cs=out.buf.cs, y_co=out.co, act=act, dtype=x.dtype)

@@ -49,12 +49,18 @@ def pack_direct(full: torch.Tensor) -> torch.Tensor:
     return full.permute(2, 3, 1, 0).reshape(kh * kw, ci, co).contiguous()
 
 
-def pack_umma(full: torch.Tensor) -> Tuple[torch.Tensor, int, int]:
-    """[cout_p][cin_p][kh][kw] -> bf16 [kh*kw][cout_p16][cin_p64] (K-major rows)."""
+def pack_umma(full: torch.Tensor, passes: int = 1) -> Tuple[torch.Tensor, int, int]:
+    """[cout_p][cin_p][kh][kw] -> bf16 [passes*kh*kw][cout_p16][cin_p64] (K-major rows).
+    passes=2 appends the low halves: taps [0,kh*kw) hold bf16(w), taps [kh*kw, 2*kh*kw) hold
+    bf16(w - bf16(w)), so that accumulating both gives 16 mantissa bits of the weight."""
     co, ci, kh, kw = full.shape
     co_p, ci_p = ceil_to(co, 16), ceil_to(ci, 64)
-    out = torch.zeros(kh * kw, co_p, ci_p, dtype=torch.bfloat16, device=full.device)
-    out[:, :co, :ci] = full.permute(2, 3, 0, 1).reshape(kh * kw, co, ci).to(torch.bfloat16)
+    taps = full.permute(2, 3, 0, 1).reshape(kh * kw, co, ci)
+    out = torch.zeros(passes * kh * kw, co_p, ci_p, dtype=torch.bfloat16, device=full.device)
+    hi = taps.to(torch.bfloat16)
+    out[:kh * kw, :co, :ci] = hi
+    if passes == 2:
+        out[kh * kw:, :co, :ci] = (taps - hi.float()).to(torch.bfloat16)
     return out.contiguous(), co_p, ci_p
 
 

@@ -14,7 +14,13 @@
  * element (n,h,w,c) of a view lives at base[((n*H+h)*W+w)*cs + co + c]; cs (channel
  * stride) and co (channel offset) are multiples of 8 elements so that every pixel slice
  * is 16-byte aligned, lanes between the real channel count and the next multiple of 8
- * hold zeros.  dtype: EDE_F32 or EDE_BF16.
+ * hold zeros.  dtype: EDE_F32, EDE_BF16 or EDE_BF16X2.
+ * EDE_BF16X2 ("split bf16") keeps 16 mantissa bits per value: every group of 8 lanes is stored as
+ * [8 x bf16 hi][8 x bf16 lo] (4 bytes per lane, value = hi + lo).  The same bytes seen as a plain
+ * EDE_BF16 view with twice the lanes (cs, co, c_p all doubled) are a valid tensor-core operand: with
+ * weights duplicated over the hi/lo lanes one K=16 MMA computes (hi+lo).w.  ede_conv2d therefore takes a
+ * split INPUT as x_dtype = EDE_BF16 with doubled lane numbers, and w_passes = 2 adds the low half of the
+ * weights (w_umma holds [w_hi ; w_lo] as 2*kh*kw taps) -- the accurate path of the encoders.
  */
 #ifndef EDE_H_
 #define EDE_H_
@@ -25,9 +31,9 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 1
+#define EDE_ABI_VERSION 2
 
-enum { EDE_F32 = 0, EDE_BF16 = 1 };
+enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
 enum { EDE_OK = 0, EDE_E_ARG = -1, EDE_E_CUDA = -2, EDE_E_UNSUPPORTED = -3, EDE_E_DRIVER = -4 };
 enum { EDE_NHWC = 0, EDE_NCHW = 1 };
@@ -57,6 +63,7 @@ typedef struct EdeConv {
     int32_t relu_in;        /* apply ReLU to x while loading (lasinger2019.py:153), direct path  */
     int32_t w_umma_cout_p, w_umma_cin_p;         /* padded dims of w_umma                        */
     int32_t force_direct;   /* 1: never take the tcgen05 path (fp32 parity mode / debugging)     */
+    int32_t w_passes;       /* 1, or 2: w_umma holds 2*kh*kw taps, [w_hi taps ; w_lo taps]          */
 } EdeConv;
 int ede_conv2d(const EdeConv* a, void* stream);
 

@@ -30,6 +30,16 @@ class Ctx:
         if self.taps is not None:
             self.taps[name] = t.detach().clone()
 
+    # Precision-study hooks (oracle/precision_study.py): identity in the oracle proper.  `aq` is applied
+    # to every stored activation where it is consumed, `wq` to dense-conv weights.
+    stage = ""
+
+    def aq(self, x):
+        return x
+
+    def wq(self, w):
+        return w
+
 
 def _interp(x, size):
     # F.interpolate(..., mode='bilinear', align_corners=True): modules.py:34, lasinger2019.py:244,289
@@ -37,7 +47,8 @@ def _interp(x, size):
 
 
 def _conv(c: Ctx, x, key, stride=1, padding=0, groups=1):
-    return F.conv2d(x, c.sd[key + ".weight"], c.sd.get(key + ".bias"), stride, padding, 1, groups)
+    w = c.sd[key + ".weight"]
+    return F.conv2d(c.aq(x), c.wq(w) if groups == 1 else w, c.sd.get(key + ".bias"), stride, padding, 1, groups)
 
 
 def _bn(c: Ctx, x, key, eps=1e-5):
@@ -60,7 +71,7 @@ def bottleneck(c: Ctx, x, p: str, stride: int, has_ds: bool):
     out = F.relu(_bn(c, _conv(c, out, p + "conv2", stride, 1), p + "bn2"))
     out = _bn(c, _conv(c, out, p + "conv3"), p + "bn3")
     res = _bn(c, _conv(c, x, p + "downsample.0", stride), p + "downsample.1") if has_ds else x
-    return F.relu(out + res)
+    return F.relu(out + c.aq(res))
 
 
 def resnet50_stages(c: Ctx, x, stem: str, layer_fmt: str) -> List[torch.Tensor]:
@@ -97,11 +108,13 @@ def mbconv(c: Ctx, x, p: str, b: spec.BlockSpec, res: int):
         h = _swish(_bn(c, _same_conv(c, h, p + "_expand_conv", 1, 1, res), p + "_bn0", spec.BN_EPS))
     h = _swish(_bn(c, _same_conv(c, h, p + "_depthwise_conv", b.kernel, b.stride, res, b.cexp),
                    p + "_bn1", spec.BN_EPS))
+    h = c.aq(h)
     s = F.adaptive_avg_pool2d(h, 1)
-    s = _conv(c, _swish(_conv(c, s, p + "_se_reduce")), p + "_se_expand")
+    s = F.conv2d(_swish(F.conv2d(s, c.sd[p + "_se_reduce.weight"], c.sd[p + "_se_reduce.bias"])),
+                 c.sd[p + "_se_expand.weight"], c.sd[p + "_se_expand.bias"])
     h = torch.sigmoid(s) * h
     h = _bn(c, _same_conv(c, h, p + "_project_conv", 1, 1, res), p + "_bn2", spec.BN_EPS)
-    return h + x if b.skip else h
+    return h + c.aq(x) if b.skip else h
 
 
 def effnet_block_prefixes(name: str, blocks_prefix: str) -> List[str]:
@@ -134,11 +147,11 @@ def efficientnet_stages(c: Ctx, x, name: str, blocks_prefix: str) -> List[torch.
 # ----------------------------------------------------------------------------- Hu decoder
 def up_projection(c: Ctx, x, p: str, size):
     """_UpProjection.forward, ReSIDE/models/modules.py:33-41."""
-    x = _interp(x, size)
+    x = _interp(c.aq(x), size)
     b1 = F.relu(_bn(c, _conv(c, x, p + "conv1", 1, 2), p + "bn1"))
     b1 = _bn(c, _conv(c, b1, p + "conv1_2", 1, 1), p + "bn1_2")
     b2 = _bn(c, _conv(c, x, p + "conv2", 1, 2), p + "bn2")
-    return F.relu(b1 + b2)
+    return F.relu(b1 + c.aq(b2))
 
 
 def hu_D(c: Ctx, b1, b2, b3, b4, p="D."):
@@ -169,14 +182,18 @@ def hu_encoder(c: Ctx, x, encoder: str):
     return efficientnet_stages(c, x, encoder, "E.blocks.")
 
 
-def hu_forward(sd: SD, x, encoder: str, calibrate=False, taps=None):
+def hu_forward(sd: SD, x, encoder: str, calibrate=False, taps=None, ctx=None):
     """model.forward, ReSIDE/models/net.py:26-32."""
-    c = Ctx(sd, calibrate, taps)
+    c = ctx if ctx is not None else Ctx(sd, calibrate, taps)
+    c.stage = "E"
     b1, b2, b3, b4 = hu_encoder(c, x, encoder)
+    c.stage = "D"
     d = hu_D(c, b1, b2, b3, b4)
     c.tap("D", d)
+    c.stage = "MFF"
     m = hu_MFF(c, b1, b2, b3, b4, d.shape[2:])
     c.tap("MFF", m)
+    c.stage = "R"
     return hu_R(c, torch.cat((d, m), 1))
 
 
