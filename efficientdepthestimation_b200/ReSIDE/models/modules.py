@@ -8,11 +8,17 @@ forward of every class is an operator emission into the B200 plan:
     applies the final ReLU (modules.py:36,39).
   * MFF / model: `torch.cat` (modules.py:265, net.py:30) is producers writing channel slices.
 """
+import os
+
 from torch import nn
 
 from ... import _cabi as A
 from ...efficientnet_pytorch import EfficientNet
 from ...engine import EdeModule, cat_views, emit
+
+
+_LOWRES_UPCONV = os.environ.get("EDE_LOWRES_UPCONV", "1") != "0"
+_LOWRES_MIN_CIN = int(os.environ.get("EDE_LOWRES_MIN_CIN", "192"))
 
 
 class _UpProjection(EdeModule, nn.Sequential):
@@ -28,9 +34,16 @@ class _UpProjection(EdeModule, nn.Sequential):
         self.bn2 = nn.BatchNorm2d(cout)
 
     def _emit(self, g, x, size, out=None, tag="up"):
-        x = g.resize(x, size, tag=tag + ".resize")
-        pair = g.conv(x, [(self.conv1.weight, self.bn1, None, True), (self.conv2.weight, self.bn2, None, False)],
-                      1, (2, 2, 2, 2), A.ACT_RELU, tag=tag + ".conv1+conv2")
+        parts = [(self.conv1.weight, self.bn1, None, True), (self.conv2.weight, self.bn2, None, False)]
+        grow = (int(size[0]) * int(size[1])) / float(x.h * x.w)
+        if (_LOWRES_UPCONV and g.precision != "fp32" and grow >= 3.0 and 2 * self.conv1.out_channels <= 64
+                and x.c >= _LOWRES_MIN_CIN):
+            # narrow projection of a wide, strongly upsampled map (MFF): contract Cin on the low-resolution grid.
+            # Below ~192 input channels the 25-tap gather on the CUDA cores costs more than the direct conv.
+            pair = g.upconv(x, size, parts, (2, 2, 2, 2), A.ACT_RELU, tag=tag + ".conv1+conv2")
+        else:
+            x = g.resize(x, size, tag=tag + ".resize")
+            pair = g.conv(x, parts, 1, (2, 2, 2, 2), A.ACT_RELU, tag=tag + ".conv1+conv2")
         half = pair.c_p // 2
         return g.conv_bn_act(pair.slice(0, half), self.conv1_2, self.bn1_2, A.ACT_RELU,
                              res=pair.slice(half, half), out=out, tag=tag + ".conv1_2")

@@ -15,7 +15,7 @@ F32, BF16, BF16X2 = 0, 1, 2
 ACT_NONE, ACT_RELU, ACT_SWISH, ACT_SIGMOID = 0, 1, 2, 3
 NHWC, NCHW = 0, 1
 (OP_CONV, OP_DWCONV, OP_SE_FC, OP_SE_SCALE, OP_RESIZE, OP_MAXPOOL, OP_ELTWISE, OP_TO_NHWC, OP_TO_NCHW,
- OP_ZERO) = range(1, 11)
+ OP_ZERO, OP_UPCONV) = range(1, 12)
 
 
 def _ints(*names):
@@ -71,6 +71,12 @@ class EdeLayout(Structure):
     _fields_ = [("src", c_void_p), ("dst", c_void_p)] + _ints("n", "c", "h", "w", "c_p", "cs", "co", "dtype")
 
 
+class EdeUpConv(Structure):
+    _fields_ = [("z", c_void_p), ("y", c_void_p), ("scale", c_void_p), ("shift", c_void_p)] + _ints(
+        "n", "h", "w", "z_cs", "z_co", "oh", "ow", "cgrp", "y_cs", "y_co", "y_dtype", "kh", "kw", "pt", "pl", "act",
+        "act_c_end")
+
+
 class _Zero(Structure):
     _fields_ = [("p", c_void_p), ("bytes", c_int64)]
 
@@ -78,7 +84,7 @@ class _Zero(Structure):
 class _OpU(Union):
     _fields_ = [("conv", EdeConv), ("dw", EdeDwConv), ("se_fc", EdeSeFc), ("se_scale", EdeSeScale),
                 ("resize", EdeResize), ("maxpool", EdeMaxPool), ("eltwise", EdeEltwise), ("layout", EdeLayout),
-                ("zero", _Zero)]
+                ("upconv", EdeUpConv), ("zero", _Zero)]
 
 
 class EdeOp(Structure):
@@ -87,13 +93,13 @@ class EdeOp(Structure):
 
 OP_FIELD = {OP_CONV: "conv", OP_DWCONV: "dw", OP_SE_FC: "se_fc", OP_SE_SCALE: "se_scale", OP_RESIZE: "resize",
             OP_MAXPOOL: "maxpool", OP_ELTWISE: "eltwise", OP_TO_NHWC: "layout", OP_TO_NCHW: "layout",
-            OP_ZERO: "zero"}
+            OP_ZERO: "zero", OP_UPCONV: "upconv"}
 
 # every symbol include/ede.h declares (checked by tests/test_cabi.py without a GPU)
-EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_dwconv2d", "ede_se_fc", "ede_se_scale",
+EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_dwconv2d", "ede_se_fc", "ede_se_scale",
            "ede_resize_bilinear_ac", "ede_resize_planes_f32", "ede_maxpool3x3s2", "ede_eltwise", "ede_nchw_to_nhwc", "ede_nhwc_to_nchw",
            "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_plan_run",
-           "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available"]
+           "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof"]
 
 _lib = None
 
@@ -111,7 +117,8 @@ def lib():
     for name, st in (("ede_conv2d", EdeConv), ("ede_dwconv2d", EdeDwConv), ("ede_se_fc", EdeSeFc),
                      ("ede_se_scale", EdeSeScale), ("ede_resize_bilinear_ac", EdeResize),
                      ("ede_maxpool3x3s2", EdeMaxPool), ("ede_eltwise", EdeEltwise),
-                     ("ede_nchw_to_nhwc", EdeLayout), ("ede_nhwc_to_nchw", EdeLayout)):
+                     ("ede_nchw_to_nhwc", EdeLayout), ("ede_nhwc_to_nchw", EdeLayout),
+                     ("ede_upconv_taps", EdeUpConv)):
         f = getattr(L, name)
         f.argtypes = [POINTER(st), c_void_p]
         f.restype = c_int32
@@ -134,6 +141,8 @@ def lib():
     L.ede_version.restype = c_int32
     L.ede_last_error.restype = C.c_char_p
     L.ede_umma_available.restype = c_int32
+    L.ede_debug_umma_prof.argtypes = [c_void_p, c_int64]
+    L.ede_debug_umma_prof.restype = c_int64
     _lib = L
     return L
 

@@ -83,6 +83,21 @@ __device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, ui
         "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// descriptors passed as (lo, hi) words: the hi word and the constant lo bits are loop invariant, only the
+// 14-bit start-address field changes per MMA, so the issuing thread spends ~6 instructions per tcgen05.mma
+__device__ __forceinline__ void tc_mma_bf16_w(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi,
+                                              uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t"
+        "}" ::"r"(d_tmem),
+        "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate));
+}
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
@@ -96,90 +111,155 @@ __device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sy
 
 // ------------------------------------------------------------------ kernel parameters
 constexpr int MAX_STAGES = 8;
+constexpr int NUM_THREADS = 192;             // warp 0 TMA, warp 1 MMA, warps 2..5 epilogue
+constexpr int EPI_THREADS = 128;
 
 struct alignas(64) UmmaParams {
     CUtensorMap tm_a;     // activations: (C, W, H, N) bf16
     CUtensorMap tm_b;     // weights: (Cin_p, Cout_p, taps) bf16
-    int oh, ow, tiles_w, tiles_h;
+    int oh, ow, tiles_w, tiles_h, n_img, n_tiles, total_tiles;
     int a_mode, ck_bytes, n_chunks, kh, kw, sh, sw, pt, pl, w_passes;
     int bw, bh, pitch, box_bytes;
-    int m_tiles, n_pad;
+    int m_tiles, n_pad, acc_cols;
     int a_stages, b_stages, a_stage_bytes, b_stage_bytes, b_tx_bytes;
-    int layout_type, sbo_bytes, tmem_cols, base_off_mode, flat;
+    int layout_type, sbo_bytes, tmem_cols, flat;
     uint32_t idesc;
     void* y;
     const void* res;
     const float* scale;
     const float* shift;
     int y_cs, y_co, res_cs, res_co, cout_p, act, act_c_end, y_dtype;
+    unsigned long long* prof;   // debug: 8 u64 per CTA (EDE_UMMA_PROF=1), else nullptr
 };
 
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr, const UmmaParams& p) {
-    uint64_t d = (uint64_t)((addr & 0x3FFFFu) >> 4);
-    d |= (uint64_t)1 << 16;                                  // leading byte offset (unused for swizzled K-major)
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P;\n\t"
+        "elect.sync _|P, 0xffffffff;\n\t"
+        "selp.b32 %0, 1, 0, P;\n\t"
+        "}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void epi_bar_sync() {      // named barrier 1 over the 128 epilogue threads
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+}
+
+// constant part of a K-major swizzled UMMA shared-memory descriptor (start address field = 0)
+__device__ __forceinline__ uint64_t smem_desc_const(const UmmaParams& p) {
+    uint64_t d = (uint64_t)1 << 16;                          // leading byte offset (unused for swizzled K-major)
     d |= (uint64_t)((uint32_t)p.sbo_bytes >> 4) << 32;       // stride between 8-row groups
     d |= (uint64_t)1 << 46;                                  // descriptor version (Blackwell)
-    if (p.base_off_mode) d |= (uint64_t)((addr >> 7) & 7u) << 49;
     d |= (uint64_t)p.layout_type << 61;
     return d;
 }
 
+struct TileCoord {
+    int ntile, img, oh0, ow0;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) {
+    TileCoord t;
+    const int per_ntile = p.n_img * p.tiles_h * p.tiles_w;
+    t.ntile = tile / per_ntile;
+    int r = tile - t.ntile * per_ntile;
+    const int per_img = p.tiles_h * p.tiles_w;
+    t.img = r / per_img;
+    r -= t.img * per_img;
+    const int th = r / p.tiles_w, tw = r - th * p.tiles_w;
+    const int tile_w_pix = p.a_mode == 0 ? p.bw : p.bw * p.m_tiles;   // output columns covered by one tile
+    t.ow0 = tw * tile_w_pix;
+    t.oh0 = th * p.bh;
+    return t;
+}
+
+// one 8-channel group of the epilogue: folded BN, residual, activation, typed store
 template <typename TY>
-__device__ __forceinline__ void epilogue_store8(const UmmaParams& p, long long pix, int c, const uint32_t* acc) {
-    float v[8], sc[8], sf[8];
-    *reinterpret_cast<float4*>(sc) = __ldg(reinterpret_cast<const float4*>(p.scale + c));
-    *reinterpret_cast<float4*>(sc + 4) = __ldg(reinterpret_cast<const float4*>(p.scale + c + 4));
-    *reinterpret_cast<float4*>(sf) = __ldg(reinterpret_cast<const float4*>(p.shift + c));
-    *reinterpret_cast<float4*>(sf + 4) = __ldg(reinterpret_cast<const float4*>(p.shift + c + 4));
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = fmaf(__uint_as_float(acc[j]), sc[j], sf[j]);
+__device__ __forceinline__ void epilogue_store8(const UmmaParams& p, long long pix, int c, int c_local,
+                                                const uint32_t* acc, const float* s_scale, const float* s_shift) {
+    float v[8];
+    const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c_local);
+    const float4 s1 = *reinterpret_cast<const float4*>(s_scale + c_local + 4);
+    const float4 f0 = *reinterpret_cast<const float4*>(s_shift + c_local);
+    const float4 f1 = *reinterpret_cast<const float4*>(s_shift + c_local + 4);
+    v[0] = fmaf(__uint_as_float(acc[0]), s0.x, f0.x); v[1] = fmaf(__uint_as_float(acc[1]), s0.y, f0.y);
+    v[2] = fmaf(__uint_as_float(acc[2]), s0.z, f0.z); v[3] = fmaf(__uint_as_float(acc[3]), s0.w, f0.w);
+    v[4] = fmaf(__uint_as_float(acc[4]), s1.x, f1.x); v[5] = fmaf(__uint_as_float(acc[5]), s1.y, f1.y);
+    v[6] = fmaf(__uint_as_float(acc[6]), s1.z, f1.z); v[7] = fmaf(__uint_as_float(acc[7]), s1.w, f1.w);
     if (p.res) {
         float r[8];
         load8<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co + c, r);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] += r[j];
     }
-    if (p.act != EDE_ACT_NONE) {
+    if (c < p.act_c_end) {                 // act_c_end is a multiple of 8: whole groups are (in)active
+        if (p.act == EDE_ACT_RELU) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-            if (c + j < p.act_c_end) v[j] = apply_act(v[j], p.act);
+            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+        } else if (p.act == EDE_ACT_SWISH) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = v[j] / (1.f + __expf(-v[j]));
+        } else if (p.act == EDE_ACT_SIGMOID) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = 1.f / (1.f + __expf(-v[j]));
+        }
     }
     store8<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co + c, v);
 }
 
-__global__ void __launch_bounds__(192) conv_umma_kernel(const __grid_constant__ UmmaParams p) {
+template <typename TY>
+__device__ __forceinline__ void epilogue_store16(const UmmaParams& p, long long pix, int c, int c_local,
+                                                 const uint32_t* acc, const float* s_scale, const float* s_shift) {
+    if (c < p.cout_p) epilogue_store8<TY>(p, pix, c, c_local, acc, s_scale, s_shift);
+    if (c + 8 < p.cout_p) epilogue_store8<TY>(p, pix, c + 8, c_local + 8, acc + 8, s_scale, s_shift);
+}
+
+// Persistent, warp-specialised implicit-GEMM convolution.  One CTA per SM walks the tile list
+// (tile = n-tile x image x output patch) with a static stride; TMEM holds TWO accumulator stages so the
+// epilogue of tile i overlaps the MMAs of tile i+1; the operand rings run on across tile boundaries.
+__global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_constant__ UmmaParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_base = smem_base;
     const uint32_t b_base = a_base + (uint32_t)p.a_stages * p.a_stage_bytes;
     const uint32_t bar_base = b_base + (uint32_t)p.b_stages * p.b_stage_bytes;
-    // barriers: a_full[8] a_empty[8] b_full[8] b_empty[8] tmem_full, then the TMEM base slot
+    // barriers: a_full[8] a_empty[8] b_full[8] b_empty[8] acc_full[2] acc_empty[2], TMEM base slot, scale/shift
     auto a_full = [&](int s) { return bar_base + 8u * s; };
     auto a_empty = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
     auto b_full = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
     auto b_empty = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + s); };
-    const uint32_t tmem_full = bar_base + 8u * (4 * MAX_STAGES);
-    const uint32_t tmem_slot = tmem_full + 8u;
+    auto acc_full = [&](int s) { return bar_base + 8u * (4 * MAX_STAGES + s); };
+    auto acc_empty = [&](int s) { return bar_base + 8u * (4 * MAX_STAGES + 2 + s); };
+    const uint32_t tmem_slot = bar_base + 8u * (4 * MAX_STAGES + 4);
+    float* const s_scale = reinterpret_cast<float*>(smem_raw + (bar_base - smem_u32(smem_raw)) + 512);
+    float* const s_shift = s_scale + 256;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-
-    // tile coordinates
-    const int tiles_per_img = p.tiles_w * p.tiles_h;
-    const int img = blockIdx.x / tiles_per_img;
-    const int t_in = blockIdx.x - img * tiles_per_img;
-    const int th = t_in / p.tiles_w, tw = t_in - th * p.tiles_w;
-    const int ntile = blockIdx.y;
     const int sp_taps = p.kh * p.kw;              // spatial taps
     const int taps = sp_taps * p.w_passes;        // weight tiles per channel chunk ([w_hi taps ; w_lo taps])
-    const int tile_w_pix = p.a_mode == 0 ? p.bw : p.bw * p.m_tiles;   // output columns covered by this CTA
-    const int ow0 = tw * tile_w_pix, oh0 = th * p.bh;
+    unsigned long long prof_t0 = 0;
+    if (p.prof && threadIdx.x == 0) prof_t0 = gtime();
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < MAX_STAGES; ++s) {
             mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1);
             mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1);
         }
-        mbar_init(tmem_full, 1);
+        mbar_init(acc_full(0), 1); mbar_init(acc_full(1), 1);
+        mbar_init(acc_empty(0), 4); mbar_init(acc_empty(1), 4);       // one arrival per epilogue warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -195,128 +275,198 @@ __global__ void __launch_bounds__(192) conv_umma_kernel(const __grid_constant__ 
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_addr) : "r"(tmem_slot) : "memory");
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
-            int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0;
-            const int ck = p.ck_bytes >> 1;
-            for (int chunk = 0; chunk < p.n_chunks; ++chunk) {
-                if (p.a_mode == 0) {
+        // ===================== TMA producer (whole warp walks the loop, one elected lane issues) ==========
+        int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0;
+        const int ck = p.ck_bytes >> 1;
+        const int a_mode = p.a_mode, n_chunks = p.n_chunks, m_tiles = p.m_tiles, kw = p.kw;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            const TileCoord t = decode_tile(p, tile);
+            for (int chunk = 0; chunk < n_chunks; ++chunk) {
+                if (a_mode == 0) {
                     mbar_wait(a_empty(a_st), a_ph ^ 1);
-                    mbar_expect_tx(a_full(a_st), (uint32_t)p.box_bytes);
-                    tma_load_4d(a_base + a_st * p.a_stage_bytes, &p.tm_a, a_full(a_st), chunk * ck, ow0 - p.pl,
-                                oh0 - p.pt, img);
+                    if (elect_one()) {
+                        mbar_expect_tx(a_full(a_st), (uint32_t)p.box_bytes);
+                        tma_load_4d(a_base + a_st * p.a_stage_bytes, &p.tm_a, a_full(a_st), chunk * ck, t.ow0 - p.pl,
+                                    t.oh0 - p.pt, t.img);
+                    }
                     if (++a_st == p.a_stages) { a_st = 0; a_ph ^= 1; }
                 }
+                int ky = 0, kx = 0;
                 for (int tap = 0; tap < taps; ++tap) {
-                    if (p.a_mode != 0) {
-                        const int stap = tap >= sp_taps ? tap - sp_taps : tap;
-                        const int ky = stap / p.kw, kx = stap - ky * p.kw;
+                    if (tap == sp_taps) { ky = 0; kx = 0; }
+                    if (a_mode != 0) {
                         mbar_wait(a_empty(a_st), a_ph ^ 1);
-                        mbar_expect_tx(a_full(a_st), (uint32_t)(p.m_tiles * 128 * p.ck_bytes));
-                        for (int m = 0; m < p.m_tiles; ++m)
-                            tma_load_4d(a_base + a_st * p.a_stage_bytes + m * 128 * p.ck_bytes, &p.tm_a, a_full(a_st),
-                                        chunk * ck, (ow0 + m * p.bw) * p.sw - p.pl + kx, oh0 * p.sh - p.pt + ky,
-                                        img);
+                        if (elect_one()) {
+                            mbar_expect_tx(a_full(a_st), (uint32_t)(m_tiles * 128 * p.ck_bytes));
+                            for (int m = 0; m < m_tiles; ++m)
+                                tma_load_4d(a_base + a_st * p.a_stage_bytes + m * 128 * p.ck_bytes, &p.tm_a,
+                                            a_full(a_st), chunk * ck, (t.ow0 + m * p.bw) * p.sw - p.pl + kx,
+                                            t.oh0 * p.sh - p.pt + ky, t.img);
+                        }
                         if (++a_st == p.a_stages) { a_st = 0; a_ph ^= 1; }
                     }
                     mbar_wait(b_empty(b_st), b_ph ^ 1);
-                    mbar_expect_tx(b_full(b_st), (uint32_t)p.b_tx_bytes);
-                    tma_load_3d(b_base + b_st * p.b_stage_bytes, &p.tm_b, b_full(b_st), chunk * ck,
-                                ntile * p.n_pad, tap);
+                    if (elect_one()) {
+                        mbar_expect_tx(b_full(b_st), (uint32_t)p.b_tx_bytes);
+                        tma_load_3d(b_base + b_st * p.b_stage_bytes, &p.tm_b, b_full(b_st), chunk * ck,
+                                    t.ntile * p.n_pad, tap);
+                    }
                     if (++b_st == p.b_stages) { b_st = 0; b_ph ^= 1; }
+                    if (++kx == kw) { kx = 0; ++ky; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0;
-            const int ksteps = p.ck_bytes >> 5;        // 32 bytes of K (16 bf16) per tcgen05.mma
+        // ===================== MMA issuer (warp-uniform loop state, one elected lane issues) ==============
+        const int a_mode = p.a_mode, m_tiles = p.m_tiles, n_pad = p.n_pad, n_chunks = p.n_chunks;
+        const int a_stages = p.a_stages, b_stages = p.b_stages, kw = p.kw, pitch = p.pitch;
+        const uint32_t ck16 = (uint32_t)p.ck_bytes >> 4;            // (bytes >> 4) units of the address field
+        const uint32_t a_stage16 = (uint32_t)p.a_stage_bytes >> 4, b_stage16 = (uint32_t)p.b_stage_bytes >> 4;
+        const uint32_t m_step16 = 128u * ck16;                       // 128 pixel rows
+        const int ksteps = p.ck_bytes >> 5;                          // 32 bytes of K (16 bf16) per tcgen05.mma
+        const uint32_t idesc = p.idesc;
+        const uint64_t dconst = smem_desc_const(p);
+        const uint32_t desc_hi = (uint32_t)(dconst >> 32);
+        const uint32_t a_base16 = (uint32_t)dconst + (a_base >> 4), b_base16 = (uint32_t)dconst + (b_base >> 4);
+        int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0, acc_st = 0, acc_ph = 0;
+        long long w_ops = 0, w_acc = 0;
+        unsigned long long t_start = 0;
+        if (p.prof) t_start = gtime();
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            long long c0 = p.prof ? clock64() : 0;
+            mbar_wait(acc_empty(acc_st), acc_ph ^ 1);                // epilogue has drained this accumulator stage
+            tc_fence_after();
+            if (p.prof) w_acc += clock64() - c0;
+            const uint32_t d_base = tmem_addr + (uint32_t)(acc_st * p.acc_cols);
             uint32_t accum = 0;
-            for (int chunk = 0; chunk < p.n_chunks; ++chunk) {
-                if (p.a_mode == 0) mbar_wait(a_full(a_st), a_ph);
+            for (int chunk = 0; chunk < n_chunks; ++chunk) {
+                if (a_mode == 0) {
+                    c0 = p.prof ? clock64() : 0;
+                    mbar_wait(a_full(a_st), a_ph);
+                    if (p.prof) w_ops += clock64() - c0;
+                }
+                int ky = 0, kx = 0;
                 for (int tap = 0; tap < taps; ++tap) {
-                    if (p.a_mode != 0) mbar_wait(a_full(a_st), a_ph);
+                    c0 = p.prof ? clock64() : 0;
+                    if (a_mode != 0) mbar_wait(a_full(a_st), a_ph);
                     mbar_wait(b_full(b_st), b_ph);
+                    if (p.prof) w_ops += clock64() - c0;
                     tc_fence_after();
-                    int shift_rows = 0;
-                    if (p.a_mode == 0) {
-                        const int stap = tap >= sp_taps ? tap - sp_taps : tap;
-                        const int ky = stap / p.kw, kx = stap - ky * p.kw;
-                        shift_rows = ky * p.pitch + kx;
-                    }
-                    const uint32_t a_addr = a_base + a_st * p.a_stage_bytes + shift_rows * p.ck_bytes;
-                    const uint32_t b_addr = b_base + b_st * p.b_stage_bytes;
-                    for (int m = 0; m < p.m_tiles; ++m) {
-                        uint32_t acc_m = accum;
-                        for (int k = 0; k < ksteps; ++k) {
-                            const uint64_t ad = make_smem_desc(a_addr + m * 128 * p.ck_bytes + k * 32, p);
-                            const uint64_t bd = make_smem_desc(b_addr + k * 32, p);
-                            tc_mma_bf16(tmem_addr + m * p.n_pad, ad, bd, p.idesc, acc_m);
-                            acc_m = 1;
+                    if (tap == sp_taps) { ky = 0; kx = 0; }
+                    const uint32_t shift16 = a_mode == 0 ? (uint32_t)(ky * pitch + kx) * ck16 : 0u;
+                    const uint32_t a0 = a_base16 + (uint32_t)a_st * a_stage16 + shift16;
+                    const uint32_t b0 = b_base16 + (uint32_t)b_st * b_stage16;
+                    if (elect_one()) {
+                        uint32_t am = a0, dm = d_base;
+                        for (int m = 0; m < m_tiles; ++m) {
+                            tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, accum);
+                            for (int k = 1; k < ksteps; ++k)
+                                tc_mma_bf16_w(dm, am + 2u * k, b0 + 2u * k, desc_hi, idesc, 1u);
+                            am += m_step16;
+                            dm += (uint32_t)n_pad;
                         }
+                        tc_commit(b_empty(b_st));
+                        if (a_mode != 0) tc_commit(a_empty(a_st));
                     }
+                    __syncwarp();
                     accum = 1;
-                    tc_commit(b_empty(b_st));
-                    if (++b_st == p.b_stages) { b_st = 0; b_ph ^= 1; }
-                    if (p.a_mode != 0) {
-                        tc_commit(a_empty(a_st));
-                        if (++a_st == p.a_stages) { a_st = 0; a_ph ^= 1; }
+                    if (++b_st == b_stages) { b_st = 0; b_ph ^= 1; }
+                    if (a_mode != 0) {
+                        if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; }
                     }
+                    if (++kx == kw) { kx = 0; ++ky; }
                 }
-                if (p.a_mode == 0) {
-                    tc_commit(a_empty(a_st));
-                    if (++a_st == p.a_stages) { a_st = 0; a_ph ^= 1; }
+                if (a_mode == 0) {
+                    if (elect_one()) tc_commit(a_empty(a_st));
+                    __syncwarp();
+                    if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; }
                 }
             }
-            tc_commit(tmem_full);
+            if (elect_one()) tc_commit(acc_full(acc_st));
+            __syncwarp();
+            if (++acc_st == 2) { acc_st = 0; acc_ph ^= 1; }
         }
-        __syncwarp();
+        if (p.prof && lane == 0) {
+            unsigned long long* q = p.prof + (size_t)blockIdx.x * 8;
+            q[1] = t_start; q[2] = gtime(); q[4] = (unsigned long long)w_ops; q[5] = (unsigned long long)w_acc;
+        }
     } else {
-        // ===================== epilogue (warps 2..5) =====================
+        // ===================== epilogue (warps 2..5): TMEM -> BN/residual/activation -> NHWC stores ========
         const int quarter = warp & 3;                 // TMEM lanes [32q, 32q+32) are visible to warp%4 == q
-        mbar_wait(tmem_full, 0);
-        tc_fence_after();
         const int r = quarter * 32 + lane;
-        for (int m = 0; m < p.m_tiles; ++m) {
-            // which output pixel does accumulator row (m, r) hold?
-            int oh, ow;
-            bool valid;
-            if (p.a_mode == 0) {
-                const int f = m * 128 + r;
-                const int fr = f / p.pitch, fc = f - fr * p.pitch;
-                oh = oh0 + fr; ow = ow0 + fc;
-                valid = fc < p.bw && fr < p.bh;
-            } else {
-                const int fr = r / p.bw, fc = r - fr * p.bw;
-                oh = oh0 + fr; ow = ow0 + m * p.bw + fc;
-                valid = true;
+        const int et = threadIdx.x - 64;              // 0..127
+        int acc_st = 0, acc_ph = 0, n_done = 0;
+        long long w_full = 0;
+        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+            const TileCoord t = decode_tile(p, tile);
+            epi_bar_sync();                           // everyone is done with the previous tile's scale/shift
+            for (int e = et; e < p.n_pad; e += EPI_THREADS) {
+                const int c = t.ntile * p.n_pad + e;
+                const bool in = c < p.cout_p;
+                s_scale[e] = in ? __ldg(p.scale + c) : 0.f;
+                s_shift[e] = in ? __ldg(p.shift + c) : 0.f;
             }
-            valid = valid && oh < p.oh && ow < p.ow;
-            const long long pix = ((long long)img * p.oh + oh) * p.ow + ow;
-            for (int c0 = 0; c0 < p.n_pad; c0 += 16) {
-                uint32_t acc[16];
-                tc_ld16(tmem_addr + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(m * p.n_pad + c0), acc);
-                tc_ld_wait();
-                if (valid) {
-                    const int c = ntile * p.n_pad + c0;
-                    if (p.y_dtype == EDE_BF16) {
-                        if (c < p.cout_p) epilogue_store8<__nv_bfloat16>(p, pix, c, acc);
-                        if (c + 8 < p.cout_p) epilogue_store8<__nv_bfloat16>(p, pix, c + 8, acc + 8);
-                    } else if (p.y_dtype == EDE_BF16X2) {
-                        if (c < p.cout_p) epilogue_store8<bf16x2_t>(p, pix, c, acc);
-                        if (c + 8 < p.cout_p) epilogue_store8<bf16x2_t>(p, pix, c + 8, acc + 8);
-                    } else {
-                        if (c < p.cout_p) epilogue_store8<float>(p, pix, c, acc);
-                        if (c + 8 < p.cout_p) epilogue_store8<float>(p, pix, c + 8, acc + 8);
+            epi_bar_sync();
+            const long long c0 = p.prof ? clock64() : 0;
+            mbar_wait(acc_full(acc_st), acc_ph);
+            if (p.prof) w_full += clock64() - c0;
+            tc_fence_after();
+            const uint32_t t_base = tmem_addr + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_st * p.acc_cols);
+            for (int m = 0; m < p.m_tiles; ++m) {
+                // which output pixel does accumulator row (m, r) hold?
+                int oh, ow;
+                bool valid;
+                if (p.a_mode == 0) {
+                    const int f = m * 128 + r;
+                    const int fr = f / p.pitch, fc = f - fr * p.pitch;
+                    oh = t.oh0 + fr; ow = t.ow0 + fc;
+                    valid = fc < p.bw && fr < p.bh;
+                } else {
+                    const int fr = r / p.bw, fc = r - fr * p.bw;
+                    oh = t.oh0 + fr; ow = t.ow0 + m * p.bw + fc;
+                    valid = true;
+                }
+                valid = valid && oh < p.oh && ow < p.ow;
+                const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
+                const uint32_t t_row = t_base + (uint32_t)(m * p.n_pad);
+                uint32_t acc0[16], acc1[16];
+                tc_ld16(t_row, acc0);
+                for (int c0l = 0; c0l < p.n_pad; c0l += 32) {
+                    tc_ld_wait();
+                    const bool more1 = c0l + 16 < p.n_pad;
+                    if (more1) tc_ld16(t_row + (uint32_t)(c0l + 16), acc1);        // in flight while acc0 is stored
+                    if (valid) {
+                        const int c = t.ntile * p.n_pad + c0l;
+                        if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, c, c0l, acc0, s_scale, s_shift);
+                        else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, c, c0l, acc0, s_scale, s_shift);
+                        else epilogue_store16<float>(p, pix, c, c0l, acc0, s_scale, s_shift);
+                    }
+                    if (!more1) break;
+                    tc_ld_wait();
+                    if (c0l + 32 < p.n_pad) tc_ld16(t_row + (uint32_t)(c0l + 32), acc0);
+                    if (valid) {
+                        const int c = t.ntile * p.n_pad + c0l + 16;
+                        if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
+                        else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
+                        else epilogue_store16<float>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
                     }
                 }
             }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty(acc_st));            // this warp has drained its TMEM lanes
+            if (++acc_st == 2) { acc_st = 0; acc_ph ^= 1; }
+            ++n_done;
+        }
+        if (p.prof && et == 0) {
+            unsigned long long* q = p.prof + (size_t)blockIdx.x * 8;
+            q[3] = gtime(); q[6] = (unsigned long long)w_full; q[7] = (unsigned long long)n_done;
         }
     }
 
     tc_fence_before();
     __syncthreads();
+    if (p.prof && threadIdx.x == 0) p.prof[(size_t)blockIdx.x * 8] = prof_t0;
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_addr),
@@ -351,7 +501,7 @@ static int env_int(const char* name, int dflt) {
 }
 
 constexpr int SMEM_BUDGET = 200 * 1024;      // operand rings; barriers + alignment slack on top
-constexpr int SMEM_EXTRA = 1024 + 512;
+constexpr int SMEM_EXTRA = 1024 + 512 + 2048;   // alignment slack + barriers + scale/shift slice
 
 static bool umma_eligible(const EdeConv& a) {
     if (a.force_direct || a.w_umma == nullptr) return false;
@@ -365,17 +515,11 @@ static bool umma_eligible(const EdeConv& a) {
     return true;
 }
 
-static int pick_ck(int cin_p) {
-    // channels per K chunk: trade zero-padded K against TMA/MMA granularity
-    const int cand[3] = {64, 32, 16};
-    const double pen[3] = {1.00, 1.04, 1.12};
-    int best = 64;
-    double best_cost = 1e30;
-    for (int i = 0; i < 3; ++i) {
-        double cost = (double)round_up(cin_p, cand[i]) * pen[i];
-        if (cost < best_cost) { best_cost = cost; best = cand[i]; }
-    }
-    return best;
+// operand ring depth: the persistent kernel owns a whole SM, so use the full smem budget
+static int fit_stages(int fixed_bytes, int stage_bytes, int /*want*/) {
+    int s = (SMEM_BUDGET - fixed_bytes) / stage_bytes;
+    if (s > MAX_STAGES) s = MAX_STAGES;
+    return s;
 }
 
 static int pow2_cols(int c) {
@@ -384,109 +528,133 @@ static int pow2_cols(int c) {
     return v;
 }
 
-constexpr int SMEM_2CTA = 98 * 1024;          // operand budget that still lets two CTAs share an SM
-
-// number of ring stages: prefer a footprint that allows 2 CTAs/SM (one CTA's epilogue then
-// overlaps the other's MMAs), else use the whole SM
-static int fit_stages(int fixed_bytes, int stage_bytes, int want) {
-    int s = (SMEM_2CTA - fixed_bytes) / stage_bytes;
-    if (s < want) s = (SMEM_BUDGET - fixed_bytes) / stage_bytes;
-    if (s > MAX_STAGES) s = MAX_STAGES;
-    return s;
+// ---- tile configuration by an explicit time model (numbers measured on B200, tools/micro/mma_rate.cu):
+// one tcgen05.mma (M=128, K=16, operands in smem) takes max(N/2, base) cycles with base = 97 / 154 / 214 for
+// the 128B / 64B / 32B swizzle (the A-operand fetch dominates below N ~ 192), independent of the start
+// address alignment.  Operand bytes per tile are charged at the share of L2->SM bandwidth one SM gets.
+static double mma_cycles(int swizzle_bytes, int n_pad) {
+    const double base = swizzle_bytes == 128 ? 97.0 : swizzle_bytes == 64 ? 154.0 : 214.0;
+    return std::max(base, n_pad * 0.5);
 }
+constexpr double L2_BYTES_PER_CLK_PER_SM = 36.0;     // ~5.3 KB/clk chip-wide over 148 SMs
+constexpr double EPI_CYCLES_PER_ROW_COL = 0.012;     // epilogue cost per accumulator element (4 warps)
+constexpr int NUM_SMS_MODEL = 148;
 
 static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     memset(&c, 0, sizeof(c));
     if (!umma_eligible(a)) return;
     const int force_mode = env_int("EDE_UMMA_MODE", -1);
     const int force_ck = env_int("EDE_UMMA_CK", 0);
-    const int ck = (force_ck == 16 || force_ck == 32 || force_ck == 64) ? force_ck : pick_ck(a.cin_p);
-    const int ck_bytes = ck * 2;
+    const int force_npad = env_int("EDE_UMMA_NPAD", 0);
     const int n16 = round_up(a.cout_p, 16);
-    const int n_tiles = ceil_div(n16, 128);
-    const int n_pad = round_up(ceil_div(n16, n_tiles), 16);
-    const int b_bytes = round_up(n_pad * ck_bytes, 1024);
     const bool is_1x1 = a.kh == 1 && a.kw == 1 && a.sh == 1 && a.pt == 0 && a.pl == 0 && a.oh == a.h && a.ow == a.w;
     const int OH = is_1x1 ? 1 : a.oh;
     const long long OWl = is_1x1 ? (long long)a.n * a.h * a.w : a.ow;
     if (OWl > 0x7fffffffLL) return;
     const int OW = (int)OWl;
-    const int max_t = 512 / n_pad;
+    const int n_img = is_1x1 ? 1 : a.n;
+    const int taps_w = a.kh * a.kw * a.w_passes;
 
     EdeUmmaCfg best{};
-    double best_score = -1;
-    // ---- per-tap candidates
-    for (int bw = 128; bw >= 1; bw >>= 1) {
-        const int bh = 128 / bw;
-        if (bw * a.sw > 256 || bh * a.sh > 256) continue;
-        if (is_1x1 && bh != 1) continue;
-        for (int T = 4; T >= 1; T >>= 1) {
-            if (T > max_t) continue;
-            const int a_bytes = T * 128 * ck_bytes;
-            const int stages = fit_stages(0, a_bytes + b_bytes, 4);
-            if (stages < 3) continue;
-            const int tiles_w = ceil_div(OW, bw * T), tiles_h = ceil_div(OH, bh);
-            const double frac = (double)OH * OW / ((double)tiles_w * tiles_h * T * 128);
-            const double score = frac + 0.004 * T + 0.01 * (bw >= 8) + 0.01 * (bw >= 16) -
-                                 0.02 * (pow2_cols(T * n_pad) > 256);
-            if (score > best_score) {
-                best_score = score;
-                best.a_mode = 1; best.bh = bh; best.bw = bw; best.pitch = bw; best.box_rows = bh;
-                best.m_tiles = T; best.a_stages = best.b_stages = stages;
-                best.a_stage_bytes = a_bytes; best.tiles_w = tiles_w; best.tiles_h = tiles_h;
-                best.useful_frac = frac;
+    double best_time = 1e300;
+    const int cks[3] = {64, 32, 16};
+    for (int ci = 0; ci < 3; ++ci) {
+        const int ck = cks[ci];
+        if (force_ck && force_ck != ck) continue;
+        const int ck_bytes = ck * 2;
+        const int n_chunks = ceil_div(a.cin_p, ck);
+        const int ksteps = ck / 16;
+        for (int n_tiles = ceil_div(n16, 256); n_tiles <= ceil_div(n16, 16) && n_tiles <= 64; ++n_tiles) {
+            const int n_pad = round_up(ceil_div(n16, n_tiles), 16);
+            if (n_pad > 256) continue;
+            if (force_npad && n_pad != force_npad) continue;
+            if (n_tiles > ceil_div(n16, 256) && n_pad < 96) break;      // finer N splits never pay
+            const int b_bytes = round_up(n_pad * ck_bytes, 1024);
+            const int max_t = 256 / n_pad;                // two accumulator stages share the 512 TMEM columns
+            if (max_t < 1) continue;
+            const double t_mma = mma_cycles(ck_bytes, n_pad);
+            auto consider = [&](const EdeUmmaCfg& cand, double a_bytes_tile, double b_bytes_tile) {
+                const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img * n_tiles;
+                const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
+                const double mma = (double)n_chunks * taps_w * cand.m_tiles * ksteps * t_mma;
+                const double mem = (a_bytes_tile + b_bytes_tile) / L2_BYTES_PER_CLK_PER_SM;
+                const double epi = cand.m_tiles * 128.0 * n_pad * EPI_CYCLES_PER_ROW_COL * 4.0 + 600.0;
+                // operand ring too shallow to cover the L2 latency (~1500 clk) -> exposed waits
+                const double per_stage = mma / std::max(1, n_chunks * taps_w);
+                const double lat = std::max(0.0, 1500.0 - cand.b_stages * per_stage) * 0.15 * n_chunks * taps_w /
+                                   std::max(1, cand.b_stages);
+                const double t = rounds * (std::max(std::max(mma, mem), epi) + lat + 300.0) + 4000.0;
+                if (t < best_time) {
+                    best_time = t;
+                    best = cand;
+                    best.ck = ck; best.swizzle = ck_bytes; best.n_pad = n_pad; best.n_tiles = n_tiles;
+                    best.b_stage_bytes = b_bytes;
+                    const double kfrac = (double)a.cin_p / (n_chunks * ck);
+                    const double nfrac = (double)a.cout_p / ((double)n_tiles * n_pad);
+                    best.useful_frac = cand.useful_frac * kfrac * nfrac;
+                }
+            };
+            // ---- per-tap candidates: every (tap, chunk) TMA-loads its own 128-pixel boxes
+            if (force_mode != 0) {
+                for (int bw = 128; bw >= 1; bw >>= 1) {
+                    const int bh = 128 / bw;
+                    if (bw * a.sw > 256 || bh * a.sh > 256) continue;
+                    if (is_1x1 && bh != 1) continue;
+                    if (!is_1x1 && bw > 2 * OW && bw > 1) continue;
+                    for (int T = std::min(4, max_t); T >= 1; --T) {
+                        const int a_bytes = T * 128 * ck_bytes;
+                        const int stages = fit_stages(0, a_bytes + b_bytes, 4);
+                        if (stages < 3) continue;
+                        EdeUmmaCfg cand{};
+                        cand.a_mode = 1; cand.bh = bh; cand.bw = bw; cand.pitch = bw; cand.box_rows = bh;
+                        cand.m_tiles = T; cand.a_stages = cand.b_stages = stages; cand.a_stage_bytes = a_bytes;
+                        cand.tiles_w = ceil_div(OW, bw * T); cand.tiles_h = ceil_div(OH, bh);
+                        cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * T * 128);
+                        consider(cand, (double)n_chunks * taps_w / a.w_passes * a_bytes * (a.w_passes),
+                                 (double)n_chunks * taps_w * n_pad * ck_bytes);
+                    }
+                }
             }
-        }
-    }
-    // ---- resident candidates (stride 1, k x k with k > 1)
-    if (a.sh == 1 && a.kh * a.kw >= 9 && force_mode != 1 && !is_1x1) {
-        EdeUmmaCfg rb{};
-        double rb_score = -1;
-        for (int div = 1; div <= 8; ++div) {
-            const int bw = ceil_div(OW, div);
-            const int P = bw + a.kw - 1;
-            if (P > 256) continue;
-            for (int bh = 1; bh <= 64 && bh <= OH + 8; ++bh) {
-                const int box_rows = bh + a.kh - 1;
-                if (box_rows > 256) break;
-                const int m_need = (bh - 1) * P + bw;
-                const int T = ceil_div(m_need, 128);
-                if (T > max_t) break;
-                const int rows_alloc = std::max(box_rows * P, T * 128 + (a.kh - 1) * P + a.kw - 1);
-                const int a_bytes = round_up(rows_alloc * ck_bytes, 1024);
-                const int b_stages = fit_stages(2 * a_bytes, b_bytes, 4);
-                if (b_stages < 3) continue;
-                const int tiles_w = ceil_div(OW, bw), tiles_h = ceil_div(OH, bh);
-                const double frac = (double)OH * OW / ((double)tiles_w * tiles_h * T * 128);
-                const double amp = (double)box_rows * P / ((double)bh * bw);   // halo read amplification
-                const double score = frac - 0.01 * amp - 0.02 * (pow2_cols(T * n_pad) > 256) -
-                                     0.02 * (2 * a_bytes + 4 * b_bytes > SMEM_2CTA);
-                if (score > rb_score) {
-                    rb_score = score;
-                    rb.a_mode = 0; rb.bh = bh; rb.bw = bw; rb.pitch = P; rb.box_rows = box_rows;
-                    rb.m_tiles = T; rb.a_stages = 2; rb.b_stages = b_stages; rb.a_stage_bytes = a_bytes;
-                    rb.tiles_w = tiles_w; rb.tiles_h = tiles_h; rb.useful_frac = frac;
+            // ---- resident candidates (stride 1, k x k with k > 1): halo tile loaded once per chunk
+            if (a.sh == 1 && a.kh * a.kw >= 9 && force_mode != 1 && !is_1x1) {
+                for (int div = 1; div <= 8; ++div) {
+                    const int bw = ceil_div(OW, div);
+                    const int P = bw + a.kw - 1;
+                    if (P > 256) continue;
+                    for (int bh = 1; bh <= 64 && bh <= OH + 8; ++bh) {
+                        const int box_rows = bh + a.kh - 1;
+                        if (box_rows > 256) break;
+                        const int m_need = (bh - 1) * P + bw;
+                        const int T = ceil_div(m_need, 128);
+                        if (T > max_t) break;
+                        const int rows_alloc = std::max(box_rows * P, T * 128 + (a.kh - 1) * P + a.kw - 1);
+                        const int a_bytes = round_up(rows_alloc * ck_bytes, 1024);
+                        const int b_stages = fit_stages(2 * a_bytes, b_bytes, 4);
+                        if (b_stages < 3) continue;
+                        EdeUmmaCfg cand{};
+                        cand.a_mode = 0; cand.bh = bh; cand.bw = bw; cand.pitch = P; cand.box_rows = box_rows;
+                        cand.m_tiles = T; cand.a_stages = 2; cand.b_stages = b_stages; cand.a_stage_bytes = a_bytes;
+                        cand.tiles_w = ceil_div(OW, bw); cand.tiles_h = ceil_div(OH, bh);
+                        cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * T * 128);
+                        consider(cand, (double)n_chunks * box_rows * P * ck_bytes,
+                                 (double)n_chunks * taps_w * n_pad * ck_bytes);
+                    }
                 }
             }
         }
-        if (rb_score > 0 && (force_mode == 0 || rb.useful_frac >= 0.8 * best.useful_frac)) best = rb;
     }
     if (best.m_tiles == 0) return;
     c = best;
     c.eligible = 1;
-    c.ck = ck; c.swizzle = ck_bytes;
-    c.n_pad = n_pad; c.n_tiles = n_tiles;
-    c.b_stage_bytes = b_bytes;
-    c.tmem_cols = pow2_cols(c.m_tiles * n_pad);
+    c.tmem_cols = pow2_cols(2 * c.m_tiles * c.n_pad);
     c.smem_bytes = c.a_stages * c.a_stage_bytes + c.b_stages * c.b_stage_bytes + SMEM_EXTRA;
     c.flat = is_1x1;
-    // real MACs / issued MACs also counts channel padding
-    const double kfrac = (double)a.cin_p / round_up(a.cin_p, ck);
-    const double nfrac = (double)a.cout_p / ((double)n_tiles * n_pad);
-    c.useful_frac *= kfrac * nfrac;
 }
 
 int conv_direct_launch(const EdeConv& a, cudaStream_t st);
+
+static unsigned long long* g_prof_last = nullptr;
+static size_t g_prof_ctas = 0;
 
 static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t st) {
     EncodeTiledFn enc = get_encode_fn();
@@ -544,6 +712,10 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     p.oh = c.flat ? 1 : a.oh;
     p.ow = c.flat ? a.n * a.h * a.w : a.ow;
     p.tiles_w = c.tiles_w; p.tiles_h = c.tiles_h;
+    p.n_img = c.flat ? 1 : a.n;
+    p.n_tiles = c.n_tiles;
+    p.total_tiles = c.tiles_w * c.tiles_h * p.n_img * c.n_tiles;
+    p.acc_cols = c.m_tiles * c.n_pad;
     p.a_mode = c.a_mode; p.ck_bytes = c.ck * 2; p.n_chunks = ceil_div(a.cin_p, c.ck);
     p.w_passes = a.w_passes;
     p.kh = a.kh; p.kw = a.kw; p.sh = a.sh; p.sw = a.sw; p.pt = a.pt; p.pl = a.pl;
@@ -554,26 +726,41 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     p.layout_type = c.swizzle == 128 ? 2 : c.swizzle == 64 ? 4 : 6;
     p.sbo_bytes = 8 * c.ck * 2;
     p.tmem_cols = c.tmem_cols;
-    p.base_off_mode = env_int("EDE_UMMA_BASE_OFFSET", 0);
     p.flat = c.flat;
     p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(c.n_pad >> 3) << 17) | ((128u >> 4) << 24);
     p.y = a.y; p.res = a.res; p.scale = a.scale; p.shift = a.shift;
     p.y_cs = a.y_cs; p.y_co = a.y_co; p.res_cs = a.res_cs; p.res_co = a.res_co;
     p.cout_p = a.cout_p; p.act = a.act; p.act_c_end = a.act_c_end; p.y_dtype = a.y_dtype;
 
+    static int sm_count[64] = {};
     static bool smem_attr_set[64] = {};
     int dev = 0;
     (void)cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && !smem_attr_set[dev]) {
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (!smem_attr_set[dev]) {
         int rc = check_cuda(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  227 * 1024),
                             "cudaFuncSetAttribute(conv_umma_kernel)");
         if (rc) return rc;
+        rc = check_cuda(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev),
+                        "cudaDeviceGetAttribute(MultiProcessorCount)");
+        if (rc) return rc;
         smem_attr_set[dev] = true;
     }
-    const int n_img = c.flat ? 1 : a.n;
-    dim3 grid((unsigned)(c.tiles_w * c.tiles_h * n_img), (unsigned)c.n_tiles);
-    conv_umma_kernel<<<grid, 192, c.smem_bytes, st>>>(p);
+    // persistent grid: one CTA per SM (the dynamic smem request is kept above half an SM so that two CTAs
+    // can never share one SM and fight over the 512 TMEM columns)
+    const int n_cta = std::min(p.total_tiles, std::max(1, sm_count[dev]));
+    static unsigned long long* prof_buf = nullptr;
+    static const int prof_on = env_int("EDE_UMMA_PROF", 0);
+    if (prof_on) {
+        if (!prof_buf && cudaMalloc(&prof_buf, (size_t)4096 * 8 * sizeof(unsigned long long)) != cudaSuccess)
+            prof_buf = nullptr;
+        p.prof = (prof_buf && n_cta <= 4096) ? prof_buf : nullptr;
+        g_prof_last = p.prof;
+        g_prof_ctas = p.prof ? (size_t)n_cta : 0;
+    }
+    const int smem = std::max(c.smem_bytes, 120 * 1024);
+    conv_umma_kernel<<<n_cta, NUM_THREADS, smem, st>>>(p);
     EDE_LAUNCH_CHECK("conv_umma_kernel");
     return EDE_OK;
 }
@@ -581,6 +768,17 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
 }  // namespace ede
 
 extern "C" {
+
+/* debug hook (EDE_UMMA_PROF=1): copies the per-CTA globaltimer stamps of the LAST tcgen05 conv launch
+ * (8 per CTA: entry, mainloop start, first operands landed, last MMA issued, accumulator ready,
+ * epilogue done, CTA done, unused) to `host`; returns the number of CTAs (0 when profiling is off). */
+int64_t ede_debug_umma_prof(unsigned long long* host, int64_t max_ctas) {
+    if (!ede::g_prof_last || !host) return 0;
+    cudaDeviceSynchronize();
+    size_t n = ede::g_prof_ctas < (size_t)max_ctas ? ede::g_prof_ctas : (size_t)max_ctas;
+    cudaMemcpy(host, ede::g_prof_last, n * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    return (int64_t)n;
+}
 
 int ede_umma_available(void) { return ede::get_encode_fn() != nullptr ? 1 : 0; }
 

@@ -145,7 +145,9 @@ class Graph:
         self.keep: List[torch.Tensor] = []        # prepacked weights etc.
         self.inputs: List[tuple] = []             # (op index, shape)
         self.outputs: List[tuple] = []            # (op index, shape)
-        self.flops = 0.0                          # algorithmic 2*MAC of the dense/depthwise convs
+        self.flops = 0.0                          # algorithmic 2*MAC of the reference graph's convs
+        self.exec_flops = 0.0                     # 2*MAC actually issued to the tensor cores / CUDA cores
+        self.count_ref_flops = True
         self.tags: List[str] = []
 
     # ------------------------------------------------------------------ helpers
@@ -259,7 +261,9 @@ class Graph:
                 act_end = len(out_lanes)
             else:
                 seen_plain = True
-            self.flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
+            if self.count_ref_flops:
+                self.flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
+            self.exec_flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
         full = torch.cat(fulls, 0)
         cout_p = len(out_lanes)
         if out is None:
@@ -323,6 +327,7 @@ class Graph:
                          oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype)
         self._add(A.OP_DWCONV, st, [("x", x.buf), ("y", out.buf)], tag)
         self.flops += 2.0 * x.n * oh * ow * c * k * k
+        self.exec_flops += 2.0 * x.n * oh * ow * c * k * k
         return out, pool_t
 
     def se_gate(self, x: View, pool_t, reduce_conv, expand_conv, tag="se") -> View:
@@ -350,6 +355,45 @@ class Graph:
         st = A.EdeSeScale(x=None, y=None, gate=self._ptr(gate), n=x.n, hw=x.h * x.w, c_p=x.c_p,
                           x_cs=x.buf.cs, x_co=x.co, y_cs=out.buf.cs, y_co=out.co, dtype=x.dtype)
         self._add(A.OP_SE_SCALE, st, [("x", x.buf), ("y", out.buf)], tag + ".scale")
+        return out
+
+    def upconv(self, x: View, size, parts, pad, act, tag="upconv") -> View:
+        """conv_kxk(bilinear_ac(x, size)) of several weight sets sharing the input, evaluated on the LOW-resolution
+        grid (csrc/upconv.cu): a 1x1 tensor-core GEMM z = [W_tap]_tap x into fp32, then the tap gather.
+        `parts` as in conv(); stride 1, symmetric `pad`."""
+        oh, ow = int(size[0]), int(size[1])
+        k = int(parts[0][0].shape[2])
+        cin = x.c
+        rows, scales, shifts, out_lanes, act_end = [], [], [], [], 0
+        for (wt, bn, bias, activated) in parts:
+            co = int(wt.shape[0])
+            co_p = P.ceil8(co)
+            w = torch.zeros(co_p, cin, k, k, dtype=torch.float32, device=wt.device)
+            w[:co] = wt.detach().float()
+            rows.append(w)
+            sc, sf = P.fold_bn(co, _bn_dict(bn), bias, wt.device)
+            omap = P.identity_map(co)
+            scales.append(P.place_lanes(sc, omap))
+            shifts.append(P.place_lanes(sf, omap))
+            base = sum(1 for v in out_lanes if v >= 0)
+            out_lanes += [base + v if v >= 0 else -1 for v in omap]
+            if activated and act != A.ACT_NONE:
+                act_end = len(out_lanes)
+            self.flops += 2.0 * x.n * oh * ow * co * cin * k * k          # what the reference graph executes
+        cgrp = len(out_lanes)
+        wz = torch.cat(rows, 0)                                            # [cgrp][cin][k][k]
+        wz = wz.permute(2, 3, 0, 1).reshape(k * k * cgrp, cin, 1, 1)       # lanes [(ty*k+tx)*cgrp + c]
+        prev = self.count_ref_flops
+        self.count_ref_flops = False
+        z = self.conv(x, [(wz, None, None, False)], 1, (0, 0, 0, 0), A.ACT_NONE, out_dtype=A.F32, tag=tag + ".z_gemm")
+        self.count_ref_flops = prev
+        out = View(self.new_buf(x.n, oh, ow, cgrp, self.decoder_dtype if self.act_dtype != A.F32 else A.F32), 0, out_lanes)
+        scale, shift = self._dev(torch.cat(scales)), self._dev(torch.cat(shifts))
+        st = A.EdeUpConv(z=None, y=None, scale=self._ptr(scale), shift=self._ptr(shift), n=x.n, h=x.h, w=x.w,
+                         z_cs=z.buf.cs, z_co=z.co, oh=oh, ow=ow, cgrp=cgrp, y_cs=out.buf.cs, y_co=out.co,
+                         y_dtype=out.dtype, kh=k, kw=k, pt=pad[0], pl=pad[1], act=act, act_c_end=act_end)
+        self._add(A.OP_UPCONV, st, [("z", z.buf), ("y", out.buf)], tag + ".taps")
+        self.exec_flops += 2.0 * x.n * oh * ow * cgrp * k * k * 4
         return out
 
     def resize(self, x: View, size, out: Optional[View] = None, out_dtype=None, force=False, tag="resize") -> View:
@@ -413,6 +457,7 @@ class Plan:
         self.arena_bytes = arena_bytes
         self.keep = g.keep
         self.flops = g.flops
+        self.exec_flops = g.exec_flops
         self.tags = [t for (_, _, _, t) in g.ops]
         self.kinds = [k for (k, _, _, _) in g.ops]
         self.inputs, self.outputs = g.inputs, g.outputs

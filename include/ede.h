@@ -123,6 +123,19 @@ int ede_resize_bilinear_ac(const EdeResize* a, void* stream);
 int ede_resize_planes_f32(const float* x, float* y, int64_t planes, int32_t h, int32_t w, int32_t oh, int32_t ow,
                           void* stream);
 
+/* Tap gather of "conv(k x k, stride 1) of a bilinearly upsampled map" evaluated on the low-resolution grid.
+ * replaces: F.interpolate(x, size, 'bilinear', align_corners=True) followed by conv1/conv2 of _UpProjection
+ *   (ReSIDE/models/modules.py:34-37) where the projection is narrow (MFF, modules.py:259-263).
+ * z: fp32 NHWC [n,h,w], lanes [(ty*kw+tx)*cgrp + c] = (W_tap x)[c], produced by ede_conv2d as a 1x1 GEMM.
+ *   y[n,oy,ox,c] = act_c( scale[c] * sum_taps inside(oy+ty-pt, ox+tx-pl) * bilinear_ac(z[.., tap, c])(oy+ty-pt, ox+tx-pl)
+ *                         + shift[c] ),  act applied to lanes c < act_c_end. */
+typedef struct EdeUpConv {
+    const float* z; void* y; const float* scale; const float* shift;
+    int32_t n, h, w, z_cs, z_co, oh, ow, cgrp, y_cs, y_co, y_dtype;
+    int32_t kh, kw, pt, pl, act, act_c_end;
+} EdeUpConv;
+int ede_upconv_taps(const EdeUpConv* a, void* stream);
+
 /* 3x3 stride-2 pad-1 max pooling. replaces: nn.MaxPool2d(3,2,1), ReSIDE/models/resnet.py:107. */
 typedef struct EdeMaxPool {
     const void* x; void* y;
@@ -169,18 +182,24 @@ int ede_edge_counts(const float* pred, const float* label, int32_t n, int32_t h,
 
 /* Run a pre-built operator list ("forward plan") back to back on one stream. */
 enum { EDE_OP_CONV = 1, EDE_OP_DWCONV = 2, EDE_OP_SE_FC = 3, EDE_OP_SE_SCALE = 4, EDE_OP_RESIZE = 5,
-       EDE_OP_MAXPOOL = 6, EDE_OP_ELTWISE = 7, EDE_OP_TO_NHWC = 8, EDE_OP_TO_NCHW = 9, EDE_OP_ZERO = 10 };
+       EDE_OP_MAXPOOL = 6, EDE_OP_ELTWISE = 7, EDE_OP_TO_NHWC = 8, EDE_OP_TO_NCHW = 9, EDE_OP_ZERO = 10,
+       EDE_OP_UPCONV = 11 };
 typedef struct EdeOp {
     int32_t kind; int32_t _pad;
     union {
         EdeConv conv; EdeDwConv dw; EdeSeFc se_fc; EdeSeScale se_scale; EdeResize resize;
-        EdeMaxPool maxpool; EdeEltwise eltwise; EdeLayout layout;
+        EdeMaxPool maxpool; EdeEltwise eltwise; EdeLayout layout; EdeUpConv upconv;
         struct { void* p; int64_t bytes; } zero;
     } u;
 } EdeOp;
 int ede_plan_run(const EdeOp* ops, int32_t n_ops, void* stream);
 /* number of kernel launches issued by this library on the calling thread since the last reset */
 int64_t ede_launch_count(int32_t reset);
+
+/* debug hook (env EDE_UMMA_PROF=1): per-CTA globaltimer stamps of the last tcgen05 conv launch, 8 x u64 per
+ * CTA [entry, mainloop start, first operands landed, last MMA issued, accumulator ready, epilogue done,
+ * CTA done, -]; synchronises the device; returns the CTA count (0 when profiling is off). */
+int64_t ede_debug_umma_prof(unsigned long long* host, int64_t max_ctas);
 
 int ede_version(void);
 const char* ede_last_error(void);

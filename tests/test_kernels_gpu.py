@@ -1,0 +1,356 @@
+"""-m gpu: every C-ABI operator against the same op in plain PyTorch fp32 on seeded inputs
+(called through ctypes exactly as the engine does), plus Sobel/loss/metrics against the golden vectors."""
+import ctypes as C
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from efficientdepthestimation_b200 import _cabi as A
+from efficientdepthestimation_b200 import loss as L
+from efficientdepthestimation_b200 import prepack as P
+from oracle import reside_cpu as rc
+from oracle import weights as W
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+TDT = {A.F32: torch.float32, A.BF16: torch.bfloat16}
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def nhwc(x_nchw, c_p, dtype):
+    n, c, h, w = x_nchw.shape
+    out = torch.zeros(n, h, w, c_p, dtype=torch.float32, device=x_nchw.device)
+    out[..., :c] = x_nchw.permute(0, 2, 3, 1)
+    return out.to(TDT[dtype]).contiguous()
+
+
+def split_store(x_nhwc_f32):
+    """fp32 NHWC -> EDE_BF16X2 bytes: per 8 lanes [8 hi][8 lo] (as a bf16 tensor with 2x lanes)."""
+    n, h, w, c = x_nhwc_f32.shape
+    hi = x_nhwc_f32.to(torch.bfloat16)
+    lo = (x_nhwc_f32 - hi.float()).to(torch.bfloat16)
+    return torch.stack((hi.view(n, h, w, c // 8, 8), lo.view(n, h, w, c // 8, 8)), dim=4).reshape(n, h, w, 2 * c).contiguous()
+
+
+def split_load(t_bf16, c):
+    n, h, w, _ = t_bf16.shape
+    v = t_bf16.float().view(n, h, w, c // 8, 2, 8)
+    return (v[..., 0, :] + v[..., 1, :]).reshape(n, h, w, c)
+
+
+CONV_CASES = [
+    # name, n, h, w, cin, cout, k, s, (pt, pl, pb, pr), res, act
+    ("1x1", 3, 15, 19, 256, 136, 1, 1, (0, 0, 0, 0), True, A.ACT_RELU),
+    ("1x1_swish_ragged", 2, 57, 76, 24, 144, 1, 1, (0, 0, 0, 0), False, A.ACT_SWISH),
+    ("3x3", 2, 29, 38, 64, 64, 3, 1, (1, 1, 1, 1), False, A.ACT_RELU),
+    ("5x5_ragged_c", 1, 114, 152, 74, 74, 5, 1, (2, 2, 2, 2), False, A.ACT_RELU),
+    ("5x5_wide_k", 1, 33, 41, 320, 32, 5, 1, (2, 2, 2, 2), False, A.ACT_RELU),
+    ("5x5_head_bias", 2, 60, 80, 128, 1, 5, 1, (2, 2, 2, 2), False, A.ACT_NONE),
+    ("3x3s2", 2, 57, 76, 128, 128, 3, 2, (1, 1, 1, 1), False, A.ACT_RELU),
+    ("1x1s2", 2, 57, 76, 256, 512, 1, 2, (0, 0, 0, 0), False, A.ACT_NONE),
+    ("7x7s2_stem", 2, 228, 304, 3, 64, 7, 2, (3, 3, 3, 3), False, A.ACT_RELU),
+    ("3x3s2_asym_stem", 2, 228, 304, 3, 32, 3, 2, (0, 0, 1, 1), False, A.ACT_NONE),
+    ("5x5s2_asym", 1, 57, 76, 144, 40, 5, 2, (1, 1, 2, 2), False, A.ACT_NONE),
+]
+
+
+@pytest.mark.parametrize("mode", ["bf16", "split", "fp32"])
+@pytest.mark.parametrize("case", CONV_CASES, ids=[c[0] for c in CONV_CASES])
+def test_conv2d(cuda, lib, case, mode):
+    name, n, h, w, cin, cout, k, s, (pt, pl, pb, pr), use_res, act = case
+    g = torch.Generator().manual_seed(len(name) * 131 + k)
+    oh, ow = (h + pt + pb - k) // s + 1, (w + pl + pr - k) // s + 1
+    cin_p, cout_p = P.ceil8(cin), P.ceil8(cout)
+    x = torch.randn(n, cin, h, w, generator=g).to(cuda)
+    wt = (torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).to(cuda)
+    scale = (0.5 + torch.rand(cout, generator=g)).to(cuda)
+    shift = (0.2 * torch.randn(cout, generator=g)).to(cuda)
+    res = torch.randn(n, cout, oh, ow, generator=g).to(cuda) if use_res else None
+    io_dt = {"bf16": A.BF16, "split": A.BF16X2, "fp32": A.F32}[mode]
+    if mode == "split":
+        xin = split_store(nhwc(x, cin_p, A.F32))
+        in_lanes = [v for g8 in range(0, cin_p, 8) for v in P.identity_map(cin, cin_p)[g8:g8 + 8] * 2]
+        mul, x_dt, passes = 2, A.BF16, 2
+        x_eff = split_load(xin, cin_p)[..., :cin].permute(0, 3, 1, 2)
+        w_eff = wt
+        resin = split_store(nhwc(res, cout_p, A.F32)) if use_res else None
+        res_eff = split_load(resin, cout_p)[..., :cout].permute(0, 3, 1, 2) if use_res else None
+        y = torch.full((n, oh, ow, 2 * cout_p), float("nan"), device=cuda, dtype=torch.bfloat16)
+    else:
+        xin = nhwc(x, cin_p, io_dt)
+        in_lanes, mul, x_dt, passes = P.identity_map(cin, cin_p), 1, io_dt, 1
+        x_eff = xin.float()[..., :cin].permute(0, 3, 1, 2)
+        w_eff = wt.to(torch.bfloat16).float() if mode == "bf16" else wt
+        resin = nhwc(res, cout_p, io_dt) if use_res else None
+        res_eff = resin.float()[..., :cout].permute(0, 3, 1, 2) if use_res else None
+        y = torch.full((n, oh, ow, cout_p), float("nan"), device=cuda, dtype=TDT[io_dt])
+    full = P.scatter_weight(wt, in_lanes, P.identity_map(cout, cout_p))
+    w_direct = P.pack_direct(full)
+    w_umma, co16, ci64 = P.pack_umma(full, passes)
+    sc = P.place_lanes(scale, P.identity_map(cout, cout_p))
+    sf = P.place_lanes(shift, P.identity_map(cout, cout_p))
+    a = A.EdeConv(x=xin.data_ptr(), y=y.data_ptr(), res=resin.data_ptr() if use_res else None, scale=sc.data_ptr(),
+                  shift=sf.data_ptr(), w_umma=w_umma.data_ptr(), w_direct=w_direct.data_ptr(), n=n, h=h, w=w,
+                  cin_p=cin_p * mul, x_cs=cin_p * mul, x_co=0, oh=oh, ow=ow, cout_p=cout_p, y_cs=cout_p, y_co=0,
+                  res_cs=cout_p, res_co=0, kh=k, kw=k, sh=s, sw=s, pt=pt, pl=pl, act=act, act_c_end=cout_p,
+                  x_dtype=x_dt, y_dtype=io_dt, x_layout=A.NHWC, relu_in=0, w_umma_cout_p=co16, w_umma_cin_p=ci64,
+                  force_direct=1 if mode == "fp32" else 0, w_passes=passes)
+    cfg = A.umma_config(a)
+    assert bool(cfg.eligible) == (mode != "fp32")
+    A.check(lib.ede_conv2d(C.byref(a), stream()), "ede_conv2d")
+    torch.cuda.synchronize()
+    ref = F.conv2d(F.pad(x_eff.double(), (pl, pr, pt, pb)), w_eff.double(), None, s)
+    ref = ref * scale.double().view(1, -1, 1, 1) + shift.double().view(1, -1, 1, 1)
+    if use_res:
+        ref = ref + res_eff.double()
+    ref = {A.ACT_RELU: F.relu, A.ACT_SWISH: lambda t: t * torch.sigmoid(t), A.ACT_NONE: lambda t: t}[act](ref)
+    ref = ref.permute(0, 2, 3, 1).float()
+    got = split_load(y, cout_p) if mode == "split" else y.float()
+    assert not torch.isnan(got).any()
+    assert float(got[..., cout:].abs().sum()) == 0.0                      # pad lanes stay zero
+    err = (got[..., :cout] - ref).abs()
+    # bf16 output rounding is 2^-9 relative; split keeps 16 bits; fp32 path is exact up to summation order.
+    # The tensor core adds into its fp32 accumulator with truncation: a bias of ~2^-24 per K=16 step that
+    # grows linearly with the K extent (measured: 2e-4 at K = 2 x 8000) -- budgeted explicitly here.
+    rel = {"bf16": 4e-3, "split": 6e-5 + 2.0e-8 * cin * k * k, "fp32": 2e-5}[mode]
+    tol = rel * ref.abs() + rel
+    assert bool((err <= tol).all()), (name, mode, float(err.max()), float((err / (ref.abs() + 1)).max()))
+
+
+@pytest.mark.parametrize("dt", [A.F32, A.BF16, A.BF16X2])
+@pytest.mark.parametrize("k,s,pad", [(3, 1, (1, 1, 1, 1)), (3, 2, (0, 0, 1, 1)), (5, 2, (1, 1, 2, 2)), (5, 1, (2, 2, 2, 2))])
+def test_dwconv_se(cuda, lib, dt, k, s, pad):
+    """Depthwise + BN + swish + SE squeeze, SE FCs and the gate multiply (App. A.3 of SURVEY.md)."""
+    g = torch.Generator().manual_seed(k * 10 + s)
+    n, c, h, w, csq = 3, 44, 29, 38, 6
+    c_p = P.ceil8(c)
+    pt, pl, pb, pr = pad
+    oh, ow = (h + pt + pb - k) // s + 1, (w + pl + pr - k) // s + 1
+    x = torch.randn(n, c, h, w, generator=g).to(cuda)
+    wt = (torch.randn(c, 1, k, k, generator=g) / k).to(cuda)
+    scale, shift = (0.5 + torch.rand(c, generator=g)).to(cuda), (0.2 * torch.randn(c, generator=g)).to(cuda)
+    w1, b1 = torch.randn(csq, c, generator=g).to(cuda) / c ** 0.5, 0.1 * torch.randn(csq, generator=g).to(cuda)
+    w2, b2 = torch.randn(c, csq, generator=g).to(cuda) / csq ** 0.5, 0.1 * torch.randn(c, generator=g).to(cuda)
+    if dt == A.BF16X2:
+        xin = split_store(nhwc(x, c_p, A.F32))
+        x_eff = split_load(xin, c_p)[..., :c].permute(0, 3, 1, 2)
+        y = torch.zeros(n, oh, ow, 2 * c_p, device=cuda, dtype=torch.bfloat16)
+        z = torch.zeros_like(y)
+    else:
+        xin = nhwc(x, c_p, dt)
+        x_eff = xin.float()[..., :c].permute(0, 3, 1, 2)
+        y = torch.zeros(n, oh, ow, c_p, device=cuda, dtype=TDT[dt])
+        z = torch.zeros_like(y)
+    lanes = P.identity_map(c, c_p)
+    wk = torch.zeros(k * k, c_p, device=cuda)
+    wk[:, :c] = wt.reshape(c, k * k).t()
+    sc, sf = P.place_lanes(scale, lanes), P.place_lanes(shift, lanes)
+    pool = torch.zeros(n, c_p, device=cuda)
+    a = A.EdeDwConv(x=xin.data_ptr(), y=y.data_ptr(), w=wk.data_ptr(), scale=sc.data_ptr(), shift=sf.data_ptr(),
+                    pool_sum=pool.data_ptr(), n=n, h=h, w_=w, c_p=c_p, x_cs=c_p, x_co=0, oh=oh, ow=ow, y_cs=c_p,
+                    y_co=0, k=k, s=s, pt=pt, pl=pl, act=A.ACT_SWISH, dtype=dt)
+    A.check(lib.ede_dwconv2d(C.byref(a), stream()), "ede_dwconv2d")
+    w1p = torch.zeros(csq, c_p, device=cuda); w1p[:, :c] = w1
+    w2p = torch.zeros(c_p, csq, device=cuda); w2p[:c] = w2
+    b2p = torch.zeros(c_p, device=cuda); b2p[:c] = b2
+    gate = torch.zeros(n, c_p, device=cuda)
+    f = A.EdeSeFc(pool_sum=pool.data_ptr(), w1=w1p.data_ptr(), b1=b1.data_ptr(), w2=w2p.data_ptr(), b2=b2p.data_ptr(),
+                  gate=gate.data_ptr(), n=n, c=c, c_p=c_p, csq=csq, inv_hw=1.0 / (oh * ow))
+    A.check(lib.ede_se_fc(C.byref(f), stream()), "ede_se_fc")
+    sa = A.EdeSeScale(x=y.data_ptr(), y=z.data_ptr(), gate=gate.data_ptr(), n=n, hw=oh * ow, c_p=c_p, x_cs=c_p, x_co=0,
+                      y_cs=c_p, y_co=0, dtype=dt)
+    A.check(lib.ede_se_scale(C.byref(sa), stream()), "ede_se_scale")
+    torch.cuda.synchronize()
+    ref = F.conv2d(F.pad(x_eff, (pl, pr, pt, pb)), wt, None, s, 0, 1, c)
+    ref = ref * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)
+    ref = ref * torch.sigmoid(ref)
+    rel = {A.F32: 1e-5, A.BF16: 4e-3, A.BF16X2: 4e-5}[dt]
+    got = (split_load(y, c_p) if dt == A.BF16X2 else y.float())[..., :c].permute(0, 3, 1, 2)
+    assert bool(((got - ref).abs() <= rel * ref.abs() + rel).all())
+    ref_pool = got.sum(dim=(2, 3))                       # the squeeze sees the stored (rounded) activations
+    assert torch.allclose(pool[:, :c], ref_pool, rtol=1e-4, atol=1e-3)
+    sref = ref_pool / (oh * ow)
+    hid = sref @ w1.t() + b1
+    hid = hid * torch.sigmoid(hid)
+    gref = torch.sigmoid(hid @ w2.t() + b2)
+    assert torch.allclose(gate[:, :c], gref, rtol=1e-4, atol=1e-5) and float(gate[:, c:].abs().sum()) == 0
+    zgot = (split_load(z, c_p) if dt == A.BF16X2 else z.float())[..., :c].permute(0, 3, 1, 2)
+    zref = got * gref.view(n, c, 1, 1)
+    assert bool(((zgot - zref).abs() <= rel * zref.abs() + rel).all())
+
+
+@pytest.mark.parametrize("dts", [(A.F32, A.F32), (A.BF16, A.BF16), (A.BF16X2, A.BF16)])
+@pytest.mark.parametrize("hw,ohw", [((8, 10), (114, 152)), ((57, 76), (114, 152)), ((15, 19), (29, 38)),
+                                    ((114, 152), (228, 304)), ((7, 9), (7, 9)), ((1, 1), (5, 3))])
+def test_resize_bilinear_align_corners(cuda, lib, dts, hw, ohw):
+    """Non-integer ratios (8->114, 10->152) as in modules.py:34; written into a channel SLICE of a wider buffer."""
+    xd, yd = dts
+    g = torch.Generator().manual_seed(hw[0] * 7 + ohw[0])
+    n, c, (h, w), (oh, ow) = 2, 20, hw, ohw
+    c_p, cs_out, co_out = 24, 48, 16
+    x = torch.randn(n, c, h, w, generator=g).to(cuda)
+    if xd == A.BF16X2:
+        xin = split_store(nhwc(x, c_p, A.F32))
+        x_eff = split_load(xin, c_p)[..., :c].permute(0, 3, 1, 2)
+    else:
+        xin = nhwc(x, c_p, xd)
+        x_eff = xin.float()[..., :c].permute(0, 3, 1, 2)
+    y = torch.full((n, oh, ow, cs_out), 7.0, device=cuda, dtype=TDT[yd])
+    a = A.EdeResize(x=xin.data_ptr(), y=y.data_ptr(), n=n, h=h, w=w, c_p=c_p, x_cs=c_p, x_co=0, oh=oh, ow=ow,
+                    y_cs=cs_out, y_co=co_out, x_dtype=xd, y_dtype=yd)
+    A.check(lib.ede_resize_bilinear_ac(C.byref(a), stream()), "ede_resize_bilinear_ac")
+    torch.cuda.synchronize()
+    ref = F.interpolate(x_eff, size=(oh, ow), mode="bilinear", align_corners=True).permute(0, 2, 3, 1)
+    got = y.float()
+    assert float((got[..., :co_out] - 7.0).abs().max()) == 0 and float((got[..., co_out + c_p:] - 7.0).abs().max()) == 0
+    tol = 1e-5 if yd == A.F32 else 4e-3
+    assert bool(((got[..., co_out:co_out + c] - ref).abs() <= tol * ref.abs() + tol).all())
+    # fp32 planes variant (post-forward depth resize, train.py:273-276)
+    if xd == A.F32:
+        yp = torch.empty(n, c, oh, ow, device=cuda)
+        A.check(lib.ede_resize_planes_f32(x.contiguous().data_ptr(), yp.data_ptr(), n * c, h, w, oh, ow, stream()))
+        torch.cuda.synchronize()
+        assert torch.allclose(yp, F.interpolate(x, size=(oh, ow), mode="bilinear", align_corners=True), atol=1e-5)
+
+
+@pytest.mark.parametrize("dt", [A.F32, A.BF16, A.BF16X2])
+@pytest.mark.parametrize("hw", [(114, 152), (113, 151), (5, 4)])
+def test_maxpool_and_eltwise_and_layout(cuda, lib, dt, hw):
+    g = torch.Generator().manual_seed(hw[0])
+    n, c, (h, w) = 2, 12, hw
+    c_p = 16
+    x = torch.randn(n, c, h, w, generator=g).to(cuda)
+    # nchw -> nhwc (network input), checked by reading back through nhwc -> nchw
+    elems = 2 * c_p if dt == A.BF16X2 else c_p
+    store = torch.bfloat16 if dt != A.F32 else torch.float32
+    xin = torch.full((n, h, w, elems), float("nan"), device=cuda, dtype=store)
+    la = A.EdeLayout(src=x.data_ptr(), dst=xin.data_ptr(), n=n, c=c, h=h, w=w, c_p=c_p, cs=c_p, co=0, dtype=dt)
+    A.check(lib.ede_nchw_to_nhwc(C.byref(la), stream()), "ede_nchw_to_nhwc")
+    back = torch.empty(n, c, h, w, device=cuda)
+    lb = A.EdeLayout(src=xin.data_ptr(), dst=back.data_ptr(), n=n, c=c, h=h, w=w, c_p=c_p, cs=c_p, co=0, dtype=dt)
+    A.check(lib.ede_nhwc_to_nchw(C.byref(lb), stream()), "ede_nhwc_to_nchw")
+    torch.cuda.synchronize()
+    assert not torch.isnan(xin.float()).any()
+    tol = {A.F32: 0.0, A.BF16: 4e-3, A.BF16X2: 2e-5}[dt]
+    assert bool(((back - x).abs() <= tol * x.abs() + 1e-30).all())
+    x_eff = back
+    # 3x3 s2 p1 max pooling (resnet.py:107)
+    oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = torch.zeros(n, oh, ow, elems, device=cuda, dtype=store)
+    m = A.EdeMaxPool(x=xin.data_ptr(), y=y.data_ptr(), n=n, h=h, w=w, c_p=c_p, x_cs=c_p, x_co=0, oh=oh, ow=ow,
+                     y_cs=c_p, y_co=0, dtype=dt)
+    A.check(lib.ede_maxpool3x3s2(C.byref(m), stream()), "ede_maxpool3x3s2")
+    # eltwise: relu(x) + x
+    z = torch.zeros(n, h, w, elems, device=cuda, dtype=store)
+    e = A.EdeEltwise(x=xin.data_ptr(), x2=xin.data_ptr(), y=z.data_ptr(), n_pix=n * h * w, c_p=c_p, x_cs=c_p, x_co=0,
+                     x2_cs=c_p, x2_co=0, y_cs=c_p, y_co=0, act=A.ACT_RELU, dtype=dt)
+    A.check(lib.ede_eltwise(C.byref(e), stream()), "ede_eltwise")
+    torch.cuda.synchronize()
+    dec = (lambda t: split_load(t, c_p)) if dt == A.BF16X2 else (lambda t: t.float())
+    got = dec(y)[..., :c].permute(0, 3, 1, 2)
+    assert torch.equal(got, F.max_pool2d(x_eff, 3, 2, 1))                 # max of stored values is exact
+    gz = dec(z)[..., :c].permute(0, 3, 1, 2)
+    rz = F.relu(x_eff) + x_eff
+    assert bool(((gz - rz).abs() <= max(tol, 1e-7) * rz.abs() + 1e-30).all())
+
+
+@pytest.mark.parametrize("holes", [False, True])
+def test_sobel_loss_metrics_against_reference_golden(cuda, lib, holes):
+    """ede_sobel / ede_sobel_loss_metrics vs the fixtures produced by ReSIDE/sobel.py, train.py:216-236 and
+    util.MetricsTracker of the REAL reference (tests/golden/make_golden.py)."""
+    g = torch.load(os.path.join(GOLDEN, f"sobel_loss_metrics{'_holes' if holes else ''}.pt"))
+    out, lab = g["output"].to(cuda), g["labels"].to(cuda)
+    from efficientdepthestimation_b200.ReSIDE.sobel import Sobel
+    from efficientdepthestimation_b200.ReSIDE.util import MetricsTracker
+    s = Sobel().to(cuda)(out)
+    assert list(Sobel().state_dict().keys()) == ["edge_conv.weight"]
+    assert torch.allclose(s.cpu(), g["sobel"], atol=1e-5)
+    sums = L.loss_metric_sums(out, lab).cpu().tolist()
+    assert sums[12] == out.numel() and sums[13] == out.shape[0]
+    if not holes:
+        mine = L.loss_from_sums(sums)
+        for k, v in g["loss"].items():
+            assert abs(mine[k] - v) <= 2e-6 * max(1.0, abs(v)), (k, mine[k], v)
+        assert abs(float(L.sobel_loss(out, lab)) - g["loss"]["loss"]) <= 1e-5
+    mt = MetricsTracker()
+    mt.update(outputs=out, labels=lab)
+    for k, v in g["metrics"].items():
+        mine = mt.to_dict()[k]
+        assert (mine != mine and v != v) or abs(mine - v) <= 1e-5 * max(1.0, abs(v)), (k, mine, v)
+
+
+def test_loss_full_size_properties(cuda, lib):
+    """BASELINE config-4 size (32 x 228x304): linearity of the sums over the batch axis (two half batches
+    accumulate to the whole), exactness of the counters, and agreement with the oracle on one image."""
+    n, h, w = 32, 228, 304
+    out = (0.5 + 9.5 * torch.rand(n, 1, h, w, generator=torch.Generator().manual_seed(3))).to(cuda)
+    lab = W.make_labels(n, h, w, seed=1, holes=True).to(cuda)
+    whole = L.loss_metric_sums(out, lab)
+    acc = L.loss_metric_sums(out[:16], lab[:16])
+    acc = L.loss_metric_sums(out[16:], lab[16:], out=acc)
+    torch.cuda.synchronize()
+    a, b = whole.cpu(), acc.cpu()
+    assert torch.equal(a[8:14], b[8:14]) and float(a[12]) == n * h * w and float(a[13]) == n
+    assert float(a[11]) == float((~torch.isnan(lab)).sum())
+    assert torch.allclose(a[[6, 7]], b[[6, 7]], rtol=1e-12)          # masked sums stay finite
+    assert bool(torch.isnan(a[:6]).all()) and bool(torch.isnan(b[:6]).all())   # NaN labels poison the unmasked sums (util.py:54-57)
+    lab0 = W.make_labels(n, h, w, seed=1).to(cuda)
+    c0 = L.loss_metric_sums(out, lab0).cpu()
+    c1 = L.loss_metric_sums(out[:16], lab0[:16])
+    c1 = L.loss_metric_sums(out[16:], lab0[16:], out=c1).cpu()
+    assert torch.allclose(c0[:8], c1[:8], rtol=1e-12) and torch.equal(c0[8:14], c1[8:14])
+    one = L.loss_metric_sums(out[:1], lab[:1]).cpu().tolist()
+    ref = rc.metric_sums(out[:1].cpu(), lab[:1].cpu())
+    assert abs(one[6] - ref["rel"]) <= 1e-5 * ref["rel"] and one[8] == ref["d1"] and one[10] == ref["d3"]
+    ec = L.edge_counts(out[:2], lab[:2], 0.25).cpu().tolist()
+    po, pl_ = rc.edge_magnitude(out[:2].cpu()) > 0.25, rc.edge_magnitude(torch.nan_to_num(lab[:2].cpu(), nan=float("nan"))) > 0.25
+    assert ec[0] == float(po.sum()) and ec[1] == float(pl_.sum()) and ec[2] == float((po & pl_).sum())
+
+
+@pytest.mark.parametrize("hw,ohw,cin,couts,split", [((8, 10), (114, 152), 72, (16, 16), True),
+                                                    ((57, 76), (114, 152), 24, (16, 16), False),
+                                                    ((14, 19), (57, 76), 40, (10, 10), True),
+                                                    ((3, 4), (9, 7), 16, (8,), False)])
+def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, split):
+    """engine.Graph.upconv (1x1 GEMM on the low-res grid + ede_upconv_taps) == relu/bn(conv5x5(bilinear_ac(x)))
+    as _UpProjection computes it (modules.py:34-37): every tap, border and non-integer ratio (8->114)."""
+    from efficientdepthestimation_b200 import engine
+    g = torch.Generator().manual_seed(hw[0] * 31 + cin)
+    n, (h, w), (oh, ow) = 2, hw, ohw
+    x = torch.randn(n, cin, h, w, generator=g)
+    parts, refs = [], []
+    for i, co in enumerate(couts):
+        wt = torch.randn(co, cin, 5, 5, generator=g) / (cin * 25) ** 0.5
+        bn = torch.nn.BatchNorm2d(co)
+        bn.weight.data = 0.5 + torch.rand(co, generator=g)
+        bn.bias.data = 0.2 * torch.randn(co, generator=g)
+        bn.running_mean = 0.1 * torch.randn(co, generator=g)
+        bn.running_var = 0.5 + torch.rand(co, generator=g)
+        parts.append((wt.to(cuda), bn.to(cuda).eval(), None, i == 0))
+        refs.append((wt, bn.eval(), i == 0))
+    gr = engine.Graph(cuda, "bf16")
+    if not split:
+        gr.encoder_dtype = A.BF16
+    xin = gr.input_nchw(x.shape)
+    out = gr.upconv(xin, (oh, ow), parts, (2, 2, 2, 2), A.ACT_RELU)
+    gr.output_nchw(out)
+    plan = gr.finalize()
+    (y,) = plan.run([x.to(cuda)])
+    torch.cuda.synchronize()
+    x_eff = x if split else x.to(torch.bfloat16).float()
+    up = F.interpolate(x_eff.double(), size=(oh, ow), mode="bilinear", align_corners=True)
+    outs = []
+    with torch.no_grad():
+        for wt, bn, activated in refs:
+            r = bn.double()(F.conv2d(up, wt.to(torch.bfloat16).double(), None, 1, 2))
+            outs.append(F.relu(r) if activated else r)
+    ref = torch.cat(outs, 1).float()
+    got = y.cpu()
+    assert got.shape == ref.shape
+    # output stored as bf16 (2^-9) on top of bf16 weights (identical on both sides)
+    assert bool(((got - ref).abs() <= 5e-3 * ref.abs() + 5e-3).all()), float((got - ref).abs().max())
