@@ -33,7 +33,7 @@ class EdeConv(Structure):
 class EdeUmmaCfg(Structure):
     _fields_ = _ints("eligible", "a_mode", "ck", "swizzle", "bh", "bw", "pitch", "box_rows", "m_tiles", "n_pad",
                      "n_tiles", "a_stages", "b_stages", "a_stage_bytes", "b_stage_bytes", "smem_bytes",
-                     "tmem_cols", "tiles_w", "tiles_h", "flat") + [("useful_frac", c_double)]
+                     "tmem_cols", "tiles_w", "tiles_h", "flat") + [("useful_frac", c_double)] + _ints("swap", "reserved")
 
 
 class EdeDwConv(Structure):

@@ -120,7 +120,7 @@ struct alignas(64) UmmaParams {
     int oh, ow, tiles_w, tiles_h, n_img, n_tiles, total_tiles;
     int a_mode, ck_bytes, n_chunks, kh, kw, sh, sw, pt, pl, w_passes;
     int bw, bh, pitch, box_bytes;
-    int m_tiles, n_pad, acc_cols;
+    int m_tiles, n_pad, acc_cols, swap;      // swap: weights are the M-side operand, 256 pixels on N
     int a_stages, b_stages, a_stage_bytes, b_stage_bytes, b_tx_bytes;
     int layout_type, sbo_bytes, tmem_cols, flat;
     uint32_t idesc;
@@ -227,6 +227,60 @@ __device__ __forceinline__ void epilogue_store16(const UmmaParams& p, long long 
     if (c + 8 < p.cout_p) epilogue_store8<TY>(p, pix, c + 8, c_local + 8, acc + 8, s_scale, s_shift);
 }
 
+// Epilogue of the operand-swapped mode: TMEM lane = output channel, column = pixel of the 256-row window.
+// Each warp transposes 16 pixels x its 32 channels through a private 2 KB fp32 smem tile so that the second phase
+// (residual, activation, packing) works on 8-channel vectors of one pixel and stores 16/32 bytes per thread.
+template <typename TY>
+__device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const TileCoord& t, uint32_t t_base, int quarter,
+                                                 int lane, float* s_tr, float sc, float sf) {
+    const int wrap = p.a_mode == 0 ? p.pitch : p.bw;
+    const int pl = lane >> 2, g = lane & 3;                  // phase-2 role: pixel pl (+8), channel group g
+    const int c = quarter * 32 + g * 8;
+    const bool c_ok = c < p.cout_p;
+    const bool act_on = c < p.act_c_end && p.act != EDE_ACT_NONE;
+    for (int c0 = 0; c0 < 256; c0 += 16) {
+        uint32_t acc[16];
+        tc_ld16(t_base + (uint32_t)c0, acc);
+        tc_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) s_tr[j * 32 + lane] = fmaf(__uint_as_float(acc[j]), sc, sf);
+        __syncwarp();
+#pragma unroll
+        for (int it = 0; it < 2; ++it) {
+            const int pj = pl + it * 8;
+            const int f = c0 + pj;                           // window row -> output pixel
+            int fr, fc, owb;
+            if (p.a_mode == 0) { fr = f / wrap; fc = f - fr * wrap; owb = t.ow0; }
+            else { const int m = f >> 7, rr = f & 127; fr = rr / wrap; fc = rr - fr * wrap; owb = t.ow0 + m * p.bw; }
+            const int oh = t.oh0 + fr, ow = owb + fc;
+            if (c_ok && fc < p.bw && fr < p.bh && oh < p.oh && ow < p.ow) {
+                const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
+                float v[8];
+                const float4 lo = *reinterpret_cast<const float4*>(s_tr + pj * 32 + g * 8);
+                const float4 hi = *reinterpret_cast<const float4*>(s_tr + pj * 32 + g * 8 + 4);
+                v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w; v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
+                if (p.res) {
+                    float r[8];
+                    load8<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co + c, r);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) v[j] += r[j];
+                }
+                if (act_on) {
+                    if (p.act == EDE_ACT_RELU) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], p.act);
+                    }
+                }
+                store8<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co + c, v);
+            }
+        }
+        __syncwarp();
+    }
+}
+
 // Persistent, warp-specialised implicit-GEMM convolution.  One CTA per SM walks the tile list
 // (tile = n-tile x image x output patch) with a static stride; TMEM holds TWO accumulator stages so the
 // epilogue of tile i overlaps the MMAs of tile i+1; the operand rings run on across tile boundaries.
@@ -318,7 +372,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (warp-uniform loop state, one elected lane issues) ==============
-        const int a_mode = p.a_mode, m_tiles = p.m_tiles, n_pad = p.n_pad, n_chunks = p.n_chunks;
+        const int a_mode = p.a_mode, m_tiles = p.m_tiles, n_pad = p.n_pad, n_chunks = p.n_chunks, swap = p.swap;
         const int a_stages = p.a_stages, b_stages = p.b_stages, kw = p.kw, pitch = p.pitch;
         const uint32_t ck16 = (uint32_t)p.ck_bytes >> 4;            // (bytes >> 4) units of the address field
         const uint32_t a_stage16 = (uint32_t)p.a_stage_bytes >> 4, b_stage16 = (uint32_t)p.b_stage_bytes >> 4;
@@ -357,13 +411,20 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                     const uint32_t a0 = a_base16 + (uint32_t)a_st * a_stage16 + shift16;
                     const uint32_t b0 = b_base16 + (uint32_t)b_st * b_stage16;
                     if (elect_one()) {
-                        uint32_t am = a0, dm = d_base;
-                        for (int m = 0; m < m_tiles; ++m) {
-                            tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, accum);
+                        if (swap) {
+                            // D[cout lanes][256 pixel columns] += W[128 x 16] . X[256 x 16]^T
+                            tc_mma_bf16_w(d_base, b0, a0, desc_hi, idesc, accum);
                             for (int k = 1; k < ksteps; ++k)
-                                tc_mma_bf16_w(dm, am + 2u * k, b0 + 2u * k, desc_hi, idesc, 1u);
-                            am += m_step16;
-                            dm += (uint32_t)n_pad;
+                                tc_mma_bf16_w(d_base, b0 + 2u * k, a0 + 2u * k, desc_hi, idesc, 1u);
+                        } else {
+                            uint32_t am = a0, dm = d_base;
+                            for (int m = 0; m < m_tiles; ++m) {
+                                tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, accum);
+                                for (int k = 1; k < ksteps; ++k)
+                                    tc_mma_bf16_w(dm, am + 2u * k, b0 + 2u * k, desc_hi, idesc, 1u);
+                                am += m_step16;
+                                dm += (uint32_t)n_pad;
+                            }
                         }
                         tc_commit(b_empty(b_st));
                         if (a_mode != 0) tc_commit(a_empty(a_st));
@@ -412,43 +473,54 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
             if (p.prof) w_full += clock64() - c0;
             tc_fence_after();
             const uint32_t t_base = tmem_addr + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_st * p.acc_cols);
-            for (int m = 0; m < p.m_tiles; ++m) {
-                // which output pixel does accumulator row (m, r) hold?
-                int oh, ow;
-                bool valid;
-                if (p.a_mode == 0) {
-                    const int f = m * 128 + r;
-                    const int fr = f / p.pitch, fc = f - fr * p.pitch;
-                    oh = t.oh0 + fr; ow = t.ow0 + fc;
-                    valid = fc < p.bw && fr < p.bh;
-                } else {
-                    const int fr = r / p.bw, fc = r - fr * p.bw;
-                    oh = t.oh0 + fr; ow = t.ow0 + m * p.bw + fc;
-                    valid = true;
+            if (p.swap) {
+                // accumulator lane = output channel, column = pixel of the 256-row window
+                if (quarter * 32 < p.cout_p) {
+                    float* const s_tr = s_shift + 256 + (warp - 2) * 512;      // this warp's [16 px][32 ch] fp32 tile
+                    const float sc = r < p.cout_p ? __ldg(p.scale + r) : 0.f, sf = r < p.cout_p ? __ldg(p.shift + r) : 0.f;
+                    if (p.y_dtype == EDE_BF16) epilogue_swapped<__nv_bfloat16>(p, t, t_base, quarter, lane, s_tr, sc, sf);
+                    else if (p.y_dtype == EDE_BF16X2) epilogue_swapped<bf16x2_t>(p, t, t_base, quarter, lane, s_tr, sc, sf);
+                    else epilogue_swapped<float>(p, t, t_base, quarter, lane, s_tr, sc, sf);
                 }
-                valid = valid && oh < p.oh && ow < p.ow;
-                const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
-                const uint32_t t_row = t_base + (uint32_t)(m * p.n_pad);
-                uint32_t acc0[16], acc1[16];
-                tc_ld16(t_row, acc0);
-                for (int c0l = 0; c0l < p.n_pad; c0l += 32) {
-                    tc_ld_wait();
-                    const bool more1 = c0l + 16 < p.n_pad;
-                    if (more1) tc_ld16(t_row + (uint32_t)(c0l + 16), acc1);        // in flight while acc0 is stored
-                    if (valid) {
-                        const int c = t.ntile * p.n_pad + c0l;
-                        if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, c, c0l, acc0, s_scale, s_shift);
-                        else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, c, c0l, acc0, s_scale, s_shift);
-                        else epilogue_store16<float>(p, pix, c, c0l, acc0, s_scale, s_shift);
+            } else {
+                for (int m = 0; m < p.m_tiles; ++m) {
+                    // which output pixel does accumulator row (m, r) hold?
+                    int oh, ow;
+                    bool valid;
+                    if (p.a_mode == 0) {
+                        const int f = m * 128 + r;
+                        const int fr = f / p.pitch, fc = f - fr * p.pitch;
+                        oh = t.oh0 + fr; ow = t.ow0 + fc;
+                        valid = fc < p.bw && fr < p.bh;
+                    } else {
+                        const int fr = r / p.bw, fc = r - fr * p.bw;
+                        oh = t.oh0 + fr; ow = t.ow0 + m * p.bw + fc;
+                        valid = true;
                     }
-                    if (!more1) break;
-                    tc_ld_wait();
-                    if (c0l + 32 < p.n_pad) tc_ld16(t_row + (uint32_t)(c0l + 32), acc0);
-                    if (valid) {
-                        const int c = t.ntile * p.n_pad + c0l + 16;
-                        if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
-                        else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
-                        else epilogue_store16<float>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
+                    valid = valid && oh < p.oh && ow < p.ow;
+                    const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
+                    const uint32_t t_row = t_base + (uint32_t)(m * p.n_pad);
+                    uint32_t acc0[16], acc1[16];
+                    tc_ld16(t_row, acc0);
+                    for (int c0l = 0; c0l < p.n_pad; c0l += 32) {
+                        tc_ld_wait();
+                        const bool more1 = c0l + 16 < p.n_pad;
+                        if (more1) tc_ld16(t_row + (uint32_t)(c0l + 16), acc1);        // in flight while acc0 is stored
+                        if (valid) {
+                            const int c = t.ntile * p.n_pad + c0l;
+                            if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, c, c0l, acc0, s_scale, s_shift);
+                            else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, c, c0l, acc0, s_scale, s_shift);
+                            else epilogue_store16<float>(p, pix, c, c0l, acc0, s_scale, s_shift);
+                        }
+                        if (!more1) break;
+                        tc_ld_wait();
+                        if (c0l + 32 < p.n_pad) tc_ld16(t_row + (uint32_t)(c0l + 32), acc0);
+                        if (valid) {
+                            const int c = t.ntile * p.n_pad + c0l + 16;
+                            if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
+                            else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
+                            else epilogue_store16<float>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
+                        }
                     }
                 }
             }
@@ -500,8 +572,8 @@ static int env_int(const char* name, int dflt) {
     return (s && *s) ? atoi(s) : dflt;
 }
 
-constexpr int SMEM_BUDGET = 200 * 1024;      // operand rings; barriers + alignment slack on top
-constexpr int SMEM_EXTRA = 1024 + 512 + 2048;   // alignment slack + barriers + scale/shift slice
+constexpr int SMEM_BUDGET = 196 * 1024;      // operand rings; barriers + alignment slack on top
+constexpr int SMEM_EXTRA = 1024 + 512 + 2048 + 8192;   // + 4 x 2 KB transpose tiles (swapped epilogue)   // alignment slack + barriers + scale/shift slice
 
 static bool umma_eligible(const EdeConv& a) {
     if (a.force_direct || a.w_umma == nullptr) return false;
@@ -643,10 +715,83 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
             }
         }
     }
+    // ---- operand-swapped candidates (Cout <= 128): weights on the M side (128 rows, zero padded by TMA),
+    // 256 pixels on N.  One MMA then costs max(128, base) cycles for 256 pixels instead of 97 for 128.
+    const int force_swap = env_int("EDE_UMMA_SWAP", -1);
+    if (n16 <= 128 && force_swap != 0) {
+        if (force_swap == 1) best_time = 1e300;
+        for (int ci = 0; ci < 3; ++ci) {
+            const int ck = cks[ci];
+            if (force_ck && force_ck != ck) continue;
+            const int ck_bytes = ck * 2, n_chunks = ceil_div(a.cin_p, ck), ksteps = ck / 16;
+            const int b_bytes = round_up(128 * ck_bytes, 1024);
+            const double base = ck_bytes == 128 ? 97.0 : ck_bytes == 64 ? 154.0 : 214.0;
+            const double t_mma = std::max(base, 128.0);
+            auto consider = [&](const EdeUmmaCfg& cand, double a_bytes_tile) {
+                const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img;
+                const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
+                const double mma = (double)n_chunks * taps_w * ksteps * t_mma;
+                const double mem = (a_bytes_tile + (double)n_chunks * taps_w * 128 * ck_bytes) / L2_BYTES_PER_CLK_PER_SM;
+                const double epi = 16.0 * 220.0 + 600.0;
+                const double per_stage = mma / std::max(1, n_chunks * taps_w);
+                const double lat = std::max(0.0, 1500.0 - cand.b_stages * per_stage) * 0.15 * n_chunks * taps_w /
+                                   std::max(1, cand.b_stages);
+                const double t = rounds * (std::max(std::max(mma, mem), epi) + lat + 300.0) + 4000.0;
+                if (t < best_time) {
+                    best_time = t;
+                    best = cand;
+                    best.swap = 1;
+                    best.ck = ck; best.swizzle = ck_bytes; best.n_pad = 128; best.n_tiles = 1;
+                    best.b_stage_bytes = b_bytes;
+                    best.useful_frac = cand.useful_frac * ((double)a.cin_p / (n_chunks * ck)) * (a.cout_p / 128.0);
+                }
+            };
+            if (force_mode != 0) {
+                for (int bw = 128; bw >= 1; bw >>= 1) {
+                    const int bh = 128 / bw;
+                    if (bw * a.sw > 256 || bh * a.sh > 256) continue;
+                    if (is_1x1 && bh != 1) continue;
+                    if (!is_1x1 && bw > 2 * OW && bw > 1) continue;
+                    const int a_bytes = 2 * 128 * ck_bytes;
+                    const int stages = fit_stages(0, a_bytes + b_bytes, 4);
+                    if (stages < 3) continue;
+                    EdeUmmaCfg cand{};
+                    cand.a_mode = 1; cand.bh = bh; cand.bw = bw; cand.pitch = bw; cand.box_rows = bh;
+                    cand.m_tiles = 2; cand.a_stages = cand.b_stages = stages; cand.a_stage_bytes = a_bytes;
+                    cand.tiles_w = ceil_div(OW, bw * 2); cand.tiles_h = ceil_div(OH, bh);
+                    cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * 256);
+                    consider(cand, (double)n_chunks * taps_w * a_bytes);
+                }
+            }
+            if (a.sh == 1 && a.kh * a.kw >= 9 && force_mode != 1 && !is_1x1) {
+                for (int div = 1; div <= 8; ++div) {
+                    const int bw = ceil_div(OW, div);
+                    const int P = bw + a.kw - 1;
+                    if (P > 256) continue;
+                    for (int bh = 1; bh <= 64 && bh <= OH + 8; ++bh) {
+                        const int box_rows = bh + a.kh - 1;
+                        if (box_rows > 256) break;
+                        const int m_need = (bh - 1) * P + bw;
+                        if (m_need > 256) break;
+                        const int rows_alloc = std::max(box_rows * P, 256 + (a.kh - 1) * P + a.kw - 1);
+                        const int a_bytes = round_up(rows_alloc * ck_bytes, 1024);
+                        const int b_stages = fit_stages(2 * a_bytes, b_bytes, 4);
+                        if (b_stages < 3) continue;
+                        EdeUmmaCfg cand{};
+                        cand.a_mode = 0; cand.bh = bh; cand.bw = bw; cand.pitch = P; cand.box_rows = box_rows;
+                        cand.m_tiles = 2; cand.a_stages = 2; cand.b_stages = b_stages; cand.a_stage_bytes = a_bytes;
+                        cand.tiles_w = ceil_div(OW, bw); cand.tiles_h = ceil_div(OH, bh);
+                        cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * 256);
+                        consider(cand, (double)n_chunks * box_rows * P * ck_bytes);
+                    }
+                }
+            }
+        }
+    }
     if (best.m_tiles == 0) return;
     c = best;
     c.eligible = 1;
-    c.tmem_cols = pow2_cols(2 * c.m_tiles * c.n_pad);
+    c.tmem_cols = c.swap ? 512 : pow2_cols(2 * c.m_tiles * c.n_pad);
     c.smem_bytes = c.a_stages * c.a_stage_bytes + c.b_stages * c.b_stage_bytes + SMEM_EXTRA;
     c.flat = is_1x1;
 }
@@ -699,7 +844,7 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
         cuuint64_t dims[3] = {(cuuint64_t)a.w_umma_cin_p, (cuuint64_t)a.w_umma_cout_p,
                               (cuuint64_t)(a.kh * a.kw * a.w_passes)};
         cuuint64_t strides[2] = {(cuuint64_t)a.w_umma_cin_p * 2, (cuuint64_t)a.w_umma_cin_p * 2 * a.w_umma_cout_p};
-        cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)c.n_pad, 1};
+        cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)(c.swap ? 128 : c.n_pad), 1};
         cuuint32_t es[3] = {1, 1, 1};
         CUresult r = enc(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, (void*)a.w_umma, dims, strides, box, es,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -715,19 +860,20 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     p.n_img = c.flat ? 1 : a.n;
     p.n_tiles = c.n_tiles;
     p.total_tiles = c.tiles_w * c.tiles_h * p.n_img * c.n_tiles;
-    p.acc_cols = c.m_tiles * c.n_pad;
+    p.acc_cols = c.swap ? 256 : c.m_tiles * c.n_pad;
     p.a_mode = c.a_mode; p.ck_bytes = c.ck * 2; p.n_chunks = ceil_div(a.cin_p, c.ck);
     p.w_passes = a.w_passes;
     p.kh = a.kh; p.kw = a.kw; p.sh = a.sh; p.sw = a.sw; p.pt = a.pt; p.pl = a.pl;
     p.bw = c.bw; p.bh = c.bh; p.pitch = c.pitch; p.box_bytes = c.pitch * c.box_rows * c.ck * 2;
     p.m_tiles = c.m_tiles; p.n_pad = c.n_pad;
     p.a_stages = c.a_stages; p.b_stages = c.b_stages;
-    p.a_stage_bytes = c.a_stage_bytes; p.b_stage_bytes = c.b_stage_bytes; p.b_tx_bytes = c.n_pad * c.ck * 2;
+    p.a_stage_bytes = c.a_stage_bytes; p.b_stage_bytes = c.b_stage_bytes; p.b_tx_bytes = (c.swap ? 128 : c.n_pad) * c.ck * 2;
     p.layout_type = c.swizzle == 128 ? 2 : c.swizzle == 64 ? 4 : 6;
     p.sbo_bytes = 8 * c.ck * 2;
     p.tmem_cols = c.tmem_cols;
     p.flat = c.flat;
-    p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(c.n_pad >> 3) << 17) | ((128u >> 4) << 24);
+    p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)((c.swap ? 256 : c.n_pad) >> 3) << 17) | ((128u >> 4) << 24);
+    p.swap = c.swap;
     p.y = a.y; p.res = a.res; p.scale = a.scale; p.shift = a.shift;
     p.y_cs = a.y_cs; p.y_co = a.y_co; p.res_cs = a.res_cs; p.res_co = a.res_co;
     p.cout_p = a.cout_p; p.act = a.act; p.act_c_end = a.act_c_end; p.y_dtype = a.y_dtype;

@@ -78,6 +78,8 @@ typedef struct EdeUmmaCfg {
     int32_t a_stages, b_stages, a_stage_bytes, b_stage_bytes, smem_bytes, tmem_cols;
     int32_t tiles_w, tiles_h, flat;              /* flat: N*H*W folded into one pixel axis (1x1)  */
     double useful_frac;     /* real MACs / issued tensor MACs                                    */
+    int32_t swap;           /* 1: weights are the M-side operand (Cout <= 128), 256 pixels on N  */
+    int32_t reserved;
 } EdeUmmaCfg;
 int ede_conv2d_umma_config(const EdeConv* a, EdeUmmaCfg* out);
 

@@ -314,7 +314,7 @@ def test_loss_full_size_properties(cuda, lib):
 
 @pytest.mark.parametrize("hw,ohw,cin,couts,split", [((8, 10), (114, 152), 72, (16, 16), True),
                                                     ((57, 76), (114, 152), 24, (16, 16), False),
-                                                    ((14, 19), (57, 76), 40, (10, 10), True),
+                                                    ((14, 19), (57, 76), 40, (8, 8), True),
                                                     ((3, 4), (9, 7), 16, (8,), False)])
 def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, split):
     """engine.Graph.upconv (1x1 GEMM on the low-res grid + ede_upconv_taps) == relu/bn(conv5x5(bilinear_ac(x)))
@@ -331,8 +331,9 @@ def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, 
         bn.bias.data = 0.2 * torch.randn(co, generator=g)
         bn.running_mean = 0.1 * torch.randn(co, generator=g)
         bn.running_var = 0.5 + torch.rand(co, generator=g)
+        import copy
+        refs.append((wt, copy.deepcopy(bn).double().eval(), i == 0))
         parts.append((wt.to(cuda), bn.to(cuda).eval(), None, i == 0))
-        refs.append((wt, bn.eval(), i == 0))
     gr = engine.Graph(cuda, "bf16")
     if not split:
         gr.encoder_dtype = A.BF16
@@ -347,7 +348,7 @@ def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, 
     outs = []
     with torch.no_grad():
         for wt, bn, activated in refs:
-            r = bn.double()(F.conv2d(up, wt.to(torch.bfloat16).double(), None, 1, 2))
+            r = bn(F.conv2d(up, wt.to(torch.bfloat16).double(), None, 1, 2))
             outs.append(F.relu(r) if activated else r)
     ref = torch.cat(outs, 1).float()
     got = y.cpu()

@@ -28,7 +28,7 @@ def main():
         fl = 2.0 * st.n * st.oh * st.ow * st.cout_p * st.cin_p * st.kh * st.kw
         tot += fl
         if "--all" in sys.argv or fl / n > 2e8:
-            path = ("umma/" + ("resident" if cfg.a_mode == 0 else "per-tap")) if cfg.eligible else "DIRECT"
+            path = ("umma/" + ("resident" if cfg.a_mode == 0 else "per-tap") + ("/swap" if cfg.swap else "")) if cfg.eligible else "DIRECT"
             print(f"  {tag:28s} {st.kh}x{st.kw}s{st.sh} {st.cin_p:5d}->{st.cout_p:5d} @{st.oh}x{st.ow} {path:14s} "
                   f"ck={cfg.ck} tile={cfg.bh}x{cfg.bw} mt={cfg.m_tiles} n_pad={cfg.n_pad}x{cfg.n_tiles} "
                   f"st={cfg.a_stages}/{cfg.b_stages} smem={cfg.smem_bytes // 1024}K frac={cfg.useful_frac:.2f} "

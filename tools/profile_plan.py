@@ -74,7 +74,7 @@ def main():
             fl = 2.0 * s.n * s.oh * s.ow * s.cout_p * s.cin_p * s.kh * s.kw * max(1, s.w_passes)
             cfg = A.umma_config(s)
             desc = (f"{s.kh}x{s.kw}s{s.sh} {s.cin_p}->{s.cout_p}@{s.oh}x{s.ow} p{s.w_passes} "
-                    f"{'res' if cfg.a_mode == 0 else 'tap'} ck{cfg.ck} {cfg.bh}x{cfg.bw} mt{cfg.m_tiles} n{cfg.n_pad}x{cfg.n_tiles}"
+                    f"{'res' if cfg.a_mode == 0 else 'tap'}{'/swap' if cfg.swap else ''} ck{cfg.ck} {cfg.bh}x{cfg.bw} mt{cfg.m_tiles} n{cfg.n_pad}x{cfg.n_tiles}"
                     if cfg.eligible else f"{s.kh}x{s.kw} DIRECT {s.cin_p}->{s.cout_p}")
         by = op_bytes(kind, s)
         rows.append(dict(i=i, tag=plan.tags[i], kind=A.OP_FIELD[kind], ms=ms, tflops=fl / ms / 1e9 if fl else 0.0,
