@@ -2,6 +2,8 @@
 //
 // Every thread owns one 8-channel vector (16 B of bf16 / 32 B of fp32) of one pixel, with the
 // channel-group index fastest across a warp so that global accesses are fully coalesced.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace ede {
@@ -69,6 +71,9 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const EdeDwConv a) {
         for (int i = threadIdx.x; i < a.c_p; i += blockDim.x) atomicAdd(a.pool_sum + (long long)n * a.c_p + i, pool_s[i]);
     }
 }
+
+
+int dwconv_tma_launch(const EdeDwConv& a, cudaStream_t st);      // dwconv.cu
 
 // ------------------------------------------------------------------ squeeze-excite FCs
 __global__ void __launch_bounds__(256) se_fc_kernel(const EdeSeFc a) {
@@ -273,6 +278,11 @@ int ede_dwconv2d(const EdeDwConv* a, void* stream) {
     EDE_REQUIRE(a && a->x && a->y && a->w && a->scale && a->shift, "ede_dwconv2d: null argument");
     EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_dwconv2d: channel counts must be multiples of 8");
     EDE_REQUIRE(a->n > 0 && a->oh > 0 && a->ow > 0 && a->k > 0 && a->s > 0, "ede_dwconv2d: bad shape");
+    static const bool generic_only = getenv("EDE_DW_GENERIC") != nullptr;   // debug: force the per-output kernel
+    if (!generic_only && dwconv_tma_launch(*a, (cudaStream_t)stream) == 0) {   // k in {3,5}, s in {1,2}: TMA-staged
+        EDE_LAUNCH_CHECK("dwconv_tma_kernel");
+        return EDE_OK;
+    }
     const long long per_img = (long long)a->oh * a->ow * (a->c_p >> 3);
     long long gx = (per_img + 256 * 4 - 1) / (256 * 4);
     if (gx < 1) gx = 1;

@@ -137,8 +137,8 @@ template <> __device__ __forceinline__ float round_as<bf16x2_t>(float v) {
 __device__ __forceinline__ float apply_act(float v, int act) {
     switch (act) {
         case EDE_ACT_RELU: return fmaxf(v, 0.f);
-        case EDE_ACT_SWISH: return v / (1.f + __expf(-v));
-        case EDE_ACT_SIGMOID: return 1.f / (1.f + __expf(-v));
+        case EDE_ACT_SWISH: return __fdividef(v, 1.f + __expf(-v));
+        case EDE_ACT_SIGMOID: return __fdividef(1.f, 1.f + __expf(-v));
         default: return v;
     }
 }

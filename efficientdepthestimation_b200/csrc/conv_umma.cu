@@ -27,46 +27,11 @@
 #include <algorithm>
 
 #include "common.cuh"
+#include "tma.cuh"
 
 namespace ede {
 
-// ------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t"
-        "}" ::"r"(bar), "r"(parity)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1, int c2,
-                                            int c3) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
-        "[%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
-        "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1, int c2) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
-        "[%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
-        "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
-        : "memory");
-}
+// ------------------------------------------------------------------ tcgen05 PTX wrappers (TMA / mbarrier ones: tma.cuh)
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
@@ -111,14 +76,15 @@ __device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sy
 
 // ------------------------------------------------------------------ kernel parameters
 constexpr int MAX_STAGES = 8;
-constexpr int NUM_THREADS = 192;             // warp 0 TMA, warp 1 MMA, warps 2..5 epilogue
-constexpr int EPI_THREADS = 128;
+constexpr int EPI_WARPS = 8;                 // two warps per TMEM lane quarter, interleaved over 16-column chunks
+constexpr int EPI_THREADS = 32 * EPI_WARPS;
+constexpr int NUM_THREADS = 64 + EPI_THREADS;   // warp 0 TMA, warp 1 MMA, warps 2.. epilogue
 
 struct alignas(64) UmmaParams {
     CUtensorMap tm_a;     // activations: (C, W, H, N) bf16
     CUtensorMap tm_b;     // weights: (Cin_p, Cout_p, taps) bf16
     int oh, ow, tiles_w, tiles_h, n_img, n_tiles, total_tiles;
-    int a_mode, ck_bytes, n_chunks, kh, kw, sh, sw, pt, pl, w_passes;
+    int a_mode, ck_bytes, k_bytes, n_chunks, kh, kw, sh, sw, pt, pl, w_passes;
     int bw, bh, pitch, box_bytes;
     int m_tiles, n_pad, acc_cols, swap;      // swap: weights are the M-side operand, 256 pixels on N
     int a_stages, b_stages, a_stage_bytes, b_stage_bytes, b_tx_bytes;
@@ -138,24 +104,8 @@ __device__ __forceinline__ unsigned long long gtime() {
     return t;
 }
 
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred P;\n\t"
-        "elect.sync _|P, 0xffffffff;\n\t"
-        "selp.b32 %0, 1, 0, P;\n\t"
-        "}"
-        : "=r"(pred));
-    return pred != 0;
-}
-
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void epi_bar_sync() {      // named barrier 1 over the 128 epilogue threads
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+__device__ __forceinline__ void epi_bar_sync() {      // named barrier 1 over the epilogue threads
+    asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
 }
 
 // constant part of a K-major swizzled UMMA shared-memory descriptor (start address field = 0)
@@ -211,10 +161,10 @@ __device__ __forceinline__ void epilogue_store8(const UmmaParams& p, long long p
             for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
         } else if (p.act == EDE_ACT_SWISH) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = v[j] / (1.f + __expf(-v[j]));
+            for (int j = 0; j < 8; ++j) v[j] = __fdividef(v[j], 1.f + __expf(-v[j]));
         } else if (p.act == EDE_ACT_SIGMOID) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = 1.f / (1.f + __expf(-v[j]));
+            for (int j = 0; j < 8; ++j) v[j] = __fdividef(1.f, 1.f + __expf(-v[j]));
         }
     }
     store8<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co + c, v);
@@ -232,13 +182,13 @@ __device__ __forceinline__ void epilogue_store16(const UmmaParams& p, long long 
 // (residual, activation, packing) works on 8-channel vectors of one pixel and stores 16/32 bytes per thread.
 template <typename TY>
 __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const TileCoord& t, uint32_t t_base, int quarter,
-                                                 int lane, float* s_tr, float sc, float sf) {
+                                                 int half, int lane, float* s_tr, float sc, float sf) {
     const int wrap = p.a_mode == 0 ? p.pitch : p.bw;
     const int pl = lane >> 2, g = lane & 3;                  // phase-2 role: pixel pl (+8), channel group g
     const int c = quarter * 32 + g * 8;
     const bool c_ok = c < p.cout_p;
     const bool act_on = c < p.act_c_end && p.act != EDE_ACT_NONE;
-    for (int c0 = 0; c0 < 256; c0 += 16) {
+    for (int c0 = half * 16; c0 < 256; c0 += 16 * (EPI_WARPS / 4)) {
         uint32_t acc[16];
         tc_ld16(t_base + (uint32_t)c0, acc);
         tc_ld_wait();
@@ -313,7 +263,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
             mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1);
         }
         mbar_init(acc_full(0), 1); mbar_init(acc_full(1), 1);
-        mbar_init(acc_empty(0), 4); mbar_init(acc_empty(1), 4);       // one arrival per epilogue warp
+        mbar_init(acc_empty(0), EPI_WARPS); mbar_init(acc_empty(1), EPI_WARPS);   // one arrival per epilogue warp
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -394,6 +344,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
             const uint32_t d_base = tmem_addr + (uint32_t)(acc_st * p.acc_cols);
             uint32_t accum = 0;
             for (int chunk = 0; chunk < n_chunks; ++chunk) {
+                // K steps that hold real channels: the tail of the last chunk is TMA zero fill, never multiplied
+                const int ks = min(ksteps, (p.k_bytes - chunk * p.ck_bytes + 31) >> 5);
                 if (a_mode == 0) {
                     c0 = p.prof ? clock64() : 0;
                     mbar_wait(a_full(a_st), a_ph);
@@ -414,13 +366,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                         if (swap) {
                             // D[cout lanes][256 pixel columns] += W[128 x 16] . X[256 x 16]^T
                             tc_mma_bf16_w(d_base, b0, a0, desc_hi, idesc, accum);
-                            for (int k = 1; k < ksteps; ++k)
+                            for (int k = 1; k < ks; ++k)
                                 tc_mma_bf16_w(d_base, b0 + 2u * k, a0 + 2u * k, desc_hi, idesc, 1u);
                         } else {
                             uint32_t am = a0, dm = d_base;
                             for (int m = 0; m < m_tiles; ++m) {
                                 tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, accum);
-                                for (int k = 1; k < ksteps; ++k)
+                                for (int k = 1; k < ks; ++k)
                                     tc_mma_bf16_w(dm, am + 2u * k, b0 + 2u * k, desc_hi, idesc, 1u);
                                 am += m_step16;
                                 dm += (uint32_t)n_pad;
@@ -452,10 +404,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
             q[1] = t_start; q[2] = gtime(); q[4] = (unsigned long long)w_ops; q[5] = (unsigned long long)w_acc;
         }
     } else {
-        // ===================== epilogue (warps 2..5): TMEM -> BN/residual/activation -> NHWC stores ========
+        // ===================== epilogue (warps 2..): TMEM -> BN/residual/activation -> NHWC stores ========
         const int quarter = warp & 3;                 // TMEM lanes [32q, 32q+32) are visible to warp%4 == q
+        const int half = (warp - 2) >> 2;             // which interleaved set of 16-column chunks this warp drains
         const int r = quarter * 32 + lane;
-        const int et = threadIdx.x - 64;              // 0..127
+        const int et = threadIdx.x - 64;              // 0..EPI_THREADS-1
         int acc_st = 0, acc_ph = 0, n_done = 0;
         long long w_full = 0;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -478,11 +431,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                 if (quarter * 32 < p.cout_p) {
                     float* const s_tr = s_shift + 256 + (warp - 2) * 512;      // this warp's [16 px][32 ch] fp32 tile
                     const float sc = r < p.cout_p ? __ldg(p.scale + r) : 0.f, sf = r < p.cout_p ? __ldg(p.shift + r) : 0.f;
-                    if (p.y_dtype == EDE_BF16) epilogue_swapped<__nv_bfloat16>(p, t, t_base, quarter, lane, s_tr, sc, sf);
-                    else if (p.y_dtype == EDE_BF16X2) epilogue_swapped<bf16x2_t>(p, t, t_base, quarter, lane, s_tr, sc, sf);
-                    else epilogue_swapped<float>(p, t, t_base, quarter, lane, s_tr, sc, sf);
+                    if (p.y_dtype == EDE_BF16) epilogue_swapped<__nv_bfloat16>(p, t, t_base, quarter, half, lane, s_tr, sc, sf);
+                    else if (p.y_dtype == EDE_BF16X2) epilogue_swapped<bf16x2_t>(p, t, t_base, quarter, half, lane, s_tr, sc, sf);
+                    else epilogue_swapped<float>(p, t, t_base, quarter, half, lane, s_tr, sc, sf);
                 }
             } else {
+                const int nch = p.n_pad >> 4;         // 16-column chunks of one accumulator row (n_pad % 16 == 0)
                 for (int m = 0; m < p.m_tiles; ++m) {
                     // which output pixel does accumulator row (m, r) hold?
                     int oh, ow;
@@ -500,26 +454,29 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                     valid = valid && oh < p.oh && ow < p.ow;
                     const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
                     const uint32_t t_row = t_base + (uint32_t)(m * p.n_pad);
+                    const int cbase = t.ntile * p.n_pad;
                     uint32_t acc0[16], acc1[16];
-                    tc_ld16(t_row, acc0);
-                    for (int c0l = 0; c0l < p.n_pad; c0l += 32) {
+                    int ci = half;
+                    if (ci < nch) tc_ld16(t_row + (uint32_t)(ci << 4), acc0);
+                    while (ci < nch) {                // chunk ci in acc0; the next one loads while it is stored
                         tc_ld_wait();
-                        const bool more1 = c0l + 16 < p.n_pad;
-                        if (more1) tc_ld16(t_row + (uint32_t)(c0l + 16), acc1);        // in flight while acc0 is stored
+                        const int cn = ci + EPI_WARPS / 4;
+                        if (cn < nch) tc_ld16(t_row + (uint32_t)(cn << 4), acc1);
                         if (valid) {
-                            const int c = t.ntile * p.n_pad + c0l;
-                            if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, c, c0l, acc0, s_scale, s_shift);
-                            else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, c, c0l, acc0, s_scale, s_shift);
-                            else epilogue_store16<float>(p, pix, c, c0l, acc0, s_scale, s_shift);
+                            const int c0l = ci << 4;
+                            if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, cbase + c0l, c0l, acc0, s_scale, s_shift);
+                            else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, cbase + c0l, c0l, acc0, s_scale, s_shift);
+                            else epilogue_store16<float>(p, pix, cbase + c0l, c0l, acc0, s_scale, s_shift);
                         }
-                        if (!more1) break;
+                        if (cn >= nch) break;
                         tc_ld_wait();
-                        if (c0l + 32 < p.n_pad) tc_ld16(t_row + (uint32_t)(c0l + 32), acc0);
+                        ci = cn + EPI_WARPS / 4;
+                        if (ci < nch) tc_ld16(t_row + (uint32_t)(ci << 4), acc0);
                         if (valid) {
-                            const int c = t.ntile * p.n_pad + c0l + 16;
-                            if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
-                            else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
-                            else epilogue_store16<float>(p, pix, c, c0l + 16, acc1, s_scale, s_shift);
+                            const int c0l = cn << 4;
+                            if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, cbase + c0l, c0l, acc1, s_scale, s_shift);
+                            else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, cbase + c0l, c0l, acc1, s_scale, s_shift);
+                            else epilogue_store16<float>(p, pix, cbase + c0l, c0l, acc1, s_scale, s_shift);
                         }
                     }
                 }
@@ -548,32 +505,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
 }
 
 // ------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-    static EncodeTiledFn fn = nullptr;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-            q == cudaDriverEntryPointSuccess)
-            fn = reinterpret_cast<EncodeTiledFn>(p);
-        (void)cudaGetLastError();
-    }
-    return fn;
-}
-
 static int env_int(const char* name, int dflt) {
     const char* s = getenv(name);
     return (s && *s) ? atoi(s) : dflt;
 }
 
 constexpr int SMEM_BUDGET = 196 * 1024;      // operand rings; barriers + alignment slack on top
-constexpr int SMEM_EXTRA = 1024 + 512 + 2048 + 8192;   // + 4 x 2 KB transpose tiles (swapped epilogue)   // alignment slack + barriers + scale/shift slice
+constexpr int SMEM_EXTRA = 1024 + 512 + 2048 + EPI_WARPS * 2048;   // alignment slack + barriers + scale/shift slice + one 2 KB transpose tile per epilogue warp (swapped epilogue)
 
 static bool umma_eligible(const EdeConv& a) {
     if (a.force_direct || a.w_umma == nullptr) return false;
@@ -629,13 +567,17 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
 
     EdeUmmaCfg best{};
     double best_time = 1e300;
+    // Channel chunk: always the 128-byte swizzle (64 bf16 channels per smem row) unless forced -- narrower
+    // swizzles feed the tensor core at 63 % / 45 % of the rate (measured, profiles/r01_mma_rate.md; the
+    // operand-swapped N = 256 form loses more), and the MMA issuer skips the K steps of the last chunk
+    // that only hold TMA zero fill, so padding K to 64 costs smem but no tensor-core time.
     const int cks[3] = {64, 32, 16};
+    const int ks_total = ceil_div(a.cin_p, 16);           // K = 16 steps that hold real channels
     for (int ci = 0; ci < 3; ++ci) {
         const int ck = cks[ci];
-        if (force_ck && force_ck != ck) continue;
+        if (force_ck ? force_ck != ck : ck != 64) continue;
         const int ck_bytes = ck * 2;
         const int n_chunks = ceil_div(a.cin_p, ck);
-        const int ksteps = ck / 16;
         for (int n_tiles = ceil_div(n16, 256); n_tiles <= ceil_div(n16, 16) && n_tiles <= 64; ++n_tiles) {
             const int n_pad = round_up(ceil_div(n16, n_tiles), 16);
             if (n_pad > 256) continue;
@@ -648,7 +590,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
             auto consider = [&](const EdeUmmaCfg& cand, double a_bytes_tile, double b_bytes_tile) {
                 const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img * n_tiles;
                 const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
-                const double mma = (double)n_chunks * taps_w * cand.m_tiles * ksteps * t_mma;
+                const double mma = (double)taps_w * cand.m_tiles * ks_total * t_mma;
                 const double mem = (a_bytes_tile + b_bytes_tile) / L2_BYTES_PER_CLK_PER_SM;
                 const double epi = cand.m_tiles * 128.0 * n_pad * EPI_CYCLES_PER_ROW_COL * 4.0 + 600.0;
                 // operand ring too shallow to cover the L2 latency (~1500 clk) -> exposed waits
@@ -722,15 +664,15 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
         if (force_swap == 1) best_time = 1e300;
         for (int ci = 0; ci < 3; ++ci) {
             const int ck = cks[ci];
-            if (force_ck && force_ck != ck) continue;
-            const int ck_bytes = ck * 2, n_chunks = ceil_div(a.cin_p, ck), ksteps = ck / 16;
+            if (force_ck ? force_ck != ck : ck != 64) continue;
+            const int ck_bytes = ck * 2, n_chunks = ceil_div(a.cin_p, ck);
             const int b_bytes = round_up(128 * ck_bytes, 1024);
-            const double base = ck_bytes == 128 ? 97.0 : ck_bytes == 64 ? 154.0 : 214.0;
-            const double t_mma = std::max(base, 128.0);
+            // 256 pixel rows on the N side: 128 clk with the 128 B swizzle; ~230 / ~330 observed with 64 B / 32 B
+            const double t_mma = ck_bytes == 128 ? 128.0 : ck_bytes == 64 ? 230.0 : 330.0;
             auto consider = [&](const EdeUmmaCfg& cand, double a_bytes_tile) {
                 const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img;
                 const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
-                const double mma = (double)n_chunks * taps_w * ksteps * t_mma;
+                const double mma = (double)taps_w * ks_total * t_mma;
                 const double mem = (a_bytes_tile + (double)n_chunks * taps_w * 128 * ck_bytes) / L2_BYTES_PER_CLK_PER_SM;
                 const double epi = 16.0 * 220.0 + 600.0;
                 const double per_stage = mma / std::max(1, n_chunks * taps_w);
@@ -841,7 +783,9 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     }
     // ---- weights
     {
-        cuuint64_t dims[3] = {(cuuint64_t)a.w_umma_cin_p, (cuuint64_t)a.w_umma_cout_p,
+        // dim 0 stops at the real K: the zero tail of the last 64-channel chunk is TMA out-of-bounds fill
+        // (no L2 traffic) instead of zeros streamed from the padded weight rows
+        cuuint64_t dims[3] = {(cuuint64_t)std::min(a.cin_p, a.w_umma_cin_p), (cuuint64_t)a.w_umma_cout_p,
                               (cuuint64_t)(a.kh * a.kw * a.w_passes)};
         cuuint64_t strides[2] = {(cuuint64_t)a.w_umma_cin_p * 2, (cuuint64_t)a.w_umma_cin_p * 2 * a.w_umma_cout_p};
         cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)(c.swap ? 128 : c.n_pad), 1};
@@ -861,7 +805,7 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     p.n_tiles = c.n_tiles;
     p.total_tiles = c.tiles_w * c.tiles_h * p.n_img * c.n_tiles;
     p.acc_cols = c.swap ? 256 : c.m_tiles * c.n_pad;
-    p.a_mode = c.a_mode; p.ck_bytes = c.ck * 2; p.n_chunks = ceil_div(a.cin_p, c.ck);
+    p.a_mode = c.a_mode; p.ck_bytes = c.ck * 2; p.k_bytes = a.cin_p * 2; p.n_chunks = ceil_div(a.cin_p, c.ck);
     p.w_passes = a.w_passes;
     p.kh = a.kh; p.kw = a.kw; p.sh = a.sh; p.sw = a.sw; p.pt = a.pt; p.pl = a.pl;
     p.bw = c.bw; p.bh = c.bh; p.pitch = c.pitch; p.box_bytes = c.pitch * c.box_rows * c.ck * 2;

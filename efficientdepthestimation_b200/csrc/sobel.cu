@@ -12,10 +12,12 @@ constexpr int STW = 64, STH = 16;       // tile of output pixels per block (256 
 __device__ __forceinline__ void sobel_at(const float (*t)[STW + 2], int y, int x, float& gx, float& gy) {
     // cross-correlation with ReSIDE/sobel.py:9-10, (y,x) are tile coords of the centre + 1
     const float a = t[y - 1][x - 1], b = t[y - 1][x], c = t[y - 1][x + 1];
-    const float d = t[y][x - 1], f = t[y][x + 1];
+    const float d = t[y][x - 1], e = t[y][x], f = t[y][x + 1];
     const float g = t[y + 1][x - 1], h = t[y + 1][x], i = t[y + 1][x + 1];
-    gx = (a - c) + 2.f * (d - f) + (g - i);
-    gy = (a + 2.f * b + c) - (g + 2.f * h + i);
+    // the zero taps stay in the sum: Conv2d multiplies them too, so a NaN/Inf anywhere in the 3x3 window
+    // poisons both gradients exactly as in the reference (0 * NaN = NaN); for finite inputs they add +0
+    gx = (a - c) + 2.f * (d - f) + (g - i) + (0.f * b + 0.f * e + 0.f * h);
+    gy = (a + 2.f * b + c) - (g + 2.f * h + i) + (0.f * d + 0.f * e + 0.f * f);
 }
 
 __device__ __forceinline__ void load_tile(float (*t)[STW + 2], const float* img, int h, int w, int y0, int x0) {

@@ -36,9 +36,16 @@ def test_two_rank_scalar_allreduce_matches_single_process(tmp_path):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
     env = dict(os.environ, EDE_ROOT=ROOT, OMP_NUM_THREADS="1")
-    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-                        "--master-addr", "127.0.0.1", "--master-port", "29731", str(script)],
-                       env=env, capture_output=True, text=True, timeout=300)
+    import socket
+    for attempt in range(2):  # a rendezvous port can be taken between probing and binding: retry once
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0))
+            port = s.getsockname()[1]
+        r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                            "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)],
+                           env=env, capture_output=True, text=True, timeout=300)
+        if r.returncode == 0:
+            break
     assert r.returncode == 0, r.stderr[-2000:]
     got = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
     assert got["world"] == 2 and got["slow"] == 2.0 and got["bounds"] == [3, 6]
