@@ -27,13 +27,13 @@ class EdeConv(Structure):
                 ("w_umma", c_void_p), ("w_direct", c_void_p)] + _ints(
         "n", "h", "w", "cin_p", "x_cs", "x_co", "oh", "ow", "cout_p", "y_cs", "y_co", "res_cs", "res_co",
         "kh", "kw", "sh", "sw", "pt", "pl", "act", "act_c_end", "x_dtype", "y_dtype", "x_layout", "relu_in",
-        "w_umma_cout_p", "w_umma_cin_p", "force_direct", "w_passes")
+        "w_umma_cout_p", "w_umma_cin_p", "force_direct", "w_passes", "w_pack_g")
 
 
 class EdeUmmaCfg(Structure):
     _fields_ = _ints("eligible", "a_mode", "ck", "swizzle", "bh", "bw", "pitch", "box_rows", "m_tiles", "n_pad",
                      "n_tiles", "a_stages", "b_stages", "a_stage_bytes", "b_stage_bytes", "smem_bytes",
-                     "tmem_cols", "tiles_w", "tiles_h", "flat") + [("useful_frac", c_double)] + _ints("swap", "reserved")
+                     "tmem_cols", "tiles_w", "tiles_h", "flat") + [("useful_frac", c_double)] + _ints("swap", "pack_g")
 
 
 class EdeDwConv(Structure):

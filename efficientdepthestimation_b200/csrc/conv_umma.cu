@@ -86,7 +86,8 @@ struct alignas(64) UmmaParams {
     int oh, ow, tiles_w, tiles_h, n_img, n_tiles, total_tiles;
     int a_mode, ck_bytes, k_bytes, n_chunks, kh, kw, sh, sw, pt, pl, w_passes;
     int bw, bh, pitch, box_bytes;
-    int m_tiles, n_pad, acc_cols, swap;      // swap: weights are the M-side operand, 256 pixels on N
+    int m_tiles, n_pad, acc_cols, swap;      // swap: weights are the M-side operand, 256 (240 packed) pixels on N
+    int pack_g, kw_steps, n_cols;            // pack_g taps share one MMA (M rows = [tap j][128/pack_g channels]); kw_steps = ceil(kw/pack_g); n_cols = UMMA N of the swapped form
     int a_stages, b_stages, a_stage_bytes, b_stage_bytes, b_tx_bytes;
     int layout_type, sbo_bytes, tmem_cols, flat;
     uint32_t idesc;
@@ -177,57 +178,76 @@ __device__ __forceinline__ void epilogue_store16(const UmmaParams& p, long long 
     if (c + 8 < p.cout_p) epilogue_store8<TY>(p, pix, c + 8, c_local + 8, acc + 8, s_scale, s_shift);
 }
 
-// Epilogue of the operand-swapped mode: TMEM lane = output channel, column = pixel of the 256-row window.
-// Each warp transposes 16 pixels x its 32 channels through a private 2 KB fp32 smem tile so that the second phase
-// (residual, activation, packing) works on 8-channel vectors of one pixel and stores 16/32 bytes per thread.
+// Epilogue of the operand-swapped mode: TMEM lane = [tap slot j][output channel], column = pixel of the window.
+// The four warps of a half-set (one per TMEM lane quarter) stage 16 window positions at a time in a shared
+// [16][128] fp32 tile -- the warp that holds tap slot j reads its columns j further right, so row k of the tile
+// holds, for every j, the partial sum that belongs to output position c0 + k -- and after one named barrier all
+// 128 threads finish 8-channel vectors of one pixel: sum over the tap slots, folded BN, residual, activation,
+// 16/32-byte stores that are contiguous along the channels of a pixel.  Two tiles alternate (one barrier/chunk).
+constexpr int STG_PITCH = 132;               // floats per staged window position (128 lanes + 4: no bank conflicts)
+constexpr int STG_FLOATS = 16 * STG_PITCH;
+
 template <typename TY>
 __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const TileCoord& t, uint32_t t_base, int quarter,
-                                                 int half, int lane, float* s_tr, float sc, float sf) {
+                                                 int half, int lane, int tid_h, float* s_stage, const float* s_scale,
+                                                 const float* s_shift) {
     const int wrap = p.a_mode == 0 ? p.pitch : p.bw;
-    const int pl = lane >> 2, g = lane & 3;                  // phase-2 role: pixel pl (+8), channel group g
-    const int c = quarter * 32 + g * 8;
-    const bool c_ok = c < p.cout_p;
-    const bool act_on = c < p.act_c_end && p.act != EDE_ACT_NONE;
-    for (int c0 = half * 16; c0 < 256; c0 += 16 * (EPI_WARPS / 4)) {
-        uint32_t acc[16];
-        tc_ld16(t_base + (uint32_t)c0, acc);
-        tc_ld_wait();
+    const int cg = 128 / p.pack_g;                           // channels per tap slot (32 / 64 / 128)
+    const int j = (quarter * 32) / cg;                       // tap slot of this warp's 32 lanes
+    const bool live = quarter * 32 - j * cg < p.cout_p;      // do these lanes hold real output channels?
+    const int r = quarter * 32 + lane;
+    const int groups = cg >> 3, pairs = 16 * groups;
+    int it = 0;
+    for (int c0 = half * 16; c0 < p.n_cols; c0 += 16 * (EPI_WARPS / 4), ++it) {
+        float* const buf = s_stage + (it & 1) * STG_FLOATS;
+        if (live) {
+            uint32_t acc[16];
+            tc_ld16(t_base + (uint32_t)(c0 + j), acc);
+            tc_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) s_tr[j * 32 + lane] = fmaf(__uint_as_float(acc[j]), sc, sf);
-        __syncwarp();
-#pragma unroll
-        for (int it = 0; it < 2; ++it) {
-            const int pj = pl + it * 8;
-            const int f = c0 + pj;                           // window row -> output pixel
+            for (int k = 0; k < 16; ++k) buf[k * STG_PITCH + r] = __uint_as_float(acc[k]);
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(2 + half) : "memory");
+        for (int i = tid_h; i < pairs; i += 128) {
+            const int pj = i / groups, c = (i - pj * groups) << 3;
+            if (c >= p.cout_p) continue;
+            const int f = c0 + pj;                           // window position -> output pixel
             int fr, fc, owb;
             if (p.a_mode == 0) { fr = f / wrap; fc = f - fr * wrap; owb = t.ow0; }
             else { const int m = f >> 7, rr = f & 127; fr = rr / wrap; fc = rr - fr * wrap; owb = t.ow0 + m * p.bw; }
             const int oh = t.oh0 + fr, ow = owb + fc;
-            if (c_ok && fc < p.bw && fr < p.bh && oh < p.oh && ow < p.ow) {
-                const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
-                float v[8];
-                const float4 lo = *reinterpret_cast<const float4*>(s_tr + pj * 32 + g * 8);
-                const float4 hi = *reinterpret_cast<const float4*>(s_tr + pj * 32 + g * 8 + 4);
-                v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w; v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
-                if (p.res) {
-                    float r[8];
-                    load8<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co + c, r);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) v[j] += r[j];
-                }
-                if (act_on) {
-                    if (p.act == EDE_ACT_RELU) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) v[j] = apply_act(v[j], p.act);
-                    }
-                }
-                store8<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co + c, v);
+            if (!(fc < p.bw && fr < p.bh && oh < p.oh && ow < p.ow)) continue;
+            const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
+            const float* src = buf + pj * STG_PITCH + c;
+            float4 lo = *reinterpret_cast<const float4*>(src), hi = *reinterpret_cast<const float4*>(src + 4);
+            for (int jj = 1; jj < p.pack_g; ++jj) {
+                const float4 l2 = *reinterpret_cast<const float4*>(src + jj * cg);
+                const float4 h2 = *reinterpret_cast<const float4*>(src + jj * cg + 4);
+                lo.x += l2.x; lo.y += l2.y; lo.z += l2.z; lo.w += l2.w;
+                hi.x += h2.x; hi.y += h2.y; hi.z += h2.z; hi.w += h2.w;
             }
+            const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c), s1 = *reinterpret_cast<const float4*>(s_scale + c + 4);
+            const float4 f0 = *reinterpret_cast<const float4*>(s_shift + c), f1 = *reinterpret_cast<const float4*>(s_shift + c + 4);
+            float v[8];
+            v[0] = fmaf(lo.x, s0.x, f0.x); v[1] = fmaf(lo.y, s0.y, f0.y); v[2] = fmaf(lo.z, s0.z, f0.z); v[3] = fmaf(lo.w, s0.w, f0.w);
+            v[4] = fmaf(hi.x, s1.x, f1.x); v[5] = fmaf(hi.y, s1.y, f1.y); v[6] = fmaf(hi.z, s1.z, f1.z); v[7] = fmaf(hi.w, s1.w, f1.w);
+            if (p.res) {
+                float rs[8];
+                load8<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co + c, rs);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) v[q] += rs[q];
+            }
+            if (c < p.act_c_end && p.act != EDE_ACT_NONE) {
+                if (p.act == EDE_ACT_RELU) {
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) v[q] = fmaxf(v[q], 0.f);
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) v[q] = apply_act(v[q], p.act);
+                }
+            }
+            store8<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co + c, v);
         }
-        __syncwarp();
     }
 }
 
@@ -252,7 +272,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
     float* const s_shift = s_scale + 256;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int sp_taps = p.kh * p.kw;              // spatial taps
+    const int sp_taps = p.kh * p.kw_steps;        // spatial steps (kw_steps = kw unless taps are packed on M)
     const int taps = sp_taps * p.w_passes;        // weight tiles per channel chunk ([w_hi taps ; w_lo taps])
     unsigned long long prof_t0 = 0;
     if (p.prof && threadIdx.x == 0) prof_t0 = gtime();
@@ -272,6 +292,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
+    if (p.a_mode == 0) {
+        // The shifted UMMA windows of the resident mode read past the TMA box (into the tail of the stage, never
+        // written by TMA).  Those rows only meet invalid output positions or, with packed taps, the zero weight
+        // rows of taps >= kw -- but 0 * stale NaN is NaN, so the tails are zeroed once and stay zero.
+        const int tail0 = p.box_bytes & ~15, tail_n = (p.a_stage_bytes - tail0) >> 4;
+        for (int st = 0; st < p.a_stages; ++st) {
+            uint8_t* base = smem_raw + (a_base - smem_u32(smem_raw)) + (size_t)st * p.a_stage_bytes + tail0;
+            for (int i = threadIdx.x; i < tail_n; i += NUM_THREADS) reinterpret_cast<uint4*>(base)[i] = make_uint4(0, 0, 0, 0);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -282,7 +313,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
         // ===================== TMA producer (whole warp walks the loop, one elected lane issues) ==========
         int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0;
         const int ck = p.ck_bytes >> 1;
-        const int a_mode = p.a_mode, n_chunks = p.n_chunks, m_tiles = p.m_tiles, kw = p.kw;
+        const int a_mode = p.a_mode, n_chunks = p.n_chunks, m_tiles = p.m_tiles, kw = p.kw_steps;
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
             const TileCoord t = decode_tile(p, tile);
             for (int chunk = 0; chunk < n_chunks; ++chunk) {
@@ -323,7 +354,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
     } else if (warp == 1) {
         // ===================== MMA issuer (warp-uniform loop state, one elected lane issues) ==============
         const int a_mode = p.a_mode, m_tiles = p.m_tiles, n_pad = p.n_pad, n_chunks = p.n_chunks, swap = p.swap;
-        const int a_stages = p.a_stages, b_stages = p.b_stages, kw = p.kw, pitch = p.pitch;
+        const int a_stages = p.a_stages, b_stages = p.b_stages, kw = p.kw_steps, pitch = p.pitch, pack_g = p.pack_g;
         const uint32_t ck16 = (uint32_t)p.ck_bytes >> 4;            // (bytes >> 4) units of the address field
         const uint32_t a_stage16 = (uint32_t)p.a_stage_bytes >> 4, b_stage16 = (uint32_t)p.b_stage_bytes >> 4;
         const uint32_t m_step16 = 128u * ck16;                       // 128 pixel rows
@@ -359,7 +390,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                     if (p.prof) w_ops += clock64() - c0;
                     tc_fence_after();
                     if (tap == sp_taps) { ky = 0; kx = 0; }
-                    const uint32_t shift16 = a_mode == 0 ? (uint32_t)(ky * pitch + kx) * ck16 : 0u;
+                    const uint32_t shift16 = a_mode == 0 ? (uint32_t)(ky * pitch + kx * pack_g) * ck16 : 0u;
                     const uint32_t a0 = a_base16 + (uint32_t)a_st * a_stage16 + shift16;
                     const uint32_t b0 = b_base16 + (uint32_t)b_st * b_stage16;
                     if (elect_one()) {
@@ -427,14 +458,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
             tc_fence_after();
             const uint32_t t_base = tmem_addr + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_st * p.acc_cols);
             if (p.swap) {
-                // accumulator lane = output channel, column = pixel of the 256-row window
-                if (quarter * 32 < p.cout_p) {
-                    float* const s_tr = s_shift + 256 + (warp - 2) * 512;      // this warp's [16 px][32 ch] fp32 tile
-                    const float sc = r < p.cout_p ? __ldg(p.scale + r) : 0.f, sf = r < p.cout_p ? __ldg(p.shift + r) : 0.f;
-                    if (p.y_dtype == EDE_BF16) epilogue_swapped<__nv_bfloat16>(p, t, t_base, quarter, half, lane, s_tr, sc, sf);
-                    else if (p.y_dtype == EDE_BF16X2) epilogue_swapped<bf16x2_t>(p, t, t_base, quarter, half, lane, s_tr, sc, sf);
-                    else epilogue_swapped<float>(p, t, t_base, quarter, half, lane, s_tr, sc, sf);
-                }
+                // accumulator lane = [tap slot][output channel], column = pixel of the window
+                float* const s_stage = s_shift + 256 + half * (2 * STG_FLOATS);
+                const int tid_h = (warp - 2 - 4 * half) * 32 + lane;
+                const uint32_t t_col = t_base;
+                if (p.y_dtype == EDE_BF16) epilogue_swapped<__nv_bfloat16>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift);
+                else if (p.y_dtype == EDE_BF16X2) epilogue_swapped<bf16x2_t>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift);
+                else epilogue_swapped<float>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift);
             } else {
                 const int nch = p.n_pad >> 4;         // 16-column chunks of one accumulator row (n_pad % 16 == 0)
                 for (int m = 0; m < p.m_tiles; ++m) {
@@ -510,8 +540,8 @@ static int env_int(const char* name, int dflt) {
     return (s && *s) ? atoi(s) : dflt;
 }
 
-constexpr int SMEM_BUDGET = 196 * 1024;      // operand rings; barriers + alignment slack on top
-constexpr int SMEM_EXTRA = 1024 + 512 + 2048 + EPI_WARPS * 2048;   // alignment slack + barriers + scale/shift slice + one 2 KB transpose tile per epilogue warp (swapped epilogue)
+constexpr int SMEM_BUDGET = 189 * 1024;      // operand rings; barriers + alignment slack on top
+constexpr int SMEM_EXTRA = 1024 + 512 + 2048 + 4 * 16 * 132 * 4;   // alignment slack + barriers + scale/shift slice + 2 half-sets x 2 staging tiles (swapped epilogue)
 
 static bool umma_eligible(const EdeConv& a) {
     if (a.force_direct || a.w_umma == nullptr) return false;
@@ -522,6 +552,7 @@ static bool umma_eligible(const EdeConv& a) {
     if ((a.x_cs | a.x_co | a.y_cs | a.y_co | a.cin_p | a.cout_p) & 7) return false;
     if (a.res && ((a.res_cs | a.res_co) & 7)) return false;
     if (a.w_umma_cin_p & 7) return false;
+    if (a.w_pack_g > 1 && (a.w_umma_cout_p != 128 || (a.w_pack_g != 2 && a.w_pack_g != 4))) return false;
     return true;
 }
 
@@ -567,6 +598,10 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
 
     EdeUmmaCfg best{};
     double best_time = 1e300;
+    const bool unpacked_ok = a.w_pack_g <= 1;            // -1: caller asks which packing to prepack for
+    // contention factors on top of the isolated MMA rates (TMA fills and the MMA operand reads share the
+    // 128 B/clk of shared-memory bandwidth; measured on the decoder convs with tools/cta_timeline.py)
+    const double F_NOSWAP = 1.5, F_SWAP = 1.3;
     // Channel chunk: always the 128-byte swizzle (64 bf16 channels per smem row) unless forced -- narrower
     // swizzles feed the tensor core at 63 % / 45 % of the rate (measured, profiles/r01_mma_rate.md; the
     // operand-swapped N = 256 form loses more), and the MMA issuer skips the K steps of the last chunk
@@ -586,7 +621,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
             const int b_bytes = round_up(n_pad * ck_bytes, 1024);
             const int max_t = 256 / n_pad;                // two accumulator stages share the 512 TMEM columns
             if (max_t < 1) continue;
-            const double t_mma = mma_cycles(ck_bytes, n_pad);
+            const double t_mma = mma_cycles(ck_bytes, n_pad) * F_NOSWAP;
             auto consider = [&](const EdeUmmaCfg& cand, double a_bytes_tile, double b_bytes_tile) {
                 const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img * n_tiles;
                 const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
@@ -609,7 +644,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                 }
             };
             // ---- per-tap candidates: every (tap, chunk) TMA-loads its own 128-pixel boxes
-            if (force_mode != 0) {
+            if (force_mode != 0 && unpacked_ok) {
                 for (int bw = 128; bw >= 1; bw >>= 1) {
                     const int bh = 128 / bw;
                     if (bw * a.sw > 256 || bh * a.sh > 256) continue;
@@ -630,7 +665,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                 }
             }
             // ---- resident candidates (stride 1, k x k with k > 1): halo tile loaded once per chunk
-            if (a.sh == 1 && a.kh * a.kw >= 9 && force_mode != 1 && !is_1x1) {
+            if (a.sh == 1 && a.kh * a.kw >= 9 && force_mode != 1 && !is_1x1 && unpacked_ok) {
                 for (int div = 1; div <= 8; ++div) {
                     const int bw = ceil_div(OW, div);
                     const int P = bw + a.kw - 1;
@@ -657,38 +692,51 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
             }
         }
     }
-    // ---- operand-swapped candidates (Cout <= 128): weights on the M side (128 rows, zero padded by TMA),
-    // 256 pixels on N.  One MMA then costs max(128, base) cycles for 256 pixels instead of 97 for 128.
+    // ---- operand-swapped candidates (Cout <= 128): weights on the M side (128 rows), pixels on N.  One MMA costs
+    // 128 cycles for 256 pixels instead of 97 for 128.  With Cout <= 64 / 32 the 128 M rows hold G = 2 / 4 taps
+    // (kx, kx+1, ...) of the kernel row at once -- row [j][c] = W[c][.][ky][gx*G + j] -- so a kernel row costs
+    // ceil(kw / G) MMAs instead of kw; the epilogue adds the G partial sums, each read j columns further right.
+    // Packed tiles use N = 240 so that those shifted reads stay inside the 256-column accumulator stage.
     const int force_swap = env_int("EDE_UMMA_SWAP", -1);
+    const int force_pack = env_int("EDE_UMMA_PACK", -1);
     if (n16 <= 128 && force_swap != 0) {
         if (force_swap == 1) best_time = 1e300;
-        for (int ci = 0; ci < 3; ++ci) {
-            const int ck = cks[ci];
-            if (force_ck ? force_ck != ck : ck != 64) continue;
-            const int ck_bytes = ck * 2, n_chunks = ceil_div(a.cin_p, ck);
-            const int b_bytes = round_up(128 * ck_bytes, 1024);
-            // 256 pixel rows on the N side: 128 clk with the 128 B swizzle; ~230 / ~330 observed with 64 B / 32 B
-            const double t_mma = ck_bytes == 128 ? 128.0 : ck_bytes == 64 ? 230.0 : 330.0;
+        const int gs[3] = {4, 2, 1};
+        for (int gi = 0; gi < 3; ++gi) {
+            const int G = gs[gi];
+            if (G > 1 && (a.cout_p > 128 / G || a.kw < 2 || a.sh != 1 || is_1x1)) continue;
+            if (a.w_pack_g >= 0 && std::max(1, a.w_pack_g) != G) continue;      // weights are already packed for one G
+            if (force_pack >= 0 && a.w_pack_g < 0 && std::max(1, force_pack) != G) continue;
+            const int kws = ceil_div(a.kw, G);
+            const int steps = a.kh * kws * a.w_passes;
+            const int n_cols = G > 1 ? 240 : 256;
+            const int ck = 64, ck_bytes = 128, n_chunks = ceil_div(a.cin_p, ck);
+            const int b_bytes = 128 * ck_bytes;
+            const double t_mma = n_cols * 0.5 * F_SWAP;
             auto consider = [&](const EdeUmmaCfg& cand, double a_bytes_tile) {
                 const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img;
                 const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
-                const double mma = (double)taps_w * ks_total * t_mma;
-                const double mem = (a_bytes_tile + (double)n_chunks * taps_w * 128 * ck_bytes) / L2_BYTES_PER_CLK_PER_SM;
+                const double mma = (double)steps * ks_total * t_mma;
+                const double w_rows = G > 1 ? 128.0 : (double)std::min(128, round_up(a.cout_p, 8));
+                const double mem = (a_bytes_tile + (double)steps * w_rows * std::min(a.cin_p, n_chunks * ck) * 2.0) /
+                                   L2_BYTES_PER_CLK_PER_SM;
                 const double epi = 16.0 * 220.0 + 600.0;
-                const double per_stage = mma / std::max(1, n_chunks * taps_w);
-                const double lat = std::max(0.0, 1500.0 - cand.b_stages * per_stage) * 0.15 * n_chunks * taps_w /
+                const double per_stage = mma / std::max(1, n_chunks * steps);
+                const double lat = std::max(0.0, 1500.0 - cand.b_stages * per_stage) * 0.15 * n_chunks * steps /
                                    std::max(1, cand.b_stages);
                 const double t = rounds * (std::max(std::max(mma, mem), epi) + lat + 300.0) + 4000.0;
                 if (t < best_time) {
                     best_time = t;
                     best = cand;
                     best.swap = 1;
+                    best.pack_g = G;
                     best.ck = ck; best.swizzle = ck_bytes; best.n_pad = 128; best.n_tiles = 1;
                     best.b_stage_bytes = b_bytes;
-                    best.useful_frac = cand.useful_frac * ((double)a.cin_p / (n_chunks * ck)) * (a.cout_p / 128.0);
+                    best.useful_frac = cand.useful_frac * ((double)a.cin_p / (ks_total * 16)) *
+                                       ((double)a.cout_p * a.kw / (128.0 * kws));
                 }
             };
-            if (force_mode != 0) {
+            if (force_mode != 0 && G == 1) {
                 for (int bw = 128; bw >= 1; bw >>= 1) {
                     const int bh = 128 / bw;
                     if (bw * a.sw > 256 || bh * a.sh > 256) continue;
@@ -702,7 +750,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                     cand.m_tiles = 2; cand.a_stages = cand.b_stages = stages; cand.a_stage_bytes = a_bytes;
                     cand.tiles_w = ceil_div(OW, bw * 2); cand.tiles_h = ceil_div(OH, bh);
                     cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * 256);
-                    consider(cand, (double)n_chunks * taps_w * a_bytes);
+                    consider(cand, (double)n_chunks * steps * a_bytes);
                 }
             }
             if (a.sh == 1 && a.kh * a.kw >= 9 && force_mode != 1 && !is_1x1) {
@@ -714,8 +762,8 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                         const int box_rows = bh + a.kh - 1;
                         if (box_rows > 256) break;
                         const int m_need = (bh - 1) * P + bw;
-                        if (m_need > 256) break;
-                        const int rows_alloc = std::max(box_rows * P, 256 + (a.kh - 1) * P + a.kw - 1);
+                        if (m_need + G - 1 > n_cols) break;
+                        const int rows_alloc = std::max(box_rows * P, n_cols + (a.kh - 1) * P + kws * G);
                         const int a_bytes = round_up(rows_alloc * ck_bytes, 1024);
                         const int b_stages = fit_stages(2 * a_bytes, b_bytes, 4);
                         if (b_stages < 3) continue;
@@ -723,7 +771,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                         cand.a_mode = 0; cand.bh = bh; cand.bw = bw; cand.pitch = P; cand.box_rows = box_rows;
                         cand.m_tiles = 2; cand.a_stages = 2; cand.b_stages = b_stages; cand.a_stage_bytes = a_bytes;
                         cand.tiles_w = ceil_div(OW, bw); cand.tiles_h = ceil_div(OH, bh);
-                        cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * 256);
+                        cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * n_cols);
                         consider(cand, (double)n_chunks * box_rows * P * ck_bytes);
                     }
                 }
@@ -733,6 +781,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     if (best.m_tiles == 0) return;
     c = best;
     c.eligible = 1;
+    if (c.pack_g < 1) c.pack_g = 1;
     c.tmem_cols = c.swap ? 512 : pow2_cols(2 * c.m_tiles * c.n_pad);
     c.smem_bytes = c.a_stages * c.a_stage_bytes + c.b_stages * c.b_stage_bytes + SMEM_EXTRA;
     c.flat = is_1x1;
@@ -789,6 +838,7 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
                               (cuuint64_t)(a.kh * a.kw * a.w_passes)};
         cuuint64_t strides[2] = {(cuuint64_t)a.w_umma_cin_p * 2, (cuuint64_t)a.w_umma_cin_p * 2 * a.w_umma_cout_p};
         cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)(c.swap ? 128 : c.n_pad), 1};
+        dims[2] = (cuuint64_t)(a.kh * ceil_div(a.kw, c.pack_g) * a.w_passes);
         cuuint32_t es[3] = {1, 1, 1};
         CUresult r = enc(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, (void*)a.w_umma, dims, strides, box, es,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -816,7 +866,8 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     p.sbo_bytes = 8 * c.ck * 2;
     p.tmem_cols = c.tmem_cols;
     p.flat = c.flat;
-    p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)((c.swap ? 256 : c.n_pad) >> 3) << 17) | ((128u >> 4) << 24);
+    p.pack_g = c.pack_g; p.kw_steps = ceil_div(a.kw, c.pack_g); p.n_cols = c.swap ? (c.pack_g > 1 ? 240 : 256) : c.n_pad;
+    p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.n_cols >> 3) << 17) | ((128u >> 4) << 24);
     p.swap = c.swap;
     p.y = a.y; p.res = a.res; p.scale = a.scale; p.shift = a.shift;
     p.y_cs = a.y_cs; p.y_co = a.y_co; p.res_cs = a.res_cs; p.res_co = a.res_co;

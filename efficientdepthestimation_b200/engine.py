@@ -275,21 +275,29 @@ class Graph:
         # hi+lo weights whenever the OUTPUT is kept at split precision (the accurate encoder path)
         passes = 2 if (out.dtype == A.BF16X2 and self.precision != "fp32") else 1
         w_direct = self._dev(P.pack_direct(full))
-        w_umma, co16, ci64 = P.pack_umma(full, passes)
-        w_umma = self._dev(w_umma)
         scale = self._dev(torch.cat(scales))
         shift = self._dev(torch.cat(shifts))
         if res is not None and res.dtype != out.dtype:
             res = self.resize(res, (res.h, res.w), out_dtype=out.dtype, force=True, tag=tag + ".res_cast")
         st = A.EdeConv(x=None, y=None, res=None, scale=self._ptr(scale), shift=self._ptr(shift),
-                       w_umma=self._ptr(w_umma), w_direct=self._ptr(w_direct),
+                       w_umma=1, w_direct=self._ptr(w_direct),
                        n=x.n, h=x.h, w=x.w, cin_p=x.c_p * mul, x_cs=x.buf.cs * mul, x_co=x.co * mul,
                        oh=oh, ow=ow, cout_p=cout_p, y_cs=out.buf.cs, y_co=out.co,
                        res_cs=res.buf.cs if res is not None else 0, res_co=res.co if res is not None else 0,
                        kh=kh, kw=kw, sh=stride, sw=stride, pt=pt, pl=pl, act=act, act_c_end=act_end,
                        x_dtype=A.BF16 if split_in else x.dtype, y_dtype=out.dtype, x_layout=A.NHWC,
-                       relu_in=1 if relu_in else 0, w_umma_cout_p=co16, w_umma_cin_p=ci64,
-                       force_direct=1 if self.precision == "fp32" else 0, w_passes=passes)
+                       relu_in=1 if relu_in else 0, w_umma_cout_p=P.ceil_to(cout_p, 16),
+                       w_umma_cin_p=P.ceil_to(x.c_p * mul, 64),
+                       force_direct=1 if self.precision == "fp32" else 0, w_passes=passes, w_pack_g=-1)
+        # ask the tile picker how many kernel-row taps it wants on the 128 M rows, then prepack for exactly that
+        cfg = A.umma_config(st)
+        pack_g = int(cfg.pack_g) if cfg.eligible and cfg.pack_g > 1 else 1
+        if pack_g > 1:
+            w_umma, co16, ci64 = P.pack_umma_taps(full, passes, pack_g)
+        else:
+            w_umma, co16, ci64 = P.pack_umma(full, passes)
+        w_umma = self._dev(w_umma)
+        st.w_umma, st.w_umma_cout_p, st.w_umma_cin_p, st.w_pack_g = self._ptr(w_umma), co16, ci64, pack_g
         refs = [("x", x.buf), ("y", out.buf)] + ([("res", res.buf)] if res is not None else [])
         self._add(A.OP_CONV, st, refs, tag)
         return out

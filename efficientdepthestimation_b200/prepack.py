@@ -64,6 +64,29 @@ def pack_umma(full: torch.Tensor, passes: int = 1) -> Tuple[torch.Tensor, int, i
     return out.contiguous(), co_p, ci_p
 
 
+def pack_umma_taps(full: torch.Tensor, passes: int, g: int) -> Tuple[torch.Tensor, int, int]:
+    """Tap-packed weights for the operand-swapped tcgen05 form with `g` (2 or 4) taps of a kernel row per MMA
+    (include/ede.h, EdeConv.w_pack_g): [cout_p][cin_p][kh][kw] -> bf16 [passes*kh*ceil(kw/g)][128][cin_p64] with
+    row j*(128/g)+c of tile (ky, gx) = w[c][.][ky][gx*g + j]; rows of taps beyond kw and of channels beyond
+    cout_p stay zero.  passes=2 appends the bf16 low halves as in pack_umma."""
+    co, ci, kh, kw = full.shape
+    cg = 128 // g
+    if co > cg:
+        raise ValueError(f"pack_umma_taps: {co} output lanes do not fit {g} taps in 128 rows")
+    kws, ci_p = (kw + g - 1) // g, ceil_to(ci, 64)
+    tiles = torch.zeros(kh * kws, 128, ci, dtype=torch.float32, device=full.device)
+    for ky in range(kh):
+        for kx in range(kw):
+            gx, j = divmod(kx, g)
+            tiles[ky * kws + gx, j * cg:j * cg + co] = full[:, :, ky, kx]
+    out = torch.zeros(passes * kh * kws, 128, ci_p, dtype=torch.bfloat16, device=full.device)
+    hi = tiles.to(torch.bfloat16)
+    out[:kh * kws, :, :ci] = hi
+    if passes == 2:
+        out[kh * kws:, :, :ci] = (tiles - hi.float()).to(torch.bfloat16)
+    return out.contiguous(), 128, ci_p
+
+
 def fold_bn(cout: int, bn: Optional[dict], conv_bias: Optional[torch.Tensor], device) -> Tuple[torch.Tensor, torch.Tensor]:
     """-> (scale, shift) fp32 [cout] with  bn(conv(x)+b) == scale*conv(x) + shift.
     bn: dict(weight, bias, mean, var, eps) or None."""

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 2
+#define EDE_ABI_VERSION 3
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
@@ -64,6 +64,11 @@ typedef struct EdeConv {
     int32_t w_umma_cout_p, w_umma_cin_p;         /* padded dims of w_umma                        */
     int32_t force_direct;   /* 1: never take the tcgen05 path (fp32 parity mode / debugging)     */
     int32_t w_passes;       /* 1, or 2: w_umma holds 2*kh*kw taps, [w_hi taps ; w_lo taps]          */
+    int32_t w_pack_g;       /* how w_umma packs kernel-row taps on its Cout axis: 0/1 = one tap per tile
+                               (layout above); G = 2/4: tiles [kh*ceil(kw/G)][128][cin_p64] with row
+                               j*(128/G)+c = w[c][.][ky][gx*G+j] (zero rows for taps >= kw), needs
+                               cout_p <= 128/G; -1 only for ede_conv2d_umma_config: 'which G should I
+                               prepack for?' (answer in EdeUmmaCfg.pack_g)                            */
 } EdeConv;
 int ede_conv2d(const EdeConv* a, void* stream);
 
@@ -79,7 +84,7 @@ typedef struct EdeUmmaCfg {
     int32_t tiles_w, tiles_h, flat;              /* flat: N*H*W folded into one pixel axis (1x1)  */
     double useful_frac;     /* real MACs / issued tensor MACs                                    */
     int32_t swap;           /* 1: weights are the M-side operand (Cout <= 128), 256 pixels on N  */
-    int32_t reserved;
+    int32_t pack_g;         /* kernel-row taps per MMA in the swapped form (1, 2 or 4), see w_pack_g */
 } EdeUmmaCfg;
 int ede_conv2d_umma_config(const EdeConv* a, EdeUmmaCfg* out);
 

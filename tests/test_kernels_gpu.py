@@ -56,6 +56,12 @@ CONV_CASES = [
     ("7x7s2_stem", 2, 228, 304, 3, 64, 7, 2, (3, 3, 3, 3), False, A.ACT_RELU),
     ("3x3s2_asym_stem", 2, 228, 304, 3, 32, 3, 2, (0, 0, 1, 1), False, A.ACT_NONE),
     ("5x5s2_asym", 1, 57, 76, 144, 40, 5, 2, (1, 1, 2, 2), False, A.ACT_NONE),
+    # kernel-row taps packed on the 128 M rows of the operand-swapped form (EdeConv.w_pack_g = 4 / 2)
+    ("5x5_24_to_32_pack4", 2, 57, 76, 24, 32, 5, 1, (2, 2, 2, 2), False, A.ACT_RELU),
+    ("5x5_64_to_64_pack2", 2, 40, 50, 64, 64, 5, 1, (2, 2, 2, 2), False, A.ACT_RELU),
+    ("3x3_40_to_40_pack2_res", 2, 28, 38, 40, 40, 3, 1, (1, 1, 1, 1), True, A.ACT_RELU),
+    ("3x3_16_to_8_pack4_wide", 1, 114, 152, 16, 8, 3, 1, (1, 1, 1, 1), True, A.ACT_SWISH),
+    ("5x5_74_to_1_pack4_bias", 1, 114, 152, 74, 1, 5, 1, (2, 2, 2, 2), False, A.ACT_NONE),
 ]
 
 
@@ -92,6 +98,7 @@ def test_conv2d(cuda, lib, case, mode):
     full = P.scatter_weight(wt, in_lanes, P.identity_map(cout, cout_p))
     w_direct = P.pack_direct(full)
     w_umma, co16, ci64 = P.pack_umma(full, passes)
+    pack_g = 1
     sc = P.place_lanes(scale, P.identity_map(cout, cout_p))
     sf = P.place_lanes(shift, P.identity_map(cout, cout_p))
     a = A.EdeConv(x=xin.data_ptr(), y=y.data_ptr(), res=resin.data_ptr() if use_res else None, scale=sc.data_ptr(),
@@ -99,9 +106,16 @@ def test_conv2d(cuda, lib, case, mode):
                   cin_p=cin_p * mul, x_cs=cin_p * mul, x_co=0, oh=oh, ow=ow, cout_p=cout_p, y_cs=cout_p, y_co=0,
                   res_cs=cout_p, res_co=0, kh=k, kw=k, sh=s, sw=s, pt=pt, pl=pl, act=act, act_c_end=cout_p,
                   x_dtype=x_dt, y_dtype=io_dt, x_layout=A.NHWC, relu_in=0, w_umma_cout_p=co16, w_umma_cin_p=ci64,
-                  force_direct=1 if mode == "fp32" else 0, w_passes=passes)
+                  force_direct=1 if mode == "fp32" else 0, w_passes=passes, w_pack_g=-1)
+    # as engine.Graph.conv does: ask the tile picker which tap packing it wants, prepack for exactly that
+    q = A.umma_config(a)
+    pack_g = int(q.pack_g) if q.eligible and q.pack_g > 1 else 1
+    if pack_g > 1:
+        w_umma, co16, ci64 = P.pack_umma_taps(full, passes, pack_g)
+        a.w_umma, a.w_umma_cout_p, a.w_umma_cin_p = w_umma.data_ptr(), co16, ci64
+    a.w_pack_g = pack_g
     cfg = A.umma_config(a)
-    assert bool(cfg.eligible) == (mode != "fp32")
+    assert bool(cfg.eligible) == (mode != "fp32") and (not cfg.eligible or cfg.pack_g == pack_g)
     A.check(lib.ede_conv2d(C.byref(a), stream()), "ede_conv2d")
     torch.cuda.synchronize()
     ref = F.conv2d(F.pad(x_eff.double(), (pl, pr, pt, pb)), w_eff.double(), None, s)
