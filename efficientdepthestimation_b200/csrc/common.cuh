@@ -69,13 +69,27 @@ template <> struct Elt<bf16x2_t> {
     }
 };
 
-// 8 consecutive channels (one 16-byte bf16 vector / two float4) <-> 8 floats
+// 256-bit global accesses (sm_100: LDG.E.256 / STG.E.256); p must be 32-byte aligned
+__device__ __forceinline__ void ldg256(const void* p, uint32_t (&r)[8]) {
+    asm volatile("ld.global.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "l"(p));
+}
+__device__ __forceinline__ void stg256(void* p, const uint32_t (&r)[8]) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]),
+                 "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+}
+
+// 8 consecutive channels (one 16-byte bf16 vector / one 32-byte fp32 or split-bf16 vector) <-> 8 floats
 template <typename T> __device__ __forceinline__ void load8(const T* p, float (&v)[8]);
 template <> __device__ __forceinline__ void load8<float>(const float* p, float (&v)[8]) {
     float4 a = *reinterpret_cast<const float4*>(p);
     float4 b = *reinterpret_cast<const float4*>(p + 4);
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
 }
+__device__ __forceinline__ float bf16lo_f(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16hi_f(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
     uint4 u = *reinterpret_cast<const uint4*>(p);
     const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
@@ -86,20 +100,20 @@ template <> __device__ __forceinline__ void load8<__nv_bfloat16>(const __nv_bflo
     }
 }
 template <> __device__ __forceinline__ void load8<bf16x2_t>(const bf16x2_t* p, float (&v)[8]) {
-    const uint4 uh = *reinterpret_cast<const uint4*>(p);
-    const uint4 ul = *(reinterpret_cast<const uint4*>(p) + 1);
-    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&uh);
-    const __nv_bfloat162* l = reinterpret_cast<const __nv_bfloat162*>(&ul);
+    uint32_t u[8];                                   // [4 x hi pairs][4 x lo pairs], one 256-bit load
+    ldg256(p, u);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const float2 a = __bfloat1622float2(h[i]), b = __bfloat1622float2(l[i]);
-        v[2 * i] = a.x + b.x; v[2 * i + 1] = a.y + b.y;
+        v[2 * i] = bf16lo_f(u[i]) + bf16lo_f(u[4 + i]);
+        v[2 * i + 1] = bf16hi_f(u[i]) + bf16hi_f(u[4 + i]);
     }
 }
 template <typename T> __device__ __forceinline__ void store8(T* p, const float (&v)[8]);
 template <> __device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
-    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
-    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    uint32_t u[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) u[i] = __float_as_uint(v[i]);
+    stg256(p, u);
 }
 template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
     uint4 u;
@@ -110,17 +124,15 @@ template <> __device__ __forceinline__ void store8<__nv_bfloat16>(__nv_bfloat16*
 }
 
 template <> __device__ __forceinline__ void store8<bf16x2_t>(bf16x2_t* p, const float (&v)[8]) {
-    uint4 uh, ul;
-    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&uh);
-    __nv_bfloat162* l = reinterpret_cast<__nv_bfloat162*>(&ul);
+    uint32_t u[8];                                   // [4 x hi pairs][4 x lo pairs], one 256-bit store
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-        const float2 r = __bfloat1622float2(h[i]);
-        l[i] = __floats2bfloat162_rn(v[2 * i] - r.x, v[2 * i + 1] - r.y);
+        const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+        u[i] = *reinterpret_cast<const uint32_t*>(&h);
+        const __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * i] - bf16lo_f(u[i]), v[2 * i + 1] - bf16hi_f(u[i]));
+        u[4 + i] = *reinterpret_cast<const uint32_t*>(&l);
     }
-    *reinterpret_cast<uint4*>(p) = uh;
-    *(reinterpret_cast<uint4*>(p) + 1) = ul;
+    stg256(p, u);
 }
 
 template <typename T> __device__ __forceinline__ float round_as(float v);

@@ -137,9 +137,18 @@ __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) 
     return t;
 }
 
-// one 8-channel group of the epilogue: folded BN, residual, activation, typed store
-template <typename TY>
-__device__ __forceinline__ void epilogue_store8(const UmmaParams& p, long long pix, int c, int c_local,
+// one 8-channel group of the epilogue: folded BN, residual, activation, typed store.  ACT and RES are compile
+// time (the tile loop dispatches once per tile), so the hot loop carries no per-element branches.
+template <int ACT>
+__device__ __forceinline__ float act_ct(float v) {
+    if (ACT == EDE_ACT_RELU) return fmaxf(v, 0.f);
+    if (ACT == EDE_ACT_SWISH) return __fdividef(v, 1.f + __expf(-v));
+    return v;
+}
+constexpr int ACT_RUNTIME = 99;              // kernel variant that reads p.act at run time (sigmoid, anything else)
+
+template <typename TY, int ACT, bool RES>
+__device__ __forceinline__ void epilogue_store8(const UmmaParams& p, TY* yrow, const TY* rrow, int c, int c_local,
                                                 const uint32_t* acc, const float* s_scale, const float* s_shift) {
     float v[8];
     const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c_local);
@@ -150,32 +159,48 @@ __device__ __forceinline__ void epilogue_store8(const UmmaParams& p, long long p
     v[2] = fmaf(__uint_as_float(acc[2]), s0.z, f0.z); v[3] = fmaf(__uint_as_float(acc[3]), s0.w, f0.w);
     v[4] = fmaf(__uint_as_float(acc[4]), s1.x, f1.x); v[5] = fmaf(__uint_as_float(acc[5]), s1.y, f1.y);
     v[6] = fmaf(__uint_as_float(acc[6]), s1.z, f1.z); v[7] = fmaf(__uint_as_float(acc[7]), s1.w, f1.w);
-    if (p.res) {
+    if (RES) {
         float r[8];
-        load8<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co + c, r);
+        load8<TY>(rrow + c, r);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] += r[j];
     }
-    if (c < p.act_c_end) {                 // act_c_end is a multiple of 8: whole groups are (in)active
-        if (p.act == EDE_ACT_RELU) {
+    if (ACT != EDE_ACT_NONE && c < p.act_c_end) {          // act_c_end is a multiple of 8: whole groups are (in)active
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
-        } else if (p.act == EDE_ACT_SWISH) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = __fdividef(v[j], 1.f + __expf(-v[j]));
-        } else if (p.act == EDE_ACT_SIGMOID) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = __fdividef(1.f, 1.f + __expf(-v[j]));
-        }
+        for (int j = 0; j < 8; ++j) v[j] = ACT == ACT_RUNTIME ? apply_act(v[j], p.act) : act_ct<ACT>(v[j]);
     }
-    store8<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co + c, v);
+    store8<TY>(yrow + c, v);
 }
 
-template <typename TY>
-__device__ __forceinline__ void epilogue_store16(const UmmaParams& p, long long pix, int c, int c_local,
-                                                 const uint32_t* acc, const float* s_scale, const float* s_shift) {
-    if (c < p.cout_p) epilogue_store8<TY>(p, pix, c, c_local, acc, s_scale, s_shift);
-    if (c + 8 < p.cout_p) epilogue_store8<TY>(p, pix, c + 8, c_local + 8, acc + 8, s_scale, s_shift);
+// all 16-column chunks of one accumulator row that this warp drains (chunks half, half + 2, ...): the next
+// tcgen05.ld is in flight while the current chunk is converted and stored
+template <typename TY, int ACT, bool RES>
+__device__ __forceinline__ void epilogue_row(const UmmaParams& p, uint32_t t_row, int nch, int half, bool valid,
+                                             long long pix, int cbase, const float* s_scale, const float* s_shift) {
+    TY* const yrow = reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co;
+    const TY* const rrow = RES ? reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co : nullptr;
+    uint32_t acc0[16], acc1[16];
+    int ci = half;
+    if (ci < nch) tc_ld16(t_row + (uint32_t)(ci << 4), acc0);
+    while (ci < nch) {
+        tc_ld_wait();
+        const int cn = ci + EPI_WARPS / 4;
+        if (cn < nch) tc_ld16(t_row + (uint32_t)(cn << 4), acc1);
+        if (valid) {
+            const int c0l = ci << 4, c = cbase + c0l;
+            if (c < p.cout_p) epilogue_store8<TY, ACT, RES>(p, yrow, rrow, c, c0l, acc0, s_scale, s_shift);
+            if (c + 8 < p.cout_p) epilogue_store8<TY, ACT, RES>(p, yrow, rrow, c + 8, c0l + 8, acc0 + 8, s_scale, s_shift);
+        }
+        if (cn >= nch) break;
+        tc_ld_wait();
+        ci = cn + EPI_WARPS / 4;
+        if (ci < nch) tc_ld16(t_row + (uint32_t)(ci << 4), acc0);
+        if (valid) {
+            const int c0l = cn << 4, c = cbase + c0l;
+            if (c < p.cout_p) epilogue_store8<TY, ACT, RES>(p, yrow, rrow, c, c0l, acc1, s_scale, s_shift);
+            if (c + 8 < p.cout_p) epilogue_store8<TY, ACT, RES>(p, yrow, rrow, c + 8, c0l + 8, acc1 + 8, s_scale, s_shift);
+        }
+    }
 }
 
 // Epilogue of the operand-swapped mode: TMEM lane = [tap slot j][output channel], column = pixel of the window.
@@ -187,7 +212,7 @@ __device__ __forceinline__ void epilogue_store16(const UmmaParams& p, long long 
 constexpr int STG_PITCH = 132;               // floats per staged window position (128 lanes + 4: no bank conflicts)
 constexpr int STG_FLOATS = 16 * STG_PITCH;
 
-template <typename TY>
+template <typename TY, int ACT, bool RES>
 __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const TileCoord& t, uint32_t t_base, int quarter,
                                                  int half, int lane, int tid_h, float* s_stage, const float* s_scale,
                                                  const float* s_shift) {
@@ -231,20 +256,15 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
             float v[8];
             v[0] = fmaf(lo.x, s0.x, f0.x); v[1] = fmaf(lo.y, s0.y, f0.y); v[2] = fmaf(lo.z, s0.z, f0.z); v[3] = fmaf(lo.w, s0.w, f0.w);
             v[4] = fmaf(hi.x, s1.x, f1.x); v[5] = fmaf(hi.y, s1.y, f1.y); v[6] = fmaf(hi.z, s1.z, f1.z); v[7] = fmaf(hi.w, s1.w, f1.w);
-            if (p.res) {
+            if (RES) {
                 float rs[8];
                 load8<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co + c, rs);
 #pragma unroll
                 for (int q = 0; q < 8; ++q) v[q] += rs[q];
             }
-            if (c < p.act_c_end && p.act != EDE_ACT_NONE) {
-                if (p.act == EDE_ACT_RELU) {
+            if (ACT != EDE_ACT_NONE && c < p.act_c_end) {
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) v[q] = fmaxf(v[q], 0.f);
-                } else {
-#pragma unroll
-                    for (int q = 0; q < 8; ++q) v[q] = apply_act(v[q], p.act);
-                }
+                for (int q = 0; q < 8; ++q) v[q] = ACT == ACT_RUNTIME ? apply_act(v[q], p.act) : act_ct<ACT>(v[q]);
             }
             store8<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co + c, v);
         }
@@ -254,6 +274,7 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
 // Persistent, warp-specialised implicit-GEMM convolution.  One CTA per SM walks the tile list
 // (tile = n-tile x image x output patch) with a static stride; TMEM holds TWO accumulator stages so the
 // epilogue of tile i overlaps the MMAs of tile i+1; the operand rings run on across tile boundaries.
+template <typename TY, int ACT, bool RES>
 __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_constant__ UmmaParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -462,9 +483,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                 float* const s_stage = s_shift + 256 + half * (2 * STG_FLOATS);
                 const int tid_h = (warp - 2 - 4 * half) * 32 + lane;
                 const uint32_t t_col = t_base;
-                if (p.y_dtype == EDE_BF16) epilogue_swapped<__nv_bfloat16>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift);
-                else if (p.y_dtype == EDE_BF16X2) epilogue_swapped<bf16x2_t>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift);
-                else epilogue_swapped<float>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift);
+                epilogue_swapped<TY, ACT, RES>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift);
             } else {
                 const int nch = p.n_pad >> 4;         // 16-column chunks of one accumulator row (n_pad % 16 == 0)
                 for (int m = 0; m < p.m_tiles; ++m) {
@@ -485,30 +504,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                     const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
                     const uint32_t t_row = t_base + (uint32_t)(m * p.n_pad);
                     const int cbase = t.ntile * p.n_pad;
-                    uint32_t acc0[16], acc1[16];
-                    int ci = half;
-                    if (ci < nch) tc_ld16(t_row + (uint32_t)(ci << 4), acc0);
-                    while (ci < nch) {                // chunk ci in acc0; the next one loads while it is stored
-                        tc_ld_wait();
-                        const int cn = ci + EPI_WARPS / 4;
-                        if (cn < nch) tc_ld16(t_row + (uint32_t)(cn << 4), acc1);
-                        if (valid) {
-                            const int c0l = ci << 4;
-                            if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, cbase + c0l, c0l, acc0, s_scale, s_shift);
-                            else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, cbase + c0l, c0l, acc0, s_scale, s_shift);
-                            else epilogue_store16<float>(p, pix, cbase + c0l, c0l, acc0, s_scale, s_shift);
-                        }
-                        if (cn >= nch) break;
-                        tc_ld_wait();
-                        ci = cn + EPI_WARPS / 4;
-                        if (ci < nch) tc_ld16(t_row + (uint32_t)(ci << 4), acc0);
-                        if (valid) {
-                            const int c0l = cn << 4;
-                            if (p.y_dtype == EDE_BF16) epilogue_store16<__nv_bfloat16>(p, pix, cbase + c0l, c0l, acc1, s_scale, s_shift);
-                            else if (p.y_dtype == EDE_BF16X2) epilogue_store16<bf16x2_t>(p, pix, cbase + c0l, c0l, acc1, s_scale, s_shift);
-                            else epilogue_store16<float>(p, pix, cbase + c0l, c0l, acc1, s_scale, s_shift);
-                        }
-                    }
+                    epilogue_row<TY, ACT, RES>(p, t_row, nch, half, valid, pix, cbase, s_scale, s_shift);
                 }
             }
             tc_fence_before();
@@ -792,6 +788,20 @@ int conv_direct_launch(const EdeConv& a, cudaStream_t st);
 static unsigned long long* g_prof_last = nullptr;
 static size_t g_prof_ctas = 0;
 
+template <typename TY, int ACT, bool RES>
+static int launch_variant(const UmmaParams& p, int n_cta, int smem, int dev, cudaStream_t st) {
+    static bool attr_set[64] = {};
+    if (!attr_set[dev]) {
+        int rc = check_cuda(cudaFuncSetAttribute(conv_umma_kernel<TY, ACT, RES>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024),
+                            "cudaFuncSetAttribute(conv_umma_kernel)");
+        if (rc) return rc;
+        attr_set[dev] = true;
+    }
+    conv_umma_kernel<TY, ACT, RES><<<n_cta, NUM_THREADS, smem, st>>>(p);
+    return EDE_OK;
+}
+
 static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t st) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) {
@@ -874,19 +884,13 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     p.cout_p = a.cout_p; p.act = a.act; p.act_c_end = a.act_c_end; p.y_dtype = a.y_dtype;
 
     static int sm_count[64] = {};
-    static bool smem_attr_set[64] = {};
     int dev = 0;
     (void)cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
-    if (!smem_attr_set[dev]) {
-        int rc = check_cuda(cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 227 * 1024),
-                            "cudaFuncSetAttribute(conv_umma_kernel)");
+    if (sm_count[dev] == 0) {
+        int rc = check_cuda(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev),
+                            "cudaDeviceGetAttribute(MultiProcessorCount)");
         if (rc) return rc;
-        rc = check_cuda(cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev),
-                        "cudaDeviceGetAttribute(MultiProcessorCount)");
-        if (rc) return rc;
-        smem_attr_set[dev] = true;
     }
     // persistent grid: one CTA per SM (the dynamic smem request is kept above half an SM so that two CTAs
     // can never share one SM and fight over the 512 TMEM columns)
@@ -901,7 +905,24 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
         g_prof_ctas = p.prof ? (size_t)n_cta : 0;
     }
     const int smem = std::max(c.smem_bytes, 120 * 1024);
-    conv_umma_kernel<<<n_cta, NUM_THREADS, smem, st>>>(p);
+    // one kernel instantiation per (output dtype, activation, residual): the epilogue has no per-element branches
+    int rc = EDE_OK;
+#define EDE_UMMA_LAUNCH(TY, ACT, RES) rc = launch_variant<TY, ACT, RES>(p, n_cta, smem, dev, st)
+#define EDE_UMMA_ACT(TY, ACT) do { if (a.res) EDE_UMMA_LAUNCH(TY, ACT, true); else EDE_UMMA_LAUNCH(TY, ACT, false); } while (0)
+#define EDE_UMMA_TY(TY)                                                      \
+    do {                                                                     \
+        if (a.act == EDE_ACT_NONE) EDE_UMMA_ACT(TY, EDE_ACT_NONE);           \
+        else if (a.act == EDE_ACT_RELU) EDE_UMMA_ACT(TY, EDE_ACT_RELU);      \
+        else if (a.act == EDE_ACT_SWISH) EDE_UMMA_ACT(TY, EDE_ACT_SWISH);    \
+        else EDE_UMMA_ACT(TY, ACT_RUNTIME);                                  \
+    } while (0)
+    if (a.y_dtype == EDE_BF16) EDE_UMMA_TY(__nv_bfloat16);
+    else if (a.y_dtype == EDE_BF16X2) EDE_UMMA_TY(bf16x2_t);
+    else EDE_UMMA_TY(float);
+#undef EDE_UMMA_TY
+#undef EDE_UMMA_ACT
+#undef EDE_UMMA_LAUNCH
+    if (rc) return rc;
     EDE_LAUNCH_CHECK("conv_umma_kernel");
     return EDE_OK;
 }
