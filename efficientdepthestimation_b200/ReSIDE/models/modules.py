@@ -18,7 +18,8 @@ from ...engine import EdeModule, cat_views, emit
 
 
 _LOWRES_UPCONV = os.environ.get("EDE_LOWRES_UPCONV", "1") != "0"
-_LOWRES_MIN_CIN = int(os.environ.get("EDE_LOWRES_MIN_CIN", "192"))
+_LOWRES_MIN_CIN = int(os.environ.get("EDE_LOWRES_MIN_CIN", "192"))        # for moderate upsampling (4x in area)
+_LOWRES_MIN_CIN_BIG = int(os.environ.get("EDE_LOWRES_MIN_CIN_BIG", "32"))  # for >= 8x in area: z is tiny
 
 
 class _UpProjection(EdeModule, nn.Sequential):
@@ -37,9 +38,10 @@ class _UpProjection(EdeModule, nn.Sequential):
         parts = [(self.conv1.weight, self.bn1, None, True), (self.conv2.weight, self.bn2, None, False)]
         grow = (int(size[0]) * int(size[1])) / float(x.h * x.w)
         if (_LOWRES_UPCONV and g.precision != "fp32" and grow >= 3.0 and 2 * self.conv1.out_channels <= 64
-                and x.c >= _LOWRES_MIN_CIN):
-            # narrow projection of a wide, strongly upsampled map (MFF): contract Cin on the low-resolution grid.
-            # Below ~192 input channels the 25-tap gather on the CUDA cores costs more than the direct conv.
+                and x.c >= (_LOWRES_MIN_CIN_BIG if grow >= 8.0 else _LOWRES_MIN_CIN)):
+            # narrow projection of a strongly upsampled map (MFF): contract Cin on the low-resolution grid, then
+            # gather the taps separably.  The intermediate z has 25*32 fp32 lanes per LOW-resolution pixel, so for
+            # a mere 2x2 upsampling it only pays when Cin is large; from 8x in area on it is always smaller.
             pair = g.upconv(x, size, parts, (2, 2, 2, 2), A.ACT_RELU, tag=tag + ".conv1+conv2")
         else:
             x = g.resize(x, size, tag=tag + ".resize")

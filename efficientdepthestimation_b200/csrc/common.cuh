@@ -135,6 +135,41 @@ template <> __device__ __forceinline__ void store8<bf16x2_t>(bf16x2_t* p, const 
     stg256(p, u);
 }
 
+// 4 consecutive channels (c % 4 == 0) of one pixel row `p` (lane 0 of the row, 32-byte aligned)
+template <typename T> __device__ __forceinline__ void load4(const T* p, int c, float (&v)[4]);
+template <typename T> __device__ __forceinline__ void store4(T* p, int c, const float (&v)[4]);
+template <> __device__ __forceinline__ void load4<float>(const float* p, int c, float (&v)[4]) {
+    const float4 a = *reinterpret_cast<const float4*>(p + c);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+template <> __device__ __forceinline__ void store4<float>(float* p, int c, const float (&v)[4]) {
+    *reinterpret_cast<float4*>(p + c) = make_float4(v[0], v[1], v[2], v[3]);
+}
+template <> __device__ __forceinline__ void load4<__nv_bfloat16>(const __nv_bfloat16* p, int c, float (&v)[4]) {
+    const uint2 u = *reinterpret_cast<const uint2*>(p + c);
+    v[0] = bf16lo_f(u.x); v[1] = bf16hi_f(u.x); v[2] = bf16lo_f(u.y); v[3] = bf16hi_f(u.y);
+}
+template <> __device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, int c, const float (&v)[4]) {
+    const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+    *reinterpret_cast<uint2*>(p + c) = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+// split bf16: group of 8 lanes = [8 x hi][8 x lo]; lanes c..c+3 are 8 bytes in each half
+template <> __device__ __forceinline__ void load4<bf16x2_t>(const bf16x2_t* p, int c, float (&v)[4]) {
+    const uint2* g = reinterpret_cast<const uint2*>(p + (c & ~7)) + ((c & 7) >> 2);
+    const uint2 h = g[0], l = g[2];
+    v[0] = bf16lo_f(h.x) + bf16lo_f(l.x); v[1] = bf16hi_f(h.x) + bf16hi_f(l.x);
+    v[2] = bf16lo_f(h.y) + bf16lo_f(l.y); v[3] = bf16hi_f(h.y) + bf16hi_f(l.y);
+}
+template <> __device__ __forceinline__ void store4<bf16x2_t>(bf16x2_t* p, int c, const float (&v)[4]) {
+    uint2* g = reinterpret_cast<uint2*>(p + (c & ~7)) + ((c & 7) >> 2);
+    const __nv_bfloat162 a = __floats2bfloat162_rn(v[0], v[1]), b = __floats2bfloat162_rn(v[2], v[3]);
+    const uint32_t ua = *reinterpret_cast<const uint32_t*>(&a), ub = *reinterpret_cast<const uint32_t*>(&b);
+    const __nv_bfloat162 la = __floats2bfloat162_rn(v[0] - bf16lo_f(ua), v[1] - bf16hi_f(ua));
+    const __nv_bfloat162 lb = __floats2bfloat162_rn(v[2] - bf16lo_f(ub), v[3] - bf16hi_f(ub));
+    g[0] = make_uint2(ua, ub);
+    g[2] = make_uint2(*reinterpret_cast<const uint32_t*>(&la), *reinterpret_cast<const uint32_t*>(&lb));
+}
+
 template <typename T> __device__ __forceinline__ float round_as(float v);
 template <> __device__ __forceinline__ float round_as<float>(float v) { return v; }
 template <> __device__ __forceinline__ float round_as<__nv_bfloat16>(float v) {

@@ -75,7 +75,7 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 __device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------ kernel parameters
-constexpr int MAX_STAGES = 8;
+constexpr int MAX_STAGES = 12;
 constexpr int EPI_WARPS = 8;                 // two warps per TMEM lane quarter, interleaved over 16-column chunks
 constexpr int EPI_THREADS = 32 * EPI_WARPS;
 constexpr int NUM_THREADS = 64 + EPI_THREADS;   // warp 0 TMA, warp 1 MMA, warps 2.. epilogue
@@ -217,56 +217,66 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
                                                  int half, int lane, int tid_h, float* s_stage, const float* s_scale,
                                                  const float* s_shift) {
     const int wrap = p.a_mode == 0 ? p.pitch : p.bw;
+    const uint32_t wrap_inv = 65536u / (uint32_t)wrap + 1u;   // f / wrap for f < 256 (one correction step below)
     const int cg = 128 / p.pack_g;                           // channels per tap slot (32 / 64 / 128)
     const int j = (quarter * 32) / cg;                       // tap slot of this warp's 32 lanes
     const bool live = quarter * 32 - j * cg < p.cout_p;      // do these lanes hold real output channels?
     const int r = quarter * 32 + lane;
-    const int groups = cg >> 3, pairs = 16 * groups;
-    int it = 0;
-    for (int c0 = half * 16; c0 < p.n_cols; c0 += 16 * (EPI_WARPS / 4), ++it) {
-        float* const buf = s_stage + (it & 1) * STG_FLOATS;
-        if (live) {
-            uint32_t acc[16];
-            tc_ld16(t_base + (uint32_t)(c0 + j), acc);
-            tc_ld_wait();
+    const int upp = cg >> 2;                                 // 4-channel units per staged position: 8 / 16 / 32
+    const int upp_lg = 31 - __clz(upp);
+    const int upt = (16 * upp) >> 7;                         // units per thread and chunk: 1 / 2 / 4
+    const int step = 16 * (EPI_WARPS / 4);
+    uint32_t acc[16];
+    if (live) {                                              // chunk 0 -> staging tile 0
+        tc_ld16(t_base + (uint32_t)(half * 16 + j), acc);
+        tc_ld_wait();
 #pragma unroll
-            for (int k = 0; k < 16; ++k) buf[k * STG_PITCH + r] = __uint_as_float(acc[k]);
-        }
-        asm volatile("bar.sync %0, 128;" ::"r"(2 + half) : "memory");
-        for (int i = tid_h; i < pairs; i += 128) {
-            const int pj = i / groups, c = (i - pj * groups) << 3;
+        for (int k = 0; k < 16; ++k) s_stage[k * STG_PITCH + r] = __uint_as_float(acc[k]);
+    }
+    int it = 0;
+    for (int c0 = half * 16; c0 < p.n_cols; c0 += step, ++it) {
+        const float* const buf = s_stage + (it & 1) * STG_FLOATS;
+        const bool next = live && c0 + step < p.n_cols;
+        if (next) tc_ld16(t_base + (uint32_t)(c0 + step + j), acc);      // in flight across the barrier and phase 2
+        if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
+        else asm volatile("bar.sync 3, 128;" ::: "memory");
+        for (int k = 0; k < upt; ++k) {
+            const int u = tid_h + (k << 7);
+            const int pj = u >> upp_lg, c = (u & (upp - 1)) << 2;
             if (c >= p.cout_p) continue;
-            const int f = c0 + pj;                           // window position -> output pixel
-            int fr, fc, owb;
-            if (p.a_mode == 0) { fr = f / wrap; fc = f - fr * wrap; owb = t.ow0; }
-            else { const int m = f >> 7, rr = f & 127; fr = rr / wrap; fc = rr - fr * wrap; owb = t.ow0 + m * p.bw; }
+            int f = c0 + pj, owb = t.ow0;                    // window position -> output pixel
+            if (p.a_mode != 0) { owb += (f >> 7) * p.bw; f &= 127; }
+            int fr = (int)(((uint32_t)f * wrap_inv) >> 16);
+            if (fr * wrap > f) --fr;
+            const int fc = f - fr * wrap;
             const int oh = t.oh0 + fr, ow = owb + fc;
             if (!(fc < p.bw && fr < p.bh && oh < p.oh && ow < p.ow)) continue;
             const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
             const float* src = buf + pj * STG_PITCH + c;
-            float4 lo = *reinterpret_cast<const float4*>(src), hi = *reinterpret_cast<const float4*>(src + 4);
+            float4 a4 = *reinterpret_cast<const float4*>(src);
             for (int jj = 1; jj < p.pack_g; ++jj) {
-                const float4 l2 = *reinterpret_cast<const float4*>(src + jj * cg);
-                const float4 h2 = *reinterpret_cast<const float4*>(src + jj * cg + 4);
-                lo.x += l2.x; lo.y += l2.y; lo.z += l2.z; lo.w += l2.w;
-                hi.x += h2.x; hi.y += h2.y; hi.z += h2.z; hi.w += h2.w;
+                const float4 b4 = *reinterpret_cast<const float4*>(src + jj * cg);
+                a4.x += b4.x; a4.y += b4.y; a4.z += b4.z; a4.w += b4.w;
             }
-            const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c), s1 = *reinterpret_cast<const float4*>(s_scale + c + 4);
-            const float4 f0 = *reinterpret_cast<const float4*>(s_shift + c), f1 = *reinterpret_cast<const float4*>(s_shift + c + 4);
-            float v[8];
-            v[0] = fmaf(lo.x, s0.x, f0.x); v[1] = fmaf(lo.y, s0.y, f0.y); v[2] = fmaf(lo.z, s0.z, f0.z); v[3] = fmaf(lo.w, s0.w, f0.w);
-            v[4] = fmaf(hi.x, s1.x, f1.x); v[5] = fmaf(hi.y, s1.y, f1.y); v[6] = fmaf(hi.z, s1.z, f1.z); v[7] = fmaf(hi.w, s1.w, f1.w);
+            const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c), f0 = *reinterpret_cast<const float4*>(s_shift + c);
+            float v[4] = {fmaf(a4.x, s0.x, f0.x), fmaf(a4.y, s0.y, f0.y), fmaf(a4.z, s0.z, f0.z), fmaf(a4.w, s0.w, f0.w)};
             if (RES) {
-                float rs[8];
-                load8<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co + c, rs);
+                float rs[4];
+                load4<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co, c, rs);
 #pragma unroll
-                for (int q = 0; q < 8; ++q) v[q] += rs[q];
+                for (int q = 0; q < 4; ++q) v[q] += rs[q];
             }
-            if (ACT != EDE_ACT_NONE && c < p.act_c_end) {
+            if (ACT != EDE_ACT_NONE && c < p.act_c_end) {    // act_c_end is a multiple of 8
 #pragma unroll
-                for (int q = 0; q < 8; ++q) v[q] = ACT == ACT_RUNTIME ? apply_act(v[q], p.act) : act_ct<ACT>(v[q]);
+                for (int q = 0; q < 4; ++q) v[q] = ACT == ACT_RUNTIME ? apply_act(v[q], p.act) : act_ct<ACT>(v[q]);
             }
-            store8<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co + c, v);
+            store4<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co, c, v);
+        }
+        if (next) {                                          // chunk it+1 -> the other staging tile (its readers of
+            tc_ld_wait();                                    // chunk it-1 all passed this iteration's barrier)
+            float* const nb = s_stage + ((it + 1) & 1) * STG_FLOATS;
+#pragma unroll
+            for (int k = 0; k < 16; ++k) nb[k * STG_PITCH + r] = __uint_as_float(acc[k]);
         }
     }
 }
@@ -707,7 +717,10 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
             const int steps = a.kh * kws * a.w_passes;
             const int n_cols = G > 1 ? 240 : 256;
             const int ck = 64, ck_bytes = 128, n_chunks = ceil_div(a.cin_p, ck);
-            const int b_bytes = 128 * ck_bytes;
+            // unpacked: the TMA box stops at the real output channels; the MMA still reads 128 rows, the rows past
+            // the box are stale smem that lands in accumulator lanes nobody reads (each lane is independent)
+            const int w_rows_box = G > 1 ? 128 : std::min(128, round_up(a.cout_p, 8));
+            const int b_bytes = round_up(w_rows_box * ck_bytes, 1024);
             const double t_mma = n_cols * 0.5 * F_SWAP;
             auto consider = [&](const EdeUmmaCfg& cand, double a_bytes_tile) {
                 const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img;
@@ -847,7 +860,8 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
         cuuint64_t dims[3] = {(cuuint64_t)std::min(a.cin_p, a.w_umma_cin_p), (cuuint64_t)a.w_umma_cout_p,
                               (cuuint64_t)(a.kh * a.kw * a.w_passes)};
         cuuint64_t strides[2] = {(cuuint64_t)a.w_umma_cin_p * 2, (cuuint64_t)a.w_umma_cin_p * 2 * a.w_umma_cout_p};
-        cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)(c.swap ? 128 : c.n_pad), 1};
+        const int w_rows_box = c.swap ? (c.pack_g > 1 ? 128 : std::min(128, round_up(a.cout_p, 8))) : c.n_pad;
+        cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)w_rows_box, 1};
         dims[2] = (cuuint64_t)(a.kh * ceil_div(a.kw, c.pack_g) * a.w_passes);
         cuuint32_t es[3] = {1, 1, 1};
         CUresult r = enc(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, (void*)a.w_umma, dims, strides, box, es,
@@ -871,7 +885,7 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     p.bw = c.bw; p.bh = c.bh; p.pitch = c.pitch; p.box_bytes = c.pitch * c.box_rows * c.ck * 2;
     p.m_tiles = c.m_tiles; p.n_pad = c.n_pad;
     p.a_stages = c.a_stages; p.b_stages = c.b_stages;
-    p.a_stage_bytes = c.a_stage_bytes; p.b_stage_bytes = c.b_stage_bytes; p.b_tx_bytes = (c.swap ? 128 : c.n_pad) * c.ck * 2;
+    p.a_stage_bytes = c.a_stage_bytes; p.b_stage_bytes = c.b_stage_bytes; p.b_tx_bytes = (c.swap ? (c.pack_g > 1 ? 128 : std::min(128, round_up(a.cout_p, 8))) : c.n_pad) * c.ck * 2;
     p.layout_type = c.swizzle == 128 ? 2 : c.swizzle == 64 ? 4 : 6;
     p.sbo_bytes = 8 * c.ck * 2;
     p.tmem_cols = c.tmem_cols;

@@ -75,6 +75,90 @@ __global__ void __launch_bounds__(256) upconv_taps_kernel(const EdeUpConv a, flo
     }
 }
 
+// ---- separable form (used when the caller provides the `rows` workspace): bilinear interpolation is a lerp
+// along x followed by a lerp along y, and the zero-padding mask of a tap is a product of an x and a y mask, so
+//   rows[n][y][ty][px][c] = sum_tx inside_x(px+tx-pl) * lerp_x(z[n][y][.][(ty,tx),c], px+tx-pl)      (pass 1)
+//   y[n][py][px][c]       = act(scale * sum_ty inside_y(py+ty-pt) * lerp_y(rows[n][.][ty][px][c], py+ty-pt) + shift)
+// Pass 1 runs on the h low-resolution rows only; pass 2 reads 2*K vectors per output instead of 4*K*K.
+template <int K>
+__global__ void __launch_bounds__(256) upconv_rows_kernel(const EdeUpConv a, float scale_w) {
+    const int ngrp = a.cgrp >> 3;
+    const long long total = (long long)a.n * a.h * K * a.ow * ngrp;
+    const float* __restrict__ z = a.z;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % ngrp) << 3;
+        long long r = i / ngrp;
+        const int px = (int)(r % a.ow);
+        r /= a.ow;
+        const int ty = (int)(r % K);
+        const long long ny = r / K;                          // n * h + y
+        const float* zrow = z + ny * a.w * (long long)a.z_cs + a.z_co + (long long)ty * K * a.cgrp + c;
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int tx = 0; tx < K; ++tx) {
+            const int qx = px + tx - a.pl;
+            if (qx < 0 || qx >= a.ow) continue;              // tap column in the zero padding
+            const float sx = scale_w * qx;
+            const int x0 = (int)sx, x1 = x0 + (x0 < a.w - 1 ? 1 : 0);
+            const float lx = sx - x0, hx = 1.f - lx;
+            float v0[8], v1[8];
+            load8<float>(zrow + (long long)x0 * a.z_cs + tx * a.cgrp, v0);
+            load8<float>(zrow + (long long)x1 * a.z_cs + tx * a.cgrp, v1);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = fmaf(hx, v0[j], fmaf(lx, v1[j], acc[j]));
+        }
+        float* dst = a.rows + i * 8;                         // [n*h + y][ty][px][cgrp] is exactly the thread order
+        *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    }
+}
+
+template <int K, typename TY>
+__global__ void __launch_bounds__(256) upconv_cols_kernel(const EdeUpConv a, float scale_h) {
+    const int ngrp = a.cgrp >> 3;
+    const long long total = (long long)a.n * a.oh * a.ow * ngrp;
+    const float* __restrict__ rows = a.rows;
+    const long long ty_stride = (long long)a.ow * a.cgrp, y_stride = ty_stride * K;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(i % ngrp) << 3;
+        long long pix = i / ngrp;
+        const int ox = (int)(pix % a.ow);
+        pix /= a.ow;
+        const int oy = (int)(pix % a.oh);
+        const int n = (int)(pix / a.oh);
+        const float* base = rows + (long long)n * a.h * y_stride + (long long)ox * a.cgrp + c;
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int ty = 0; ty < K; ++ty) {
+            const int qy = oy + ty - a.pt;
+            if (qy < 0 || qy >= a.oh) continue;              // tap row in the zero padding
+            const float sy = scale_h * qy;
+            const int y0 = (int)sy, y1 = y0 + (y0 < a.h - 1 ? 1 : 0);
+            const float ly = sy - y0, hy = 1.f - ly;
+            float v0[8], v1[8];
+            load8<float>(base + y0 * y_stride + ty * ty_stride, v0);
+            load8<float>(base + y1 * y_stride + ty * ty_stride, v1);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] = fmaf(hy, v0[j], fmaf(ly, v1[j], acc[j]));
+        }
+        float sc[8], sf[8];
+        load8<float>(a.scale + c, sc);
+        load8<float>(a.shift + c, sf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            acc[j] = fmaf(acc[j], sc[j], sf[j]);
+            if (c < a.act_c_end) acc[j] = apply_act(acc[j], a.act);
+        }
+        store8<TY>(reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oy) * a.ow + ox) * a.y_cs + a.y_co + c, acc);
+    }
+}
+
 }  // namespace ede
 
 using namespace ede;
@@ -91,6 +175,21 @@ extern "C" int ede_upconv_taps(const EdeUpConv* a, void* stream) {
     long long g = (total + 255) / 256;
     if (g > 148LL * 64) g = 148LL * 64;
     cudaStream_t st = (cudaStream_t)stream;
+    if (a->rows) {                                           // separable two-pass form
+        const long long total1 = (long long)a->n * a->h * a->kh * a->ow * (a->cgrp >> 3);
+        long long g1 = (total1 + 255) / 256;
+        if (g1 > 148LL * 64) g1 = 148LL * 64;
+        if (a->kh == 5) upconv_rows_kernel<5><<<(unsigned)g1, 256, 0, st>>>(*a, sw);
+        else upconv_rows_kernel<3><<<(unsigned)g1, 256, 0, st>>>(*a, sw);
+        EDE_LAUNCH_CHECK("upconv_rows_kernel");
+        if (a->kh == 5) {
+            EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<5, TY><<<(unsigned)g, 256, 0, st>>>(*a, sh)));
+        } else {
+            EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<3, TY><<<(unsigned)g, 256, 0, st>>>(*a, sh)));
+        }
+        EDE_LAUNCH_CHECK("upconv_cols_kernel");
+        return EDE_OK;
+    }
     if (a->kh == 5) {
         EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_taps_kernel<5, TY><<<(unsigned)g, 256, 0, st>>>(*a, sh, sw)));
     } else {

@@ -135,9 +135,11 @@ int ede_resize_planes_f32(const float* x, float* y, int64_t planes, int32_t h, i
  *   (ReSIDE/models/modules.py:34-37) where the projection is narrow (MFF, modules.py:259-263).
  * z: fp32 NHWC [n,h,w], lanes [(ty*kw+tx)*cgrp + c] = (W_tap x)[c], produced by ede_conv2d as a 1x1 GEMM.
  *   y[n,oy,ox,c] = act_c( scale[c] * sum_taps inside(oy+ty-pt, ox+tx-pl) * bilinear_ac(z[.., tap, c])(oy+ty-pt, ox+tx-pl)
- *                         + shift[c] ),  act applied to lanes c < act_c_end. */
+ *                         + shift[c] ),  act applied to lanes c < act_c_end.
+ * rows: optional fp32 workspace [n][h][kh][ow][cgrp]; when given the gather runs in its separable form (x-lerp of
+ *   every tap on the h low-resolution rows into `rows`, then the y-lerp), NULL = one-pass 4-corner gather. */
 typedef struct EdeUpConv {
-    const float* z; void* y; const float* scale; const float* shift;
+    const float* z; void* y; const float* scale; const float* shift; float* rows;
     int32_t n, h, w, z_cs, z_co, oh, ow, cgrp, y_cs, y_co, y_dtype;
     int32_t kh, kw, pt, pl, act, act_c_end;
 } EdeUpConv;
