@@ -341,129 +341,129 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_addr) : "r"(tmem_slot) : "memory");
 
     if (warp == 0) {
-        // ===================== TMA producer (whole warp walks the loop, one elected lane issues) ==========
-        int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0;
-        const int ck = p.ck_bytes >> 1;
-        const int a_mode = p.a_mode, n_chunks = p.n_chunks, m_tiles = p.m_tiles, kw = p.kw_steps;
-        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-            const TileCoord t = decode_tile(p, tile);
-            for (int chunk = 0; chunk < n_chunks; ++chunk) {
-                if (a_mode == 0) {
-                    mbar_wait(a_empty(a_st), a_ph ^ 1);
-                    if (elect_one()) {
-                        mbar_expect_tx(a_full(a_st), (uint32_t)p.box_bytes);
-                        tma_load_4d(a_base + a_st * p.a_stage_bytes, &p.tm_a, a_full(a_st), chunk * ck, t.ow0 - p.pl,
-                                    t.oh0 - p.pt, t.img);
-                    }
-                    if (++a_st == p.a_stages) { a_st = 0; a_ph ^= 1; }
-                }
-                int ky = 0, kx = 0;
-                for (int tap = 0; tap < taps; ++tap) {
-                    if (tap == sp_taps) { ky = 0; kx = 0; }
-                    if (a_mode != 0) {
+        // ===================== TMA producer: ONE thread walks the loop (no warp-collective ops on the hot path)
+        if (lane == 0) {
+            int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0;
+            const int ck = p.ck_bytes >> 1;
+            const int a_mode = p.a_mode, n_chunks = p.n_chunks, m_tiles = p.m_tiles, kws = p.kw_steps;
+            const int a_stages = p.a_stages, b_stages = p.b_stages;
+            const uint32_t a_stage_bytes = (uint32_t)p.a_stage_bytes, b_stage_bytes = (uint32_t)p.b_stage_bytes;
+            const uint32_t box_bytes = (uint32_t)p.box_bytes, b_tx = (uint32_t)p.b_tx_bytes;
+            const uint32_t a_tx = (uint32_t)(m_tiles * 128 * p.ck_bytes), m_bytes = (uint32_t)(128 * p.ck_bytes);
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const TileCoord t = decode_tile(p, tile);
+                const int wrow = t.ntile * p.n_pad;
+                for (int chunk = 0; chunk < n_chunks; ++chunk) {
+                    const int cch = chunk * ck;
+                    if (a_mode == 0) {
                         mbar_wait(a_empty(a_st), a_ph ^ 1);
-                        if (elect_one()) {
-                            mbar_expect_tx(a_full(a_st), (uint32_t)(m_tiles * 128 * p.ck_bytes));
+                        mbar_expect_tx(a_full(a_st), box_bytes);
+                        tma_load_4d(a_base + a_st * a_stage_bytes, &p.tm_a, a_full(a_st), cch, t.ow0 - p.pl,
+                                    t.oh0 - p.pt, t.img);
+                        if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; }
+                    }
+                    int ky = 0, kx = 0;
+                    for (int tap = 0; tap < taps; ++tap) {
+                        if (a_mode != 0) {
+                            if (tap == sp_taps) { ky = 0; kx = 0; }
+                            mbar_wait(a_empty(a_st), a_ph ^ 1);
+                            mbar_expect_tx(a_full(a_st), a_tx);
                             for (int m = 0; m < m_tiles; ++m)
-                                tma_load_4d(a_base + a_st * p.a_stage_bytes + m * 128 * p.ck_bytes, &p.tm_a,
-                                            a_full(a_st), chunk * ck, (t.ow0 + m * p.bw) * p.sw - p.pl + kx,
-                                            t.oh0 * p.sh - p.pt + ky, t.img);
+                                tma_load_4d(a_base + a_st * a_stage_bytes + m * m_bytes, &p.tm_a, a_full(a_st), cch,
+                                            (t.ow0 + m * p.bw) * p.sw - p.pl + kx, t.oh0 * p.sh - p.pt + ky, t.img);
+                            if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; }
+                            if (++kx == kws) { kx = 0; ++ky; }
                         }
-                        if (++a_st == p.a_stages) { a_st = 0; a_ph ^= 1; }
+                        mbar_wait(b_empty(b_st), b_ph ^ 1);
+                        mbar_expect_tx(b_full(b_st), b_tx);
+                        tma_load_3d(b_base + b_st * b_stage_bytes, &p.tm_b, b_full(b_st), cch, wrow, tap);
+                        if (++b_st == b_stages) { b_st = 0; b_ph ^= 1; }
                     }
-                    mbar_wait(b_empty(b_st), b_ph ^ 1);
-                    if (elect_one()) {
-                        mbar_expect_tx(b_full(b_st), (uint32_t)p.b_tx_bytes);
-                        tma_load_3d(b_base + b_st * p.b_stage_bytes, &p.tm_b, b_full(b_st), chunk * ck,
-                                    t.ntile * p.n_pad, tap);
-                    }
-                    if (++b_st == p.b_stages) { b_st = 0; b_ph ^= 1; }
-                    if (++kx == kw) { kx = 0; ++ky; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================== MMA issuer (warp-uniform loop state, one elected lane issues) ==============
-        const int a_mode = p.a_mode, m_tiles = p.m_tiles, n_pad = p.n_pad, n_chunks = p.n_chunks, swap = p.swap;
-        const int a_stages = p.a_stages, b_stages = p.b_stages, kw = p.kw_steps, pitch = p.pitch, pack_g = p.pack_g;
-        const uint32_t ck16 = (uint32_t)p.ck_bytes >> 4;            // (bytes >> 4) units of the address field
-        const uint32_t a_stage16 = (uint32_t)p.a_stage_bytes >> 4, b_stage16 = (uint32_t)p.b_stage_bytes >> 4;
-        const uint32_t m_step16 = 128u * ck16;                       // 128 pixel rows
-        const int ksteps = p.ck_bytes >> 5;                          // 32 bytes of K (16 bf16) per tcgen05.mma
-        const uint32_t idesc = p.idesc;
-        const uint64_t dconst = smem_desc_const(p);
-        const uint32_t desc_hi = (uint32_t)(dconst >> 32);
-        const uint32_t a_base16 = (uint32_t)dconst + (a_base >> 4), b_base16 = (uint32_t)dconst + (b_base >> 4);
-        int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0, acc_st = 0, acc_ph = 0;
-        long long w_ops = 0, w_acc = 0;
-        unsigned long long t_start = 0;
-        if (p.prof) t_start = gtime();
-        for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-            long long c0 = p.prof ? clock64() : 0;
-            mbar_wait(acc_empty(acc_st), acc_ph ^ 1);                // epilogue has drained this accumulator stage
-            tc_fence_after();
-            if (p.prof) w_acc += clock64() - c0;
-            const uint32_t d_base = tmem_addr + (uint32_t)(acc_st * p.acc_cols);
-            uint32_t accum = 0;
-            for (int chunk = 0; chunk < n_chunks; ++chunk) {
-                // K steps that hold real channels: the tail of the last chunk is TMA zero fill, never multiplied
-                const int ks = min(ksteps, (p.k_bytes - chunk * p.ck_bytes + 31) >> 5);
-                if (a_mode == 0) {
-                    c0 = p.prof ? clock64() : 0;
-                    mbar_wait(a_full(a_st), a_ph);
-                    if (p.prof) w_ops += clock64() - c0;
-                }
-                int ky = 0, kx = 0;
-                for (int tap = 0; tap < taps; ++tap) {
-                    c0 = p.prof ? clock64() : 0;
-                    if (a_mode != 0) mbar_wait(a_full(a_st), a_ph);
-                    mbar_wait(b_full(b_st), b_ph);
-                    if (p.prof) w_ops += clock64() - c0;
-                    tc_fence_after();
-                    if (tap == sp_taps) { ky = 0; kx = 0; }
-                    const uint32_t shift16 = a_mode == 0 ? (uint32_t)(ky * pitch + kx * pack_g) * ck16 : 0u;
-                    const uint32_t a0 = a_base16 + (uint32_t)a_st * a_stage16 + shift16;
-                    const uint32_t b0 = b_base16 + (uint32_t)b_st * b_stage16;
-                    if (elect_one()) {
+        // ===================== MMA issuer: ONE thread; per (tap, chunk) step it waits for the operands, issues the
+        // K steps that hold real channels and commits the stage back -- kept to a few dozen instructions because
+        // narrow layers have only 1..2 MMAs (128..256 tensor-pipe cycles) per step
+        if (lane == 0) {
+            const int a_mode = p.a_mode, m_tiles = p.m_tiles, n_pad = p.n_pad, n_chunks = p.n_chunks, swap = p.swap;
+            const int a_stages = p.a_stages, b_stages = p.b_stages, kws = p.kw_steps;
+            const uint32_t ck16 = (uint32_t)p.ck_bytes >> 4;            // (bytes >> 4) units of the address field
+            const uint32_t a_stage16 = (uint32_t)p.a_stage_bytes >> 4, b_stage16 = (uint32_t)p.b_stage_bytes >> 4;
+            const uint32_t m_step16 = 128u * ck16;                       // 128 pixel rows
+            const int ksteps = p.ck_bytes >> 5;                          // 32 bytes of K (16 bf16) per tcgen05.mma
+            const uint32_t idesc = p.idesc;
+            const uint64_t dconst = smem_desc_const(p);
+            const uint32_t desc_hi = (uint32_t)(dconst >> 32);
+            const uint32_t a_base16 = (uint32_t)dconst + (a_base >> 4), b_base16 = (uint32_t)dconst + (b_base >> 4);
+            const uint32_t kx_step16 = a_mode == 0 ? (uint32_t)p.pack_g * ck16 : 0u;       // next tap of a kernel row
+            const uint32_t ky_step16 = a_mode == 0 ? (uint32_t)(p.pitch - kws * p.pack_g) * ck16 : 0u;   // row wrap
+            const int k_bytes = p.k_bytes, ck_bytes = p.ck_bytes;
+            int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0, acc_st = 0, acc_ph = 0;
+            uint32_t a_cur = a_base16, b_cur = b_base16;                 // descriptor low words of the current stages
+            unsigned long long t_start = 0;
+            if (p.prof) t_start = gtime();
+            for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                mbar_wait(acc_empty(acc_st), acc_ph ^ 1);                // epilogue has drained this accumulator stage
+                tc_fence_after();
+                const uint32_t d_base = tmem_addr + (uint32_t)(acc_st * p.acc_cols);
+                uint32_t accum = 0;
+                for (int chunk = 0; chunk < n_chunks; ++chunk) {
+                    // K steps that hold real channels: the tail of the last chunk is TMA zero fill, never multiplied
+                    const int ks = min(ksteps, (k_bytes - chunk * ck_bytes + 31) >> 5);
+                    if (a_mode == 0) mbar_wait(a_full(a_st), a_ph);
+                    uint32_t shift16 = 0;
+                    int kx = 0, tap_in_pass = 0;
+                    for (int tap = 0; tap < taps; ++tap) {
+                        if (a_mode != 0) mbar_wait(a_full(a_st), a_ph);
+                        mbar_wait(b_full(b_st), b_ph);
+                        tc_fence_after();
+                        const uint32_t a0 = a_cur + shift16, b0 = b_cur;
                         if (swap) {
-                            // D[cout lanes][256 pixel columns] += W[128 x 16] . X[256 x 16]^T
+                            // D[cout lanes][pixel columns] += W[128 x 16] . X[n_cols x 16]^T
                             tc_mma_bf16_w(d_base, b0, a0, desc_hi, idesc, accum);
-                            for (int k = 1; k < ks; ++k)
-                                tc_mma_bf16_w(d_base, b0 + 2u * k, a0 + 2u * k, desc_hi, idesc, 1u);
+                            if (ks > 1) tc_mma_bf16_w(d_base, b0 + 2u, a0 + 2u, desc_hi, idesc, 1u);
+                            if (ks > 2) tc_mma_bf16_w(d_base, b0 + 4u, a0 + 4u, desc_hi, idesc, 1u);
+                            if (ks > 3) tc_mma_bf16_w(d_base, b0 + 6u, a0 + 6u, desc_hi, idesc, 1u);
                         } else {
                             uint32_t am = a0, dm = d_base;
                             for (int m = 0; m < m_tiles; ++m) {
                                 tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, accum);
-                                for (int k = 1; k < ks; ++k)
-                                    tc_mma_bf16_w(dm, am + 2u * k, b0 + 2u * k, desc_hi, idesc, 1u);
+                                if (ks > 1) tc_mma_bf16_w(dm, am + 2u, b0 + 2u, desc_hi, idesc, 1u);
+                                if (ks > 2) tc_mma_bf16_w(dm, am + 4u, b0 + 4u, desc_hi, idesc, 1u);
+                                if (ks > 3) tc_mma_bf16_w(dm, am + 6u, b0 + 6u, desc_hi, idesc, 1u);
                                 am += m_step16;
                                 dm += (uint32_t)n_pad;
                             }
                         }
                         tc_commit(b_empty(b_st));
-                        if (a_mode != 0) tc_commit(a_empty(a_st));
+                        accum = 1;
+                        b_cur += b_stage16;
+                        if (++b_st == b_stages) { b_st = 0; b_ph ^= 1; b_cur = b_base16; }
+                        if (a_mode != 0) {
+                            tc_commit(a_empty(a_st));
+                            a_cur += a_stage16;
+                            if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; a_cur = a_base16; }
+                        } else {
+                            shift16 += kx_step16;                        // next tap slot of this kernel row ...
+                            if (++kx == kws) { kx = 0; shift16 += ky_step16; }           // ... or the next row
+                            if (++tap_in_pass == sp_taps) { tap_in_pass = 0; shift16 = 0; kx = 0; }   // w_lo pass
+                        }
                     }
-                    __syncwarp();
-                    accum = 1;
-                    if (++b_st == b_stages) { b_st = 0; b_ph ^= 1; }
-                    if (a_mode != 0) {
-                        if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; }
+                    if (a_mode == 0) {
+                        tc_commit(a_empty(a_st));
+                        a_cur += a_stage16;
+                        if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; a_cur = a_base16; }
                     }
-                    if (++kx == kw) { kx = 0; ++ky; }
                 }
-                if (a_mode == 0) {
-                    if (elect_one()) tc_commit(a_empty(a_st));
-                    __syncwarp();
-                    if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; }
-                }
+                tc_commit(acc_full(acc_st));
+                if (++acc_st == 2) { acc_st = 0; acc_ph ^= 1; }
             }
-            if (elect_one()) tc_commit(acc_full(acc_st));
-            __syncwarp();
-            if (++acc_st == 2) { acc_st = 0; acc_ph ^= 1; }
-        }
-        if (p.prof && lane == 0) {
-            unsigned long long* q = p.prof + (size_t)blockIdx.x * 8;
-            q[1] = t_start; q[2] = gtime(); q[4] = (unsigned long long)w_ops; q[5] = (unsigned long long)w_acc;
+            if (p.prof) {
+                unsigned long long* q = p.prof + (size_t)blockIdx.x * 8;
+                q[1] = t_start; q[2] = gtime(); q[4] = 0; q[5] = 0;
+            }
         }
     } else {
         // ===================== epilogue (warps 2..): TMEM -> BN/residual/activation -> NHWC stores ========
@@ -583,9 +583,17 @@ static double mma_cycles(int swizzle_bytes, int n_pad) {
     const double base = swizzle_bytes == 128 ? 97.0 : swizzle_bytes == 64 ? 154.0 : 214.0;
     return std::max(base, n_pad * 0.5);
 }
-constexpr double L2_BYTES_PER_CLK_PER_SM = 36.0;     // ~5.3 KB/clk chip-wide over 148 SMs
+constexpr double L2_BYTES_PER_CLK_PER_SM = 27.0;     // TMA box bytes (zero fill included) one SM ingests per clock:
+                                                     // 26..28 measured on the decoder convs (ncu, xbar2l1tex tma_ld)
 constexpr double EPI_CYCLES_PER_ROW_COL = 0.012;     // epilogue cost per accumulator element (4 warps)
 constexpr int NUM_SMS_MODEL = 148;
+
+// 32-channel chunks (64-byte swizzle) only when they cut the padded K -- i.e. the TMA bytes -- by at least `gain`:
+// measured, K = 24 / 32 run 1.6x faster with them, K = 64 / 80 slower (the tensor core reads narrow rows slower).
+static bool narrow_pays(int cin_p, double gain) {
+    const int k64 = round_up(cin_p, 64), k32 = round_up(cin_p, 32);
+    return k32 < k64 && (double)(k64 - k32) >= gain * k64;
+}
 
 static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     memset(&c, 0, sizeof(c));
@@ -608,15 +616,16 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     // contention factors on top of the isolated MMA rates (TMA fills and the MMA operand reads share the
     // 128 B/clk of shared-memory bandwidth; measured on the decoder convs with tools/cta_timeline.py)
     const double F_NOSWAP = 1.5, F_SWAP = 1.3;
-    // Channel chunk: always the 128-byte swizzle (64 bf16 channels per smem row) unless forced -- narrower
-    // swizzles feed the tensor core at 63 % / 45 % of the rate (measured, profiles/r01_mma_rate.md; the
-    // operand-swapped N = 256 form loses more), and the MMA issuer skips the K steps of the last chunk
-    // that only hold TMA zero fill, so padding K to 64 costs smem but no tensor-core time.
+    // Channel chunk: the 128-byte swizzle (64 bf16 channels per smem row) or the 64-byte one (32 channels).
+    // Narrower swizzles feed the tensor core at 63 % / 45 % of the rate (profiles/r01_mma_rate.md) and the MMA
+    // issuer skips the K steps of the last chunk that only hold TMA zero fill, so padding K to 64 costs no
+    // tensor-core time -- but TMA ingests the zero fill at the same ~27 B/clk as real bytes, so layers whose K
+    // is far from a multiple of 64 (24, 32, 96 ...) run faster with 32-channel chunks.  The time model decides.
     const int cks[3] = {64, 32, 16};
     const int ks_total = ceil_div(a.cin_p, 16);           // K = 16 steps that hold real channels
     for (int ci = 0; ci < 3; ++ci) {
         const int ck = cks[ci];
-        if (force_ck ? force_ck != ck : ck != 64) continue;
+        if (force_ck ? force_ck != ck : (ck == 16 || (ck == 32 && !narrow_pays(a.cin_p, 0.25)))) continue;
         const int ck_bytes = ck * 2;
         const int n_chunks = ceil_div(a.cin_p, ck);
         for (int n_tiles = ceil_div(n16, 256); n_tiles <= ceil_div(n16, 16) && n_tiles <= 64; ++n_tiles) {
@@ -716,19 +725,21 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
             const int kws = ceil_div(a.kw, G);
             const int steps = a.kh * kws * a.w_passes;
             const int n_cols = G > 1 ? 240 : 256;
-            const int ck = 64, ck_bytes = 128, n_chunks = ceil_div(a.cin_p, ck);
+          for (int cki = 0; cki < 2; ++cki) {
+            const int ck = cks[cki];
+            if (force_ck ? force_ck != ck : (ck == 32 && !narrow_pays(a.cin_p, 0.3))) continue;
+            const int ck_bytes = ck * 2, n_chunks = ceil_div(a.cin_p, ck);
             // unpacked: the TMA box stops at the real output channels; the MMA still reads 128 rows, the rows past
             // the box are stale smem that lands in accumulator lanes nobody reads (each lane is independent)
             const int w_rows_box = G > 1 ? 128 : std::min(128, round_up(a.cout_p, 8));
             const int b_bytes = round_up(w_rows_box * ck_bytes, 1024);
-            const double t_mma = n_cols * 0.5 * F_SWAP;
+            const double t_mma = n_cols * 0.5 * F_SWAP * (ck == 64 ? 1.0 : ck == 32 ? 1.3 : 1.8);
             auto consider = [&](const EdeUmmaCfg& cand, double a_bytes_tile) {
                 const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img;
                 const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
                 const double mma = (double)steps * ks_total * t_mma;
                 const double w_rows = G > 1 ? 128.0 : (double)std::min(128, round_up(a.cout_p, 8));
-                const double mem = (a_bytes_tile + (double)steps * w_rows * std::min(a.cin_p, n_chunks * ck) * 2.0) /
-                                   L2_BYTES_PER_CLK_PER_SM;
+                const double mem = (a_bytes_tile + (double)steps * n_chunks * w_rows * ck_bytes) / L2_BYTES_PER_CLK_PER_SM;
                 const double epi = 16.0 * 220.0 + 600.0;
                 const double per_stage = mma / std::max(1, n_chunks * steps);
                 const double lat = std::max(0.0, 1500.0 - cand.b_stages * per_stage) * 0.15 * n_chunks * steps /
@@ -785,6 +796,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                     }
                 }
             }
+          }
         }
     }
     if (best.m_tiles == 0) return;

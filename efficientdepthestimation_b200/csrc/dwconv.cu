@@ -15,6 +15,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 #include "tma.cuh"
 
@@ -72,23 +74,30 @@ template <> struct Pair<bf16x2_t> {
 };
 
 struct alignas(64) DwParams {
-    CUtensorMap tm_x;      // (64-channel lanes, W, H, N), element = one lane of the dtype
+    CUtensorMap tm_x;      // (channel lanes, W, H, N), element = one lane of the dtype
     EdeDwConv a;
-    int cols;              // output columns (= consumer warps) per block
-    int row_bytes;         // bytes of one ring slot: (cols*S + K - S) pixels x 64 lanes
+    int cols;              // consumer warps per block (each owns 64 / CH adjacent output columns)
+    int row_bytes;         // bytes of one ring slot: (cols * (64/CH) * S + K - S) pixels x CH lanes
+    int tx_bytes;          // bytes one TMA row box delivers (row_bytes before the 128-byte rounding)
+    int zsplit;            // grid.z: a block walks images blockIdx.z, blockIdx.z + zsplit, ...
 };
 
 template <int K> struct DwDepth { static constexpr int value = K >= 5 ? 16 : 8; };   // ring slots (power of 2)
 constexpr int DW_MAX_COLS = 16;
-// consumer warps per block: the 5x5 window + weights need ~170 registers per thread -> 12 warps (384 threads)
+// consumer warps per block: the 5x5 window + weights need ~130 registers per thread -> 12 warps (384 threads)
 template <int K> struct DwCols { static constexpr int value = K >= 5 ? 11 : DW_MAX_COLS; };
 
-template <typename T, int K, int S>
+// CH = channel lanes per block: 64 (lane = channel pair, warp = one output column) or 32 (half-warp = channel
+// pairs, the two halves of a warp own two adjacent output columns) -- the latter when c_p % 64 is in (0, 32],
+// e.g. the 32 / 96 / 144 / 480 / 672-channel stages of EfficientNet-B0, so that no lane idles.
+template <typename T, int K, int S, int CH>
 __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_kernel(const __grid_constant__ DwParams p) {
     constexpr int DEPTH = DwDepth<K>::value;
+    constexpr int SUB = 64 / CH;                           // output columns per warp
+    constexpr int PB = Pair<T>::kPixelBytes * CH / 64;     // bytes of one staged pixel
     extern __shared__ uint8_t smem_raw[];
     __shared__ alignas(8) unsigned long long bars[2 * DEPTH];
-    __shared__ float pool_s[DW_MAX_COLS][64];
+    __shared__ float pool_s[DW_MAX_COLS * 64];             // [column of the tile][CH]
     const EdeDwConv& a = p.a;
     const uint32_t ring = (smem_u32(smem_raw) + 127u) & ~127u;
     const uint8_t* const ring_g = smem_raw + (ring - smem_u32(smem_raw));
@@ -97,11 +106,10 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
     auto empty = [&](int s) { return bar0 + 8u * (DEPTH + s); };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int ow0 = blockIdx.x * p.cols;
-    const int c0 = blockIdx.y * 64;
-    const int n = blockIdx.z;
-    const int n_act = min(p.cols, a.ow - ow0);            // consumer warps that own a real output column
-    const int rows_in = (a.oh - 1) * S + K;               // input rows (incl. padding rows) the walk touches
+    const int ow0 = blockIdx.x * p.cols * SUB;
+    const int c0 = blockIdx.y * CH;
+    const int n_act = min(p.cols, (a.ow - ow0 + SUB - 1) / SUB);   // consumer warps that own a real output column
+    const int rows_in = (a.oh - 1) * S + K;               // input rows (incl. padding rows) one image's walk touches
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < DEPTH; ++s) {
@@ -112,115 +120,126 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
     }
     __syncthreads();
 
-    float2 psum = make_float2(0.f, 0.f);
     if (warp == p.cols) {
-        // ===================== producer: one TMA row per ring slot
-        for (int ir = 0; ir < rows_in; ++ir) {
-            const int slot = ir & (DEPTH - 1);
-            mbar_wait(empty(slot), ((ir / DEPTH) & 1) ^ 1);
-            if (elect_one()) {
-                mbar_expect_tx(full(slot), (uint32_t)p.row_bytes);
-                tma_load_4d(ring + slot * p.row_bytes, &p.tm_x, full(slot), c0, ow0 * S - a.pl, ir - a.pt, n);
-            }
-            __syncwarp();
+        // ===================== producer: one TMA row per ring slot, images back to back
+        if (lane == 0) {
+            int g = 0;                                     // rows issued so far (ring position)
+            for (int n = blockIdx.z; n < a.n; n += p.zsplit)
+                for (int ir = 0; ir < rows_in; ++ir, ++g) {
+                    const int slot = g & (DEPTH - 1);
+                    mbar_wait(empty(slot), ((g / DEPTH) & 1) ^ 1);
+                    mbar_expect_tx(full(slot), (uint32_t)p.tx_bytes);
+                    tma_load_4d(ring + slot * p.row_bytes, &p.tm_x, full(slot), c0, ow0 * S - a.pl, ir - a.pt, n);
+                }
         }
     } else if (warp < n_act) {
         // ===================== consumers
-        const int c = c0 + 2 * lane;
-        const bool c_ok = c < a.c_p;
-        const int cw = c_ok ? c : 0;                       // idle lanes compute on channel 0 and never store
+        const int sub = lane / (CH / 2), cl = lane % (CH / 2);     // column within the warp, channel pair
+        const int c = c0 + 2 * cl;
+        const int col = warp * SUB + sub, ow = ow0 + col;
+        const bool ok = c < a.c_p && ow < a.ow;
+        const int cw = c < a.c_p ? c : 0;                  // idle lanes compute on channel 0 and never store
         float2 w[K * K];
 #pragma unroll
         for (int t = 0; t < K * K; ++t) w[t] = *reinterpret_cast<const float2*>(a.w + (long long)t * a.c_p + cw);
         const float2 sc = *reinterpret_cast<const float2*>(a.scale + cw);
         const float2 sf = *reinterpret_cast<const float2*>(a.shift + cw);
-        const int ow = ow0 + warp;
-        T* const ycol = reinterpret_cast<T*>(a.y) + ((long long)n * a.oh * a.ow + ow) * a.y_cs + a.y_co;
-        const uint8_t* const colbase = ring_g + (size_t)(warp * S) * Pair<T>::kPixelBytes;
-        float2 xw[K][K];                                   // [row slot][kx]
-        auto load_row = [&](int ir, float2 (&row)[K]) {
-            const int slot = ir & (DEPTH - 1);
-            mbar_wait(full(slot), (ir / DEPTH) & 1);
-            const uint8_t* px = colbase + (size_t)slot * p.row_bytes;
+        const uint8_t* const colbase = ring_g + (size_t)(col * S) * PB;
+        const int n_cons = n_act * 32, ctid = threadIdx.x;     // consumer warps are warps 0 .. n_act-1
+        int g = 0;                                         // ring position of the next row this warp loads
+        for (int n = blockIdx.z; n < a.n; n += p.zsplit) {
+            T* const ycol = reinterpret_cast<T*>(a.y) + ((long long)n * a.oh * a.ow + (ok ? ow : 0)) * a.y_cs + a.y_co;
+            float2 psum = make_float2(0.f, 0.f);
+            float2 xw[K][K];                               // [row slot][kx]
+            auto load_row = [&](float2 (&row)[K]) {
+                const int slot = g & (DEPTH - 1);
+                mbar_wait(full(slot), (g / DEPTH) & 1);
+                ++g;
+                const uint8_t* px = colbase + (size_t)slot * p.row_bytes;
 #pragma unroll
-            for (int kx = 0; kx < K; ++kx) row[kx] = Pair<T>::lds(px + kx * Pair<T>::kPixelBytes, lane);
-            // the row now lives in registers of every lane: hand the slot back to the producer at once
-            // (the arrive has release semantics, so the reads above are ordered before the TMA refill)
-            __syncwarp();
-            if (lane == 0) mbar_arrive(empty(slot));
-        };
+                for (int kx = 0; kx < K; ++kx) row[kx] = Pair<T>::lds(px + kx * PB, cl);
+                // the row now lives in registers of every lane: hand the slot back to the producer at once
+                // (the arrive has release semantics, so the reads above are ordered before the TMA refill)
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty(slot));
+            };
 #pragma unroll
-        for (int ky = 0; ky < K - S; ++ky) load_row(ky, xw[ky]);
-        for (int oh0 = 0; oh0 < a.oh; oh0 += K) {
+            for (int ky = 0; ky < K - S; ++ky) load_row(xw[ky]);
+            for (int oh0 = 0; oh0 < a.oh; oh0 += K) {
 #pragma unroll
-            for (int u = 0; u < K; ++u) {
-                const int oh = oh0 + u;
-                if (oh < a.oh) {                           // block-uniform
-                    // window row ky of output row oh lives in slot (ky + S*u) % K; the S new rows arrive now
+                for (int u = 0; u < K; ++u) {
+                    const int oh = oh0 + u;
+                    if (oh < a.oh) {                       // block-uniform
+                        // window row ky of output row oh lives in slot (ky + S*u) % K; the S new rows arrive now
 #pragma unroll
-                    for (int j = 0; j < S; ++j) load_row(oh * S + K - S + j, xw[(K - S + j + S * u) % K]);
-                    float2 acc0 = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
+                        for (int j = 0; j < S; ++j) load_row(xw[(K - S + j + S * u) % K]);
+                        float2 acc0 = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
 #pragma unroll
-                    for (int ky = 0; ky < K; ++ky)
+                        for (int ky = 0; ky < K; ++ky)
 #pragma unroll
-                        for (int kx = 0; kx < K; ++kx) {
-                            const float2 xv = xw[(ky + S * u) % K][kx], wv = w[ky * K + kx];
-                            if ((ky * K + kx) & 1) { acc1.x = fmaf(xv.x, wv.x, acc1.x); acc1.y = fmaf(xv.y, wv.y, acc1.y); }
-                            else { acc0.x = fmaf(xv.x, wv.x, acc0.x); acc0.y = fmaf(xv.y, wv.y, acc0.y); }
+                            for (int kx = 0; kx < K; ++kx) {
+                                const float2 xv = xw[(ky + S * u) % K][kx], wv = w[ky * K + kx];
+                                if ((ky * K + kx) & 1) { acc1.x = fmaf(xv.x, wv.x, acc1.x); acc1.y = fmaf(xv.y, wv.y, acc1.y); }
+                                else { acc0.x = fmaf(xv.x, wv.x, acc0.x); acc0.y = fmaf(xv.y, wv.y, acc0.y); }
+                            }
+                        float2 v = make_float2(apply_act(fmaf(acc0.x + acc1.x, sc.x, sf.x), a.act),
+                                               apply_act(fmaf(acc0.y + acc1.y, sc.y, sf.y), a.act));
+                        if (ok) {
+                            v = Pair<T>::st(ycol + (long long)oh * a.ow * a.y_cs, c, v);   // the squeeze sums what is stored
+                            psum.x += v.x;
+                            psum.y += v.y;
                         }
-                    float2 v = make_float2(apply_act(fmaf(acc0.x + acc1.x, sc.x, sf.x), a.act),
-                                           apply_act(fmaf(acc0.y + acc1.y, sc.y, sf.y), a.act));
-                    if (c_ok) {
-                        v = Pair<T>::st(ycol + (long long)oh * a.ow * a.y_cs, c, v);   // the squeeze sums what is stored
-                        psum.x += v.x;
-                        psum.y += v.y;
                     }
                 }
             }
-        }
-    }
-    if (a.pool_sum) {
-        if (warp < p.cols) {
-            pool_s[warp][2 * lane] = psum.x;
-            pool_s[warp][2 * lane + 1] = psum.y;
-        }
-        __syncthreads();
-        if (threadIdx.x < 64 && c0 + threadIdx.x < a.c_p) {
-            float s = 0.f;
-            for (int r = 0; r < n_act; ++r) s += pool_s[r][threadIdx.x];
-            atomicAdd(a.pool_sum + (long long)n * a.c_p + c0 + threadIdx.x, s);
+            if (a.pool_sum) {                              // per-image squeeze: reduce over the tile's columns
+                pool_s[col * CH + 2 * cl] = psum.x;
+                pool_s[col * CH + 2 * cl + 1] = psum.y;
+                asm volatile("bar.sync 1, %0;" ::"r"(n_cons) : "memory");
+                for (int ch = ctid; ch < CH; ch += n_cons) {
+                    if (c0 + ch < a.c_p) {
+                        float sum = 0.f;
+                        for (int r = 0; r < n_act * SUB; ++r) sum += pool_s[r * CH + ch];
+                        atomicAdd(a.pool_sum + (long long)n * a.c_p + c0 + ch, sum);
+                    }
+                }
+                asm volatile("bar.sync 1, %0;" ::"r"(n_cons) : "memory");
+            }
         }
     }
 }
 
-// columns per block: as many consumer warps as registers allow, sized to waste as little of the last tile as possible
-static int pick_cols(int ow, int max_cols) {
+// consumer warps per block: as many as registers allow, sized to waste as little of the last tile as possible
+static int pick_cols(int ow_units, int max_cols) {
     int best = 1;
     double best_cost = 1e30;
     for (int c = 1; c <= max_cols; ++c) {
-        const int tiles = ceil_div(ow, c);
+        const int tiles = ceil_div(ow_units, c);
         const double cost = (double)tiles * (c + 1.5);       // +1.5: producer warp + halo columns per tile
         if (cost < best_cost - 1e-9 || (cost < best_cost + 1e-9 && c > best)) { best_cost = cost; best = c; }
     }
     return best;
 }
 
-template <typename T, int K, int S>
-static int dwconv_tma_launch_ks(const EdeDwConv& a, cudaStream_t st) {
+template <typename T, int K, int S, int CH>
+static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) return 1;
     constexpr int DEPTH = DwDepth<K>::value;
+    constexpr int SUB = 64 / CH;
     DwParams p;
     memset(&p, 0, sizeof(p));
     p.a = a;
-    p.cols = pick_cols(a.ow, DwCols<K>::value);
+    p.cols = pick_cols(ceil_div(a.ow, SUB), DwCols<K>::value);
     const int esz = a.dtype == EDE_BF16 ? 2 : 4;
-    const int box_w = p.cols * S + K - S;
-    p.row_bytes = box_w * 64 * esz;
+    const int box_w = p.cols * SUB * S + K - S;
+    if (box_w > 256) return 1;
+    p.tx_bytes = box_w * CH * esz;
+    p.row_bytes = round_up(box_w * CH * esz, 128);          // TMA shared-memory destinations are 128-byte aligned
     cuuint64_t dims[4] = {(cuuint64_t)a.c_p, (cuuint64_t)a.w_, (cuuint64_t)a.h, (cuuint64_t)a.n};
     const cuuint64_t pix = (cuuint64_t)a.x_cs * esz;
     cuuint64_t strides[3] = {pix, pix * a.w_, pix * a.w_ * a.h};
-    cuuint32_t box[4] = {64, (cuuint32_t)box_w, 1, 1};
+    cuuint32_t box[4] = {(cuuint32_t)CH, (cuuint32_t)box_w, 1, 1};
     cuuint32_t es[4] = {1, 1, 1, 1};
     void* base = (void*)(reinterpret_cast<const uint8_t*>(a.x) + (size_t)a.x_co * esz);
     CUresult r = enc(&p.tm_x, esz == 2 ? CU_TENSOR_MAP_DATA_TYPE_UINT16 : CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, base, dims,
@@ -229,21 +248,45 @@ static int dwconv_tma_launch_ks(const EdeDwConv& a, cudaStream_t st) {
     if (r != CUDA_SUCCESS) return 1;
     const int smem = DEPTH * p.row_bytes + 128;
     static bool attr_set[64] = {};
+    static int sm_count[64] = {};
     int dev = 0;
     (void)cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
     if (!attr_set[dev]) {
-        if (cudaFuncSetAttribute(dwconv_tma_kernel<T, K, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) !=
-            cudaSuccess) {
+        if (cudaFuncSetAttribute(dwconv_tma_kernel<T, K, S, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 200 * 1024) != cudaSuccess ||
+            cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
             (void)cudaGetLastError();
             return 1;
         }
         attr_set[dev] = true;
     }
-    dim3 grid((unsigned)ceil_div(a.ow, p.cols), (unsigned)ceil_div(a.c_p, 64), (unsigned)a.n);
+    // One block per SM is resident (registers).  A block's fixed cost (weights, barrier init, ring fill) is a few
+    // rows' worth of work, so small maps let one block walk several images: pick the z split that minimises
+    // waves x (images per block x rows + fixed cost).
+    const int units = ceil_div(a.ow, p.cols * SUB) * ceil_div(a.c_p, CH);
+    const int sms = std::max(1, sm_count[dev]);
+    int best_z = a.n;
+    double best_cost = 1e30;
+    for (int z = 1; z <= a.n; ++z) {
+        const double waves = (double)ceil_div(units * z, sms);
+        const double cost = waves * ((double)ceil_div(a.n, z) * (a.oh + 3.0) + 6.0);   // +3 rows per image switch
+        if (cost < best_cost - 1e-9) { best_cost = cost; best_z = z; }
+    }
+    static const char* z_env = getenv("EDE_DW_ZSPLIT");       // debug / tests: force the number of image groups
+    if (z_env && *z_env) best_z = std::max(1, std::min(a.n, atoi(z_env)));
+    p.zsplit = best_z;
+    dim3 grid((unsigned)ceil_div(a.ow, p.cols * SUB), (unsigned)ceil_div(a.c_p, CH), (unsigned)p.zsplit);
     if (grid.y > 65535u || grid.z > 65535u || smem > 200 * 1024) return 1;
-    dwconv_tma_kernel<T, K, S><<<grid, 32 * (p.cols + 1), smem, st>>>(p);
+    dwconv_tma_kernel<T, K, S, CH><<<grid, 32 * (p.cols + 1), smem, st>>>(p);
     return 0;
+}
+
+template <typename T, int K, int S>
+static int dwconv_tma_launch_ks(const EdeDwConv& a, cudaStream_t st) {
+    // 32-lane chunks when they cut the idle lanes of the last chunk by a quarter or more (c_p = 32, 96, ...)
+    if (4 * round_up(a.c_p, 32) <= 3 * round_up(a.c_p, 64)) return dwconv_tma_launch_ch<T, K, S, 32>(a, st);
+    return dwconv_tma_launch_ch<T, K, S, 64>(a, st);
 }
 
 // returns 0 when the TMA kernel was launched, 1 when this (k, s) / device has no TMA path (caller falls back)

@@ -136,12 +136,13 @@ def test_conv2d(cuda, lib, case, mode):
     assert bool((err <= tol).all()), (name, mode, float(err.max()), float((err / (ref.abs() + 1)).max()))
 
 
+@pytest.mark.parametrize("c", [44, 90, 150])      # 48 lanes (one 64-chunk), 96 (three 32-lane chunks), 152 (64+64+24)
 @pytest.mark.parametrize("dt", [A.F32, A.BF16, A.BF16X2])
 @pytest.mark.parametrize("k,s,pad", [(3, 1, (1, 1, 1, 1)), (3, 2, (0, 0, 1, 1)), (5, 2, (1, 1, 2, 2)), (5, 1, (2, 2, 2, 2))])
-def test_dwconv_se(cuda, lib, dt, k, s, pad):
+def test_dwconv_se(cuda, lib, dt, k, s, pad, c):
     """Depthwise + BN + swish + SE squeeze, SE FCs and the gate multiply (App. A.3 of SURVEY.md)."""
     g = torch.Generator().manual_seed(k * 10 + s)
-    n, c, h, w, csq = 3, 44, 29, 38, 6
+    n, h, w, csq = 3, 29, 38, 6
     c_p = P.ceil8(c)
     pt, pl, pb, pr = pad
     oh, ow = (h + pt + pb - k) // s + 1, (w + pl + pr - k) // s + 1
