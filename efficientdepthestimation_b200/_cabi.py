@@ -15,7 +15,7 @@ F32, BF16, BF16X2 = 0, 1, 2
 ACT_NONE, ACT_RELU, ACT_SWISH, ACT_SIGMOID = 0, 1, 2, 3
 NHWC, NCHW = 0, 1
 (OP_CONV, OP_DWCONV, OP_SE_FC, OP_SE_SCALE, OP_RESIZE, OP_MAXPOOL, OP_ELTWISE, OP_TO_NHWC, OP_TO_NCHW,
- OP_ZERO, OP_UPCONV) = range(1, 12)
+ OP_ZERO, OP_UPCONV, OP_STEM) = range(1, 13)
 
 
 def _ints(*names):
@@ -44,7 +44,7 @@ class EdeDwConv(Structure):
 
 class EdeSeFc(Structure):
     _fields_ = [("pool_sum", c_void_p), ("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p),
-                ("gate", c_void_p)] + _ints("n", "c", "c_p", "csq") + [("inv_hw", c_float)]
+                ("gate", c_void_p)] + _ints("n", "c", "c_p", "csq") + [("inv_hw", c_float)] + _ints("clear_pool", "w2_transposed")
 
 
 class EdeSeScale(Structure):
@@ -77,6 +77,11 @@ class EdeUpConv(Structure):
         "act_c_end")
 
 
+class EdeStem(Structure):
+    _fields_ = [("x", c_void_p), ("y", c_void_p), ("w", c_void_p), ("scale", c_void_p), ("shift", c_void_p)] + _ints(
+        "n", "cin", "h", "w_", "oh", "ow", "cout_p", "y_cs", "y_co", "k", "s", "pt", "pl", "act", "y_dtype")
+
+
 class _Zero(Structure):
     _fields_ = [("p", c_void_p), ("bytes", c_int64)]
 
@@ -84,7 +89,7 @@ class _Zero(Structure):
 class _OpU(Union):
     _fields_ = [("conv", EdeConv), ("dw", EdeDwConv), ("se_fc", EdeSeFc), ("se_scale", EdeSeScale),
                 ("resize", EdeResize), ("maxpool", EdeMaxPool), ("eltwise", EdeEltwise), ("layout", EdeLayout),
-                ("upconv", EdeUpConv), ("zero", _Zero)]
+                ("upconv", EdeUpConv), ("stem", EdeStem), ("zero", _Zero)]
 
 
 class EdeOp(Structure):
@@ -93,10 +98,10 @@ class EdeOp(Structure):
 
 OP_FIELD = {OP_CONV: "conv", OP_DWCONV: "dw", OP_SE_FC: "se_fc", OP_SE_SCALE: "se_scale", OP_RESIZE: "resize",
             OP_MAXPOOL: "maxpool", OP_ELTWISE: "eltwise", OP_TO_NHWC: "layout", OP_TO_NCHW: "layout",
-            OP_ZERO: "zero", OP_UPCONV: "upconv"}
+            OP_ZERO: "zero", OP_UPCONV: "upconv", OP_STEM: "stem"}
 
 # every symbol include/ede.h declares (checked by tests/test_cabi.py without a GPU)
-EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_dwconv2d", "ede_se_fc", "ede_se_scale",
+EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_stem_conv", "ede_stem_supported", "ede_dwconv2d", "ede_se_fc", "ede_se_scale",
            "ede_resize_bilinear_ac", "ede_resize_planes_f32", "ede_maxpool3x3s2", "ede_eltwise", "ede_nchw_to_nhwc", "ede_nhwc_to_nchw",
            "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_plan_run",
            "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof"]
@@ -118,10 +123,12 @@ def lib():
                      ("ede_se_scale", EdeSeScale), ("ede_resize_bilinear_ac", EdeResize),
                      ("ede_maxpool3x3s2", EdeMaxPool), ("ede_eltwise", EdeEltwise),
                      ("ede_nchw_to_nhwc", EdeLayout), ("ede_nhwc_to_nchw", EdeLayout),
-                     ("ede_upconv_taps", EdeUpConv)):
+                     ("ede_upconv_taps", EdeUpConv), ("ede_stem_conv", EdeStem)):
         f = getattr(L, name)
         f.argtypes = [POINTER(st), c_void_p]
         f.restype = c_int32
+    L.ede_stem_supported.argtypes = [c_int32, c_int32, c_int32, c_int32]
+    L.ede_stem_supported.restype = c_int32
     L.ede_conv2d_umma_config.argtypes = [POINTER(EdeConv), POINTER(EdeUmmaCfg)]
     L.ede_conv2d_umma_config.restype = c_int32
     L.ede_fill_zero.argtypes = [c_void_p, c_int64, c_void_p]

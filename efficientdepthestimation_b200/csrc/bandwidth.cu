@@ -81,8 +81,11 @@ __global__ void __launch_bounds__(256) se_fc_kernel(const EdeSeFc a) {
     float* mean = sm;
     float* hid = sm + a.c_p;
     const int n = blockIdx.x;
-    for (int i = threadIdx.x; i < a.c_p; i += blockDim.x)
-        mean[i] = i < a.c ? a.pool_sum[(long long)n * a.c_p + i] * a.inv_hw : 0.f;
+    for (int i = threadIdx.x; i < a.c_p; i += blockDim.x) {
+        float* ps = a.pool_sum + (long long)n * a.c_p + i;
+        mean[i] = i < a.c ? *ps * a.inv_hw : 0.f;
+        if (a.clear_pool) *ps = 0.f;                       // ready for the next forward's squeeze
+    }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     for (int j = warp; j < a.csq; j += nw) {
@@ -96,7 +99,11 @@ __global__ void __launch_bounds__(256) se_fc_kernel(const EdeSeFc a) {
         float s = 0.f;
         if (c < a.c) {
             s = a.b2[c];
-            for (int j = 0; j < a.csq; ++j) s = fmaf(a.w2[(long long)c * a.csq + j], hid[j], s);
+            if (a.w2_transposed) {
+                for (int j = 0; j < a.csq; ++j) s = fmaf(a.w2[(long long)j * a.c_p + c], hid[j], s);
+            } else {
+                for (int j = 0; j < a.csq; ++j) s = fmaf(a.w2[(long long)c * a.csq + j], hid[j], s);
+            }
         }
         a.gate[(long long)n * a.c_p + c] = c < a.c ? apply_act(s, EDE_ACT_SIGMOID) : 0.f;
     }

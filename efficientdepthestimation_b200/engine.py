@@ -140,10 +140,11 @@ class Graph:
             self.encoder_dtype = A.BF16X2 if self.encoder_precision == "bf16x2" else A.BF16
         self.act_dtype = self.decoder_dtype       # dtype of newly created activations (see encoder_scope)
         self.dry = device.type != "cuda"          # host-only compile (tests without a GPU)
+        self.dry_no_lib = self.dry and not os.path.exists(A.LIB_PATH)
         self.ops: List[tuple] = []                # (kind, struct, [(field, Buf)], tag)
         self.bufs: List[Buf] = []
         self.keep: List[torch.Tensor] = []        # prepacked weights etc.
-        self.inputs: List[tuple] = []             # (op index, shape)
+        self.inputs: List[dict] = []              # {shape, targets: [(op index, pointer field)], lazy: to_nhwc op}
         self.outputs: List[tuple] = []            # (op index, shape)
         self.flops = 0.0                          # algorithmic 2*MAC of the reference graph's convs
         self.exec_flops = 0.0                     # 2*MAC actually issued to the tensor cores / CUDA cores
@@ -209,7 +210,9 @@ class Graph:
         v = self.new_view(n, h, w, c, self.encoder_dtype)     # inputs keep 16 mantissa bits (4 B/lane)
         st = A.EdeLayout(src=None, dst=None, n=n, c=c, h=h, w=w, c_p=v.c_p, cs=v.buf.cs, co=v.co, dtype=v.dtype)
         i = self._add(A.OP_TO_NHWC, st, [("dst", v.buf)], "to_nhwc")
-        self.inputs.append((i, (n, c, h, w)))
+        # the layout pass is dropped again in finalize() when only fused stem convs (EDE_OP_STEM) consumed the input
+        self.inputs.append(dict(shape=(n, c, h, w), targets=[(i, "src")], lazy=i))
+        v.input_index = len(self.inputs) - 1
         return v
 
     def output_nchw(self, v: View) -> None:
@@ -232,6 +235,10 @@ class Graph:
             x = self.eltwise(x, act=A.ACT_RELU, tag=tag + ".relu_in")      # keeps the conv on the tcgen05 path
             relu_in = False
         kh, kw = int(parts[0][0].shape[2]), int(parts[0][0].shape[3])
+        if (getattr(x, "input_index", None) is not None and len(parts) == 1 and res is None and not relu_in
+                and out is None and kh == kw and not self.dry_no_lib
+                and A.lib().ede_stem_supported(kh, stride, x.c, P.ceil8(int(parts[0][0].shape[0])))):
+            return self._stem(x, parts[0], stride, pad, act, out_dtype, tag)
         pt, pl, pb, pr = pad
         oh = (x.h + pt + pb - kh) // stride + 1
         ow = (x.w + pl + pr - kw) // stride + 1
@@ -302,6 +309,27 @@ class Graph:
         self._add(A.OP_CONV, st, refs, tag)
         return out
 
+    def _stem(self, x: View, part, stride, pad, act, out_dtype, tag) -> View:
+        """First conv of the network straight from the fp32 NCHW input (EDE_OP_STEM, csrc/stem.cu)."""
+        wt, bn, bias, _ = part
+        co, cin, k = int(wt.shape[0]), int(wt.shape[1]), int(wt.shape[2])
+        pt, pl, pb, pr = pad
+        oh, ow = (x.h + pt + pb - k) // stride + 1, (x.w + pl + pr - k) // stride + 1
+        out = self.new_view(x.n, oh, ow, co, out_dtype)
+        w = torch.zeros(k * k * cin, out.c_p, dtype=torch.float32, device=wt.device)
+        w[:, :co] = wt.detach().float().permute(2, 3, 1, 0).reshape(k * k * cin, co)
+        sc, sf = P.fold_bn(co, _bn_dict(bn), bias, wt.device)
+        w, sc, sf = self._dev(w), self._dev(P.place_lanes(sc, out.lanes)), self._dev(P.place_lanes(sf, out.lanes))
+        st = A.EdeStem(x=None, y=None, w=self._ptr(w), scale=self._ptr(sc), shift=self._ptr(sf), n=x.n, cin=cin,
+                       h=x.h, w_=x.w, oh=oh, ow=ow, cout_p=out.c_p, y_cs=out.buf.cs, y_co=out.co, k=k, s=stride,
+                       pt=pt, pl=pl, act=act, y_dtype=out.dtype)
+        i = self._add(A.OP_STEM, st, [("y", out.buf)], tag)
+        self.inputs[x.input_index]["targets"].append((i, "x"))
+        fl = 2.0 * x.n * oh * ow * co * cin * k * k
+        self.flops += fl
+        self.exec_flops += fl
+        return out
+
     def conv_bn_act(self, x: View, conv, bn=None, act=A.ACT_NONE, res=None, out=None, relu_in=False,
                     out_dtype=None, tag="conv") -> View:
         """nn.Conv2d (+ nn.BatchNorm2d) (+ activation) as one fused operator."""
@@ -328,8 +356,9 @@ class Graph:
         w, sc, sf = self._dev(w), self._dev(P.place_lanes(sc, x.lanes)), self._dev(P.place_lanes(sf, x.lanes))
         pool_t = None
         if pool:
+            # zeroed once here; se_gate's FC kernel clears it again after reading (EdeSeFc.clear_pool), so a
+            # forward needs no fill launch
             pool_t = self._dev(torch.zeros(x.n, x.c_p, dtype=torch.float32))
-            self._add(A.OP_ZERO, A._Zero(p=self._ptr(pool_t), bytes=pool_t.numel() * 4), [], tag + ".zero")
         st = A.EdeDwConv(x=None, y=None, w=self._ptr(w), scale=self._ptr(sc), shift=self._ptr(sf),
                          pool_sum=self._ptr(pool_t), n=x.n, h=x.h, w_=x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
                          oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype)
@@ -348,8 +377,8 @@ class Graph:
             raise RuntimeError("se_gate: channels must occupy lanes 0..c-1")
         w1 = torch.zeros(csq, x.c_p, dtype=torch.float32, device=dev)
         w1[:, idx] = reduce_conv.weight.detach().float().reshape(csq, c)[:, src]
-        w2 = torch.zeros(x.c_p, csq, dtype=torch.float32, device=dev)
-        w2[idx] = expand_conv.weight.detach().float().reshape(c, csq)[src]
+        w2 = torch.zeros(csq, x.c_p, dtype=torch.float32, device=dev)              # [csq][c_p]: coalesced reads
+        w2[:, idx] = expand_conv.weight.detach().float().reshape(c, csq)[src].t()
         b2 = torch.zeros(x.c_p, dtype=torch.float32, device=dev)
         b2[idx] = expand_conv.bias.detach().float()[src]
         w1, w2, b2 = self._dev(w1), self._dev(w2), self._dev(b2)
@@ -357,7 +386,7 @@ class Graph:
         gate = self._dev(torch.zeros(x.n, x.c_p, dtype=torch.float32))
         st = A.EdeSeFc(pool_sum=self._ptr(pool_t), w1=self._ptr(w1), b1=self._ptr(b1), w2=self._ptr(w2),
                        b2=self._ptr(b2), gate=self._ptr(gate), n=x.n, c=c, c_p=x.c_p, csq=csq,
-                       inv_hw=1.0 / (x.h * x.w))
+                       inv_hw=1.0 / (x.h * x.w), clear_pool=1, w2_transposed=1)
         self._add(A.OP_SE_FC, st, [], tag + ".fc")
         out = View(self.new_buf(x.n, x.h, x.w, x.c_p, x.dtype), 0, x.lanes)
         st = A.EdeSeScale(x=None, y=None, gate=self._ptr(gate), n=x.n, hw=x.h * x.w, c_p=x.c_p,
@@ -441,6 +470,30 @@ class Graph:
     # ------------------------------------------------------------------ arena layout
     def finalize(self) -> "Plan":
         """Liveness-based first-fit placement of every buffer in one arena, then pointer patching."""
+        dead = set()
+        for inp in self.inputs:                    # NCHW -> NHWC passes whose output nobody reads
+            i = inp["lazy"]
+            dst = self.ops[i][2][0][1]
+            if len(inp["targets"]) > 1 and not any(b is dst for j, op in enumerate(self.ops) if j != i for _, b in op[2]):
+                dead.add(i)
+                inp["targets"] = [t for t in inp["targets"] if t[0] != i]
+        if dead:
+            remap, keep = {}, []
+            for j, op in enumerate(self.ops):
+                if j not in dead:
+                    remap[j] = len(keep)
+                    keep.append(op)
+            self.ops = keep
+            for inp in self.inputs:
+                inp["targets"] = [(remap[j], f) for j, f in inp["targets"]]
+            self.outputs = [(remap[j], shp) for j, shp in self.outputs]
+            for b in self.bufs:
+                b.first = b.last = -1
+            for j, (_, _, refs, _) in enumerate(self.ops):
+                for _, b in refs:
+                    if b.first < 0:
+                        b.first = j
+                    b.last = j
         live: List[Buf] = []
         top = 0
         for b in sorted((b for b in self.bufs if b.first >= 0), key=lambda b: (b.first, -b.nbytes)):
@@ -507,13 +560,14 @@ class Plan:
         outs = []
         with self._lock, torch.cuda.device(self.device):
             hold = []
-            for (i, shape), t in zip(self.inputs, tensors):
-                if tuple(t.shape) != shape:
-                    raise RuntimeError(f"plan compiled for input {shape}, got {tuple(t.shape)}")
+            for inp, t in zip(self.inputs, tensors):
+                if tuple(t.shape) != inp["shape"]:
+                    raise RuntimeError(f"plan compiled for input {inp['shape']}, got {tuple(t.shape)}")
                 if t.dtype != torch.float32 or not t.is_contiguous():
                     t = t.float().contiguous()
                 hold.append(t)
-                self.ops[i].u.layout.src = t.data_ptr()
+                for i, field in inp["targets"]:
+                    setattr(getattr(self.ops[i].u, A.OP_FIELD[self.kinds[i]]), field, t.data_ptr())
             for (i, shape) in self.outputs:
                 o = torch.empty(shape, dtype=torch.float32, device=self.device)
                 self.ops[i].u.layout.dst = o.data_ptr()

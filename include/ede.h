@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 3
+#define EDE_ABI_VERSION 4
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
@@ -104,8 +104,12 @@ int ede_dwconv2d(const EdeDwConv* a, void* stream);
  * replaces: _se_reduce -> swish -> _se_expand -> sigmoid (App. A.3).  w1: fp32 [csq][c_p],
  *   w2: fp32 [c_p][csq] (rows >= c hold zeros), gate: fp32 [n][c_p]. */
 typedef struct EdeSeFc {
-    const float* pool_sum; const float* w1; const float* b1; const float* w2; const float* b2; float* gate;
+    float* pool_sum;        /* read; zeroed afterwards when clear_pool = 1 */
+    const float* w1; const float* b1; const float* w2; const float* b2; float* gate;
     int32_t n, c, c_p, csq; float inv_hw;
+    int32_t clear_pool;     /* 1: write zeros back to pool_sum after reading it, so that the next forward's
+                               ede_dwconv2d accumulates from zero without a separate ede_fill_zero launch */
+    int32_t w2_transposed;  /* 1: w2 is fp32 [csq][c_p] (coalesced reads), 0: [c_p][csq]            */
 } EdeSeFc;
 int ede_se_fc(const EdeSeFc* a, void* stream);
 
@@ -172,6 +176,19 @@ int ede_nhwc_to_nchw(const EdeLayout* a, void* stream);
 
 int ede_fill_zero(void* p, int64_t bytes, void* stream);
 
+/* The network's first convolution straight from the fp32 NCHW image (CUDA cores, fp32 exact), fused with the
+ * folded BN, the activation and the NCHW -> NHWC layout change.
+ * replaces: conv1 7x7 s2 p3 + bn1 + ReLU of ReSIDE/models/resnet.py:103-106 and the EfficientNet stem
+ *   (conv_stem 3x3 s2 static-same padding + bn0; modules.py:185 keeps no swish after it).
+ * x: fp32 [n][cin][h][w] (cin <= 4); w: fp32 [k*k*cin][cout_p] with row (ky*k+kx)*cin+ci; y: NHWC view.
+ * Supported shapes: ede_stem_supported(k, s, cin, cout_p) (3x3 s2 -> 32/48/64 lanes, 7x7 s2 -> 64 lanes). */
+typedef struct EdeStem {
+    const float* x; void* y; const float* w; const float* scale; const float* shift;
+    int32_t n, cin, h, w_, oh, ow, cout_p, y_cs, y_co, k, s, pt, pl, act, y_dtype;
+} EdeStem;
+int ede_stem_conv(const EdeStem* a, void* stream);
+int ede_stem_supported(int32_t k, int32_t s, int32_t cin, int32_t cout_p);
+
 /* Sobel gradients. replaces: Sobel.forward, ReSIDE/sobel.py:19-23 ([n,1,h,w] -> [n,2,h,w], fp32 NCHW). */
 int ede_sobel(const float* x, float* y, int32_t n, int32_t h, int32_t w, void* stream);
 
@@ -192,12 +209,12 @@ int ede_edge_counts(const float* pred, const float* label, int32_t n, int32_t h,
 /* Run a pre-built operator list ("forward plan") back to back on one stream. */
 enum { EDE_OP_CONV = 1, EDE_OP_DWCONV = 2, EDE_OP_SE_FC = 3, EDE_OP_SE_SCALE = 4, EDE_OP_RESIZE = 5,
        EDE_OP_MAXPOOL = 6, EDE_OP_ELTWISE = 7, EDE_OP_TO_NHWC = 8, EDE_OP_TO_NCHW = 9, EDE_OP_ZERO = 10,
-       EDE_OP_UPCONV = 11 };
+       EDE_OP_UPCONV = 11, EDE_OP_STEM = 12 };
 typedef struct EdeOp {
     int32_t kind; int32_t _pad;
     union {
         EdeConv conv; EdeDwConv dw; EdeSeFc se_fc; EdeSeScale se_scale; EdeResize resize;
-        EdeMaxPool maxpool; EdeEltwise eltwise; EdeLayout layout; EdeUpConv upconv;
+        EdeMaxPool maxpool; EdeEltwise eltwise; EdeLayout layout; EdeUpConv upconv; EdeStem stem;
         struct { void* p; int64_t bytes; } zero;
     } u;
 } EdeOp;

@@ -197,6 +197,50 @@ def test_dwconv_se(cuda, lib, dt, k, s, pad, c):
     zgot = (split_load(z, c_p) if dt == A.BF16X2 else z.float())[..., :c].permute(0, 3, 1, 2)
     zref = got * gref.view(n, c, 1, 1)
     assert bool(((zgot - zref).abs() <= rel * zref.abs() + rel).all())
+    # the form the engine emits: expand weights transposed ([csq][c_p]), squeeze sums cleared for the next forward
+    gate2 = torch.zeros_like(gate)
+    w2t = w2p.t().contiguous()
+    f2 = A.EdeSeFc(pool_sum=pool.data_ptr(), w1=w1p.data_ptr(), b1=b1.data_ptr(), w2=w2t.data_ptr(), b2=b2p.data_ptr(),
+                   gate=gate2.data_ptr(), n=n, c=c, c_p=c_p, csq=csq, inv_hw=1.0 / (oh * ow), clear_pool=1,
+                   w2_transposed=1)
+    A.check(lib.ede_se_fc(C.byref(f2), stream()), "ede_se_fc")
+    torch.cuda.synchronize()
+    assert torch.allclose(gate2, gate, rtol=1e-5, atol=1e-6) and float(pool.abs().sum()) == 0
+
+
+@pytest.mark.parametrize("dt", [A.F32, A.BF16, A.BF16X2])
+@pytest.mark.parametrize("k,s,cout,pad,act,hw", [(3, 2, 32, (0, 0, 1, 1), A.ACT_SWISH, (57, 76)),     # EfficientNet-B0 stem
+                                                 (3, 2, 48, (0, 0, 1, 1), A.ACT_SWISH, (228, 304)),   # EfficientNet-B4 stem
+                                                 (7, 2, 64, (3, 3, 3, 3), A.ACT_RELU, (228, 304)),    # ResNet conv1
+                                                 (7, 2, 64, (3, 3, 3, 3), A.ACT_RELU, (37, 131))])
+def test_stem_conv_from_nchw(cuda, lib, dt, k, s, cout, pad, act, hw):
+    """First conv read straight from the fp32 NCHW image (resnet.py:103-106 / EfficientNet stem)."""
+    g = torch.Generator().manual_seed(k * 100 + cout)
+    n, cin, (h, w) = 3, 3, hw
+    pt, pl, pb, pr = pad
+    oh, ow = (h + pt + pb - k) // s + 1, (w + pl + pr - k) // s + 1
+    assert lib.ede_stem_supported(k, s, cin, cout) == 1 and lib.ede_stem_supported(5, 1, cin, cout) == 0
+    x = torch.randn(n, cin, h, w, generator=g).to(cuda)
+    wt = (torch.randn(cout, cin, k, k, generator=g) / (k * cin ** 0.5)).to(cuda)
+    scale, shift = (0.5 + torch.rand(cout, generator=g)).to(cuda), (0.2 * torch.randn(cout, generator=g)).to(cuda)
+    wk = wt.permute(2, 3, 1, 0).reshape(k * k * cin, cout).contiguous()
+    mul = 2 if dt == A.BF16X2 else 1
+    cs = cout + 16                                                   # write into a slice of a wider buffer
+    y = torch.full((n, oh, ow, cs * mul), 7.0, device=cuda, dtype=torch.bfloat16 if dt != A.F32 else torch.float32)
+    a = A.EdeStem(x=x.data_ptr(), y=y.data_ptr(), w=wk.data_ptr(), scale=scale.data_ptr(), shift=shift.data_ptr(),
+                  n=n, cin=cin, h=h, w_=w, oh=oh, ow=ow, cout_p=cout, y_cs=cs, y_co=8, k=k, s=s, pt=pt, pl=pl,
+                  act=act, y_dtype=dt)
+    A.check(lib.ede_stem_conv(C.byref(a), stream()), "ede_stem_conv")
+    torch.cuda.synchronize()
+    ref = F.conv2d(F.pad(x.double(), (pl, pr, pt, pb)), wt.double(), None, s).float()
+    ref = ref * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1)
+    ref = ref * torch.sigmoid(ref) if act == A.ACT_SWISH else torch.relu(ref)
+    full = split_load(y, cs) if dt == A.BF16X2 else y.float()
+    got = full[..., 8:8 + cout].permute(0, 3, 1, 2)
+    rel = {A.F32: 2e-5, A.BF16: 4e-3, A.BF16X2: 4e-5}[dt]
+    assert bool(((got - ref).abs() <= rel * ref.abs() + rel).all())
+    untouched = torch.cat((full[..., :8], full[..., 8 + cout:]), dim=-1)      # neighbours of the slice stay as they were
+    assert bool((untouched == (14.0 if dt == A.BF16X2 else 7.0)).all())
 
 
 @pytest.mark.parametrize("dts", [(A.F32, A.F32), (A.BF16, A.BF16), (A.BF16X2, A.BF16)])

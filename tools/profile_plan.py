@@ -34,6 +34,10 @@ def op_bytes(kind, st):
         return st.n_pix * st.c_p * es[st.dtype] * (3 if st.x2 else 2)
     if kind in (A.OP_TO_NHWC, A.OP_TO_NCHW):
         return st.n * st.h * st.w * (st.c * 4 + st.c_p * es[st.dtype])
+    if kind == A.OP_STEM:
+        return st.n * (st.cin * st.h * st.w_ * 4 + st.oh * st.ow * st.cout_p * es[st.y_dtype])
+    if kind == A.OP_UPCONV:
+        return st.n * st.cgrp * (st.h * st.w * st.kh * st.kw * 4 + st.oh * st.ow * es[st.y_dtype])
     return 0
 
 
@@ -76,6 +80,9 @@ def main():
             desc = (f"{s.kh}x{s.kw}s{s.sh} {s.cin_p}->{s.cout_p}@{s.oh}x{s.ow} p{s.w_passes} "
                     f"{'res' if cfg.a_mode == 0 else 'tap'}{'/swap' if cfg.swap else ''} ck{cfg.ck} {cfg.bh}x{cfg.bw} mt{cfg.m_tiles} n{cfg.n_pad}x{cfg.n_tiles}"
                     if cfg.eligible else f"{s.kh}x{s.kw} DIRECT {s.cin_p}->{s.cout_p}")
+        if kind == A.OP_STEM:
+            fl = 2.0 * s.n * s.oh * s.ow * s.cout_p * s.cin * s.k * s.k
+            desc = f"{s.k}x{s.k}s{s.s} {s.cin}->{s.cout_p}@{s.oh}x{s.ow} CUDA-core stem from NCHW fp32"
         by = op_bytes(kind, s)
         rows.append(dict(i=i, tag=plan.tags[i], kind=A.OP_FIELD[kind], ms=ms, tflops=fl / ms / 1e9 if fl else 0.0,
                          gbs=by / ms / 1e6, desc=desc, flops=fl, bytes=by))
