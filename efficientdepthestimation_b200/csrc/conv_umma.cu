@@ -89,6 +89,7 @@ struct alignas(64) UmmaParams {
     int m_tiles, n_pad, acc_cols, swap;      // swap: weights are the M-side operand, 256 (240 packed) pixels on N
     int pack_g, kw_steps, n_cols;            // pack_g taps share one MMA (M rows = [tap j][128/pack_g channels]); kw_steps = ceil(kw/pack_g); n_cols = UMMA N of the swapped form
     int a_stages, b_stages, a_stage_bytes, b_stage_bytes, b_tx_bytes;
+    int b_group;          // taps per weight stage (one TMA box, one wait, one commit); > 1 only swapped + resident
     int layout_type, sbo_bytes, tmem_cols, flat;
     uint32_t idesc;
     void* y;
@@ -145,6 +146,12 @@ __device__ __forceinline__ float act_ct(float v) {
     if (ACT == EDE_ACT_SWISH) return __fdividef(v, 1.f + __expf(-v));
     return v;
 }
+#ifndef EDE_UNIFORM_ISSUER
+#define EDE_UNIFORM_ISSUER 1       // MMA issuer: whole warp walks the loop, one elected lane issues (else lane 0 alone)
+#endif
+#ifndef EDE_UNIFORM_PRODUCER
+#define EDE_UNIFORM_PRODUCER 0     // same choice for the TMA producer warp
+#endif
 constexpr int ACT_RUNTIME = 99;              // kernel variant that reads p.act at run time (sigmoid, anything else)
 
 template <typename TY, int ACT, bool RES>
@@ -215,7 +222,7 @@ constexpr int STG_FLOATS = 16 * STG_PITCH;
 template <typename TY, int ACT, bool RES>
 __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const TileCoord& t, uint32_t t_base, int quarter,
                                                  int half, int lane, int tid_h, float* s_stage, const float* s_scale,
-                                                 const float* s_shift) {
+                                                 const float* s_shift, long long* ph) {
     const int wrap = p.a_mode == 0 ? p.pitch : p.bw;
     const uint32_t wrap_inv = 65536u / (uint32_t)wrap + 1u;   // f / wrap for f < 256 (one correction step below)
     const int cg = 128 / p.pack_g;                           // channels per tap slot (32 / 64 / 128)
@@ -238,8 +245,10 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
         const float* const buf = s_stage + (it & 1) * STG_FLOATS;
         const bool next = live && c0 + step < p.n_cols;
         if (next) tc_ld16(t_base + (uint32_t)(c0 + step + j), acc);      // in flight across the barrier and phase 2
+        const long long c_a = ph ? clock64() : 0;
         if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
         else asm volatile("bar.sync 3, 128;" ::: "memory");
+        const long long c_b = ph ? clock64() : 0;
         for (int k = 0; k < upt; ++k) {
             const int u = tid_h + (k << 7);
             const int pj = u >> upp_lg, c = (u & (upp - 1)) << 2;
@@ -272,12 +281,15 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
             }
             store4<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co, c, v);
         }
+        const long long c_c = ph ? clock64() : 0;
+        if (ph) { ph[0] += c_b - c_a; ph[1] += c_c - c_b; }
         if (next) {                                          // chunk it+1 -> the other staging tile (its readers of
             tc_ld_wait();                                    // chunk it-1 all passed this iteration's barrier)
             float* const nb = s_stage + ((it + 1) & 1) * STG_FLOATS;
 #pragma unroll
             for (int k = 0; k < 16; ++k) nb[k * STG_PITCH + r] = __uint_as_float(acc[k]);
         }
+        if (ph) ph[2] += clock64() - c_c;
     }
 }
 
@@ -341,15 +353,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_addr) : "r"(tmem_slot) : "memory");
 
     if (warp == 0) {
-        // ===================== TMA producer: ONE thread walks the loop (no warp-collective ops on the hot path)
+        // ===================== TMA producer: ONE thread walks the loop (no warp-collective ops on the hot path; a
+        // warp-uniform loop with an elected issuing lane measured 7 % slower on the 5x5 decoder convs)
+#if EDE_UNIFORM_PRODUCER
+        {
+            const bool leader = elect_one();
+#else
         if (lane == 0) {
+            const bool leader = true;
+#endif
             int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0;
             const int ck = p.ck_bytes >> 1;
             const int a_mode = p.a_mode, n_chunks = p.n_chunks, m_tiles = p.m_tiles, kws = p.kw_steps;
             const int a_stages = p.a_stages, b_stages = p.b_stages;
             const uint32_t a_stage_bytes = (uint32_t)p.a_stage_bytes, b_stage_bytes = (uint32_t)p.b_stage_bytes;
-            const uint32_t box_bytes = (uint32_t)p.box_bytes, b_tx = (uint32_t)p.b_tx_bytes;
+            const int b_group = p.b_group;
+            const uint32_t box_bytes = (uint32_t)p.box_bytes, b_tx = (uint32_t)(p.b_tx_bytes * b_group);
             const uint32_t a_tx = (uint32_t)(m_tiles * 128 * p.ck_bytes), m_bytes = (uint32_t)(128 * p.ck_bytes);
+            const bool prof = p.prof != nullptr;
+            long long w_empty = 0;
             for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
                 const TileCoord t = decode_tile(p, tile);
                 const int wrow = t.ntile * p.n_pad;
@@ -357,36 +379,54 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                     const int cch = chunk * ck;
                     if (a_mode == 0) {
                         mbar_wait(a_empty(a_st), a_ph ^ 1);
-                        mbar_expect_tx(a_full(a_st), box_bytes);
-                        tma_load_4d(a_base + a_st * a_stage_bytes, &p.tm_a, a_full(a_st), cch, t.ow0 - p.pl,
-                                    t.oh0 - p.pt, t.img);
+                        if (leader) {
+                            mbar_expect_tx(a_full(a_st), box_bytes);
+                            tma_load_4d(a_base + a_st * a_stage_bytes, &p.tm_a, a_full(a_st), cch, t.ow0 - p.pl,
+                                        t.oh0 - p.pt, t.img);
+                        }
                         if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; }
                     }
                     int ky = 0, kx = 0;
-                    for (int tap = 0; tap < taps; ++tap) {
+                    for (int tap = 0; tap < taps; tap += b_group) {
                         if (a_mode != 0) {
                             if (tap == sp_taps) { ky = 0; kx = 0; }
                             mbar_wait(a_empty(a_st), a_ph ^ 1);
-                            mbar_expect_tx(a_full(a_st), a_tx);
-                            for (int m = 0; m < m_tiles; ++m)
-                                tma_load_4d(a_base + a_st * a_stage_bytes + m * m_bytes, &p.tm_a, a_full(a_st), cch,
-                                            (t.ow0 + m * p.bw) * p.sw - p.pl + kx, t.oh0 * p.sh - p.pt + ky, t.img);
+                            if (leader) {
+                                mbar_expect_tx(a_full(a_st), a_tx);
+                                for (int m = 0; m < m_tiles; ++m)
+                                    tma_load_4d(a_base + a_st * a_stage_bytes + m * m_bytes, &p.tm_a, a_full(a_st), cch,
+                                                (t.ow0 + m * p.bw) * p.sw - p.pl + kx, t.oh0 * p.sh - p.pt + ky, t.img);
+                            }
                             if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; }
                             if (++kx == kws) { kx = 0; ++ky; }
                         }
+                        const long long c0 = prof ? clock64() : 0;
                         mbar_wait(b_empty(b_st), b_ph ^ 1);
-                        mbar_expect_tx(b_full(b_st), b_tx);
-                        tma_load_3d(b_base + b_st * b_stage_bytes, &p.tm_b, b_full(b_st), cch, wrow, tap);
+                        if (prof) w_empty += clock64() - c0;
+                        if (leader) {
+                            mbar_expect_tx(b_full(b_st), b_tx);
+                            tma_load_3d(b_base + b_st * b_stage_bytes, &p.tm_b, b_full(b_st), cch, wrow, tap);
+                        }
                         if (++b_st == b_stages) { b_st = 0; b_ph ^= 1; }
+#if EDE_UNIFORM_PRODUCER
+                        __syncwarp();
+#endif
                     }
                 }
             }
+            if (prof && lane == 0) p.prof[(size_t)blockIdx.x * 16 + 5] = (unsigned long long)w_empty;
         }
     } else if (warp == 1) {
         // ===================== MMA issuer: ONE thread; per (tap, chunk) step it waits for the operands, issues the
         // K steps that hold real channels and commits the stage back -- kept to a few dozen instructions because
         // narrow layers have only 1..2 MMAs (128..256 tensor-pipe cycles) per step
+#if EDE_UNIFORM_ISSUER
+        {
+            const bool leader = elect_one();
+#else
         if (lane == 0) {
+            const bool leader = true;
+#endif
             const int a_mode = p.a_mode, m_tiles = p.m_tiles, n_pad = p.n_pad, n_chunks = p.n_chunks, swap = p.swap;
             const int a_stages = p.a_stages, b_stages = p.b_stages, kws = p.kw_steps;
             const uint32_t ck16 = (uint32_t)p.ck_bytes >> 4;            // (bytes >> 4) units of the address field
@@ -403,9 +443,74 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
             int a_st = 0, a_ph = 0, b_st = 0, b_ph = 0, acc_st = 0, acc_ph = 0;
             uint32_t a_cur = a_base16, b_cur = b_base16;                 // descriptor low words of the current stages
             unsigned long long t_start = 0;
-            if (p.prof) t_start = gtime();
+            const bool prof = p.prof != nullptr;
+            long long w_ops = 0, w_acc = 0;
+            const long long c_start = prof ? clock64() : 0;
+            if (prof) t_start = gtime();
+            if (swap && a_mode == 0) {
+                // ---- operand-swapped, resident pixel tile: a weight stage holds b_group taps, so one wait and one
+                // commit cover b_group * ks MMAs (the per-step bookkeeping of this thread, not the tensor pipe, was
+                // the limit of the 5x5 decoder convs: tools/micro/mma_contend.cu, profiles/r01_issue_overhead.md)
+                const int T = p.b_group;
+                const uint32_t tap16 = (uint32_t)p.b_tx_bytes >> 4;
+                for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                    const long long ca = prof ? clock64() : 0;
+                    mbar_wait(acc_empty(acc_st), acc_ph ^ 1);
+                    if (prof) w_acc += clock64() - ca;
+                    tc_fence_after();
+                    const uint32_t d_base = tmem_addr + (uint32_t)(acc_st * p.acc_cols);
+                    uint32_t accum = 0;
+                    for (int chunk = 0; chunk < n_chunks; ++chunk) {
+                        const int ks = min(ksteps, (k_bytes - chunk * ck_bytes + 31) >> 5);
+                        mbar_wait(a_full(a_st), a_ph);
+                        uint32_t shift16 = 0;
+                        int kx = 0, tap_in_pass = 0;
+                        for (int tap0 = 0; tap0 < taps; tap0 += T) {
+                            const long long c0 = prof ? clock64() : 0;
+                            mbar_wait(b_full(b_st), b_ph);
+                            if (prof) w_ops += clock64() - c0;
+                            tc_fence_after();
+                            const int nt = min(T, taps - tap0);
+                            uint32_t bt = b_cur;
+                            for (int t = 0; t < nt; ++t) {
+                                const uint32_t a0 = a_cur + shift16;
+                                if (leader) {
+                                    if (ks == 4) {
+                                        tc_mma_bf16_w(d_base, bt, a0, desc_hi, idesc, accum);
+                                        tc_mma_bf16_w(d_base, bt + 2u, a0 + 2u, desc_hi, idesc, 1u);
+                                        tc_mma_bf16_w(d_base, bt + 4u, a0 + 4u, desc_hi, idesc, 1u);
+                                        tc_mma_bf16_w(d_base, bt + 6u, a0 + 6u, desc_hi, idesc, 1u);
+                                    } else {
+                                        tc_mma_bf16_w(d_base, bt, a0, desc_hi, idesc, accum);
+                                        if (ks > 1) tc_mma_bf16_w(d_base, bt + 2u, a0 + 2u, desc_hi, idesc, 1u);
+                                        if (ks > 2) tc_mma_bf16_w(d_base, bt + 4u, a0 + 4u, desc_hi, idesc, 1u);
+                                    }
+                                }
+                                accum = 1;
+                                bt += tap16;
+                                shift16 += kx_step16;
+                                if (++kx == kws) { kx = 0; shift16 += ky_step16; }
+                                if (++tap_in_pass == sp_taps) { tap_in_pass = 0; shift16 = 0; kx = 0; }
+                            }
+                            if (leader) tc_commit(b_empty(b_st));
+#if EDE_UNIFORM_ISSUER
+                            __syncwarp();
+#endif
+                            b_cur += b_stage16;
+                            if (++b_st == b_stages) { b_st = 0; b_ph ^= 1; b_cur = b_base16; }
+                        }
+                        if (leader) tc_commit(a_empty(a_st));
+                        a_cur += a_stage16;
+                        if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; a_cur = a_base16; }
+                    }
+                    if (leader) tc_commit(acc_full(acc_st));
+                    if (++acc_st == 2) { acc_st = 0; acc_ph ^= 1; }
+                }
+            } else
             for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+                const long long ca = prof ? clock64() : 0;
                 mbar_wait(acc_empty(acc_st), acc_ph ^ 1);                // epilogue has drained this accumulator stage
+                if (prof) w_acc += clock64() - ca;
                 tc_fence_after();
                 const uint32_t d_base = tmem_addr + (uint32_t)(acc_st * p.acc_cols);
                 uint32_t accum = 0;
@@ -416,33 +521,40 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                     uint32_t shift16 = 0;
                     int kx = 0, tap_in_pass = 0;
                     for (int tap = 0; tap < taps; ++tap) {
+                        const long long c0 = prof ? clock64() : 0;
                         if (a_mode != 0) mbar_wait(a_full(a_st), a_ph);
                         mbar_wait(b_full(b_st), b_ph);
+                        if (prof) w_ops += clock64() - c0;
                         tc_fence_after();
                         const uint32_t a0 = a_cur + shift16, b0 = b_cur;
-                        if (swap) {
-                            // D[cout lanes][pixel columns] += W[128 x 16] . X[n_cols x 16]^T
-                            tc_mma_bf16_w(d_base, b0, a0, desc_hi, idesc, accum);
-                            if (ks > 1) tc_mma_bf16_w(d_base, b0 + 2u, a0 + 2u, desc_hi, idesc, 1u);
-                            if (ks > 2) tc_mma_bf16_w(d_base, b0 + 4u, a0 + 4u, desc_hi, idesc, 1u);
-                            if (ks > 3) tc_mma_bf16_w(d_base, b0 + 6u, a0 + 6u, desc_hi, idesc, 1u);
-                        } else {
-                            uint32_t am = a0, dm = d_base;
-                            for (int m = 0; m < m_tiles; ++m) {
-                                tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, accum);
-                                if (ks > 1) tc_mma_bf16_w(dm, am + 2u, b0 + 2u, desc_hi, idesc, 1u);
-                                if (ks > 2) tc_mma_bf16_w(dm, am + 4u, b0 + 4u, desc_hi, idesc, 1u);
-                                if (ks > 3) tc_mma_bf16_w(dm, am + 6u, b0 + 6u, desc_hi, idesc, 1u);
-                                am += m_step16;
-                                dm += (uint32_t)n_pad;
+                        if (leader) {
+                            if (swap) {
+                                // D[cout lanes][pixel columns] += W[128 x 16] . X[n_cols x 16]^T
+                                tc_mma_bf16_w(d_base, b0, a0, desc_hi, idesc, accum);
+                                if (ks > 1) tc_mma_bf16_w(d_base, b0 + 2u, a0 + 2u, desc_hi, idesc, 1u);
+                                if (ks > 2) tc_mma_bf16_w(d_base, b0 + 4u, a0 + 4u, desc_hi, idesc, 1u);
+                                if (ks > 3) tc_mma_bf16_w(d_base, b0 + 6u, a0 + 6u, desc_hi, idesc, 1u);
+                            } else {
+                                uint32_t am = a0, dm = d_base;
+                                for (int m = 0; m < m_tiles; ++m) {
+                                    tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, accum);
+                                    if (ks > 1) tc_mma_bf16_w(dm, am + 2u, b0 + 2u, desc_hi, idesc, 1u);
+                                    if (ks > 2) tc_mma_bf16_w(dm, am + 4u, b0 + 4u, desc_hi, idesc, 1u);
+                                    if (ks > 3) tc_mma_bf16_w(dm, am + 6u, b0 + 6u, desc_hi, idesc, 1u);
+                                    am += m_step16;
+                                    dm += (uint32_t)n_pad;
+                                }
                             }
+                            tc_commit(b_empty(b_st));
+                            if (a_mode != 0) tc_commit(a_empty(a_st));
                         }
-                        tc_commit(b_empty(b_st));
+#if EDE_UNIFORM_ISSUER
+                        __syncwarp();
+#endif
                         accum = 1;
                         b_cur += b_stage16;
                         if (++b_st == b_stages) { b_st = 0; b_ph ^= 1; b_cur = b_base16; }
                         if (a_mode != 0) {
-                            tc_commit(a_empty(a_st));
                             a_cur += a_stage16;
                             if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; a_cur = a_base16; }
                         } else {
@@ -452,17 +564,18 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                         }
                     }
                     if (a_mode == 0) {
-                        tc_commit(a_empty(a_st));
+                        if (leader) tc_commit(a_empty(a_st));
                         a_cur += a_stage16;
                         if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; a_cur = a_base16; }
                     }
                 }
-                tc_commit(acc_full(acc_st));
+                if (leader) tc_commit(acc_full(acc_st));
                 if (++acc_st == 2) { acc_st = 0; acc_ph ^= 1; }
             }
-            if (p.prof) {
-                unsigned long long* q = p.prof + (size_t)blockIdx.x * 8;
-                q[1] = t_start; q[2] = gtime(); q[4] = 0; q[5] = 0;
+            if (p.prof && lane == 0) {
+                unsigned long long* q = p.prof + (size_t)blockIdx.x * 16;
+                q[1] = t_start; q[2] = gtime(); q[4] = (unsigned long long)w_ops; q[8] = (unsigned long long)w_acc;
+                q[12] = (unsigned long long)(clock64() - c_start);
             }
         }
     } else {
@@ -472,7 +585,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
         const int r = quarter * 32 + lane;
         const int et = threadIdx.x - 64;              // 0..EPI_THREADS-1
         int acc_st = 0, acc_ph = 0, n_done = 0;
-        long long w_full = 0;
+        long long w_full = 0, ph_clk[3] = {0, 0, 0};
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
             const TileCoord t = decode_tile(p, tile);
             epi_bar_sync();                           // everyone is done with the previous tile's scale/shift
@@ -493,7 +606,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                 float* const s_stage = s_shift + 256 + half * (2 * STG_FLOATS);
                 const int tid_h = (warp - 2 - 4 * half) * 32 + lane;
                 const uint32_t t_col = t_base;
-                epilogue_swapped<TY, ACT, RES>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift);
+                epilogue_swapped<TY, ACT, RES>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift,
+                                               p.prof ? ph_clk : nullptr);
             } else {
                 const int nch = p.n_pad >> 4;         // 16-column chunks of one accumulator row (n_pad % 16 == 0)
                 for (int m = 0; m < p.m_tiles; ++m) {
@@ -524,14 +638,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
             ++n_done;
         }
         if (p.prof && et == 0) {
-            unsigned long long* q = p.prof + (size_t)blockIdx.x * 8;
+            unsigned long long* q = p.prof + (size_t)blockIdx.x * 16;
             q[3] = gtime(); q[6] = (unsigned long long)w_full; q[7] = (unsigned long long)n_done;
+            q[9] = (unsigned long long)ph_clk[0]; q[10] = (unsigned long long)ph_clk[1]; q[11] = (unsigned long long)ph_clk[2];
         }
     }
 
     tc_fence_before();
     __syncthreads();
-    if (p.prof && threadIdx.x == 0) p.prof[(size_t)blockIdx.x * 8] = prof_t0;
+    if (p.prof && threadIdx.x == 0) p.prof[(size_t)blockIdx.x * 16] = prof_t0;
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_addr),
@@ -714,6 +829,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     // Packed tiles use N = 240 so that those shifted reads stay inside the 256-column accumulator stage.
     const int force_swap = env_int("EDE_UMMA_SWAP", -1);
     const int force_pack = env_int("EDE_UMMA_PACK", -1);
+    const int force_group = env_int("EDE_UMMA_GROUP", 0);
     if (n16 <= 128 && force_swap != 0) {
         if (force_swap == 1) best_time = 1e300;
         const int gs[3] = {4, 2, 1};
@@ -751,7 +867,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                     best.swap = 1;
                     best.pack_g = G;
                     best.ck = ck; best.swizzle = ck_bytes; best.n_pad = 128; best.n_tiles = 1;
-                    best.b_stage_bytes = b_bytes;
+                    if (best.b_stage_bytes == 0) best.b_stage_bytes = b_bytes;
                     best.useful_frac = cand.useful_frac * ((double)a.cin_p / (ks_total * 16)) *
                                        ((double)a.cout_p * a.kw / (128.0 * kws));
                 }
@@ -785,11 +901,18 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                         if (m_need + G - 1 > n_cols) break;
                         const int rows_alloc = std::max(box_rows * P, n_cols + (a.kh - 1) * P + kws * G);
                         const int a_bytes = round_up(rows_alloc * ck_bytes, 1024);
-                        const int b_stages = fit_stages(2 * a_bytes, b_bytes, 4);
+                        // taps per weight stage: as many as still leave three stages (one wait + one commit per
+                        // stage; the issuing thread's bookkeeping per stage costs about as much as four MMAs)
+                        int grp = 1;
+                        for (int t = (w_rows_box * ck_bytes) % 1024 ? 1 : std::min(steps, force_group > 0 ? force_group : 6); t > 1; --t)
+                            if (fit_stages(2 * a_bytes, round_up(t * w_rows_box * ck_bytes, 1024), 4) >= 3) { grp = t; break; }
+                        const int b_grp_bytes = round_up(grp * w_rows_box * ck_bytes, 1024);
+                        const int b_stages = fit_stages(2 * a_bytes, b_grp_bytes, 4);
                         if (b_stages < 3) continue;
                         EdeUmmaCfg cand{};
                         cand.a_mode = 0; cand.bh = bh; cand.bw = bw; cand.pitch = P; cand.box_rows = box_rows;
                         cand.m_tiles = 2; cand.a_stages = 2; cand.b_stages = b_stages; cand.a_stage_bytes = a_bytes;
+                        cand.b_stage_bytes = b_grp_bytes;
                         cand.tiles_w = ceil_div(OW, bw); cand.tiles_h = ceil_div(OH, bh);
                         cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * n_cols);
                         consider(cand, (double)n_chunks * box_rows * P * ck_bytes);
@@ -873,7 +996,11 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
                               (cuuint64_t)(a.kh * a.kw * a.w_passes)};
         cuuint64_t strides[2] = {(cuuint64_t)a.w_umma_cin_p * 2, (cuuint64_t)a.w_umma_cin_p * 2 * a.w_umma_cout_p};
         const int w_rows_box = c.swap ? (c.pack_g > 1 ? 128 : std::min(128, round_up(a.cout_p, 8))) : c.n_pad;
-        cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)w_rows_box, 1};
+        // taps per weight stage: the stage size the tile picker chose, in units of one tap's box
+        const int b_group = (c.swap && c.a_mode == 0 && (w_rows_box * c.ck * 2) % 1024 == 0)
+                                ? std::max(1, c.b_stage_bytes / (w_rows_box * c.ck * 2)) : 1;
+        p.b_group = b_group;
+        cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)w_rows_box, (cuuint32_t)b_group};
         dims[2] = (cuuint64_t)(a.kh * ceil_div(a.kw, c.pack_g) * a.w_passes);
         cuuint32_t es[3] = {1, 1, 1};
         CUresult r = enc(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, (void*)a.w_umma, dims, strides, box, es,
@@ -923,8 +1050,9 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     const int n_cta = std::min(p.total_tiles, std::max(1, sm_count[dev]));
     static unsigned long long* prof_buf = nullptr;
     static const int prof_on = env_int("EDE_UMMA_PROF", 0);
+
     if (prof_on) {
-        if (!prof_buf && cudaMalloc(&prof_buf, (size_t)4096 * 8 * sizeof(unsigned long long)) != cudaSuccess)
+        if (!prof_buf && cudaMalloc(&prof_buf, (size_t)4096 * 16 * sizeof(unsigned long long)) != cudaSuccess)
             prof_buf = nullptr;
         p.prof = (prof_buf && n_cta <= 4096) ? prof_buf : nullptr;
         g_prof_last = p.prof;
@@ -958,13 +1086,14 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
 extern "C" {
 
 /* debug hook (EDE_UMMA_PROF=1): copies the per-CTA globaltimer stamps of the LAST tcgen05 conv launch
- * (8 per CTA: entry, mainloop start, first operands landed, last MMA issued, accumulator ready,
- * epilogue done, CTA done, unused) to `host`; returns the number of CTAs (0 when profiling is off). */
+ * (8 u64 per CTA: [0] entry, [1] issuer start, [2] issuer end, [3] epilogue end (globaltimer ns); [4] cycles the
+ * issuer waited for operand stages, [5] cycles the producer waited for free weight stages, [6] cycles the epilogue
+ * waited for accumulators, [7] tiles done) to `host`; returns the number of CTAs (0 when profiling is off). */
 int64_t ede_debug_umma_prof(unsigned long long* host, int64_t max_ctas) {
     if (!ede::g_prof_last || !host) return 0;
     cudaDeviceSynchronize();
     size_t n = ede::g_prof_ctas < (size_t)max_ctas ? ede::g_prof_ctas : (size_t)max_ctas;
-    cudaMemcpy(host, ede::g_prof_last, n * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    cudaMemcpy(host, ede::g_prof_last, n * 16 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
     return (int64_t)n;
 }
 

@@ -32,20 +32,24 @@ def main():
         for _ in range(2):
             A.check(lib.ede_plan_run(one, 1, st))
         torch.cuda.synchronize()
-        buf = np.zeros((4096, 8), dtype=np.uint64)
+        buf = np.zeros((4096, 16), dtype=np.uint64)
         k = lib.ede_debug_umma_prof(buf.ctypes.data, 4096)
         t = buf[:k].astype(np.int64)
         cfg = A.umma_config(plan.structs[i])
         span = (t[:, 3].max() - t[:, 0].min()) / 1e3
         mma = (t[:, 2] - t[:, 1]) / 1e3
-        clk = 1.9e3                                    # cycles per us (approx.)
+        clk = float(np.median(t[:, 12] / np.maximum(t[:, 2] - t[:, 1], 1)) * 1e3)   # SM cycles per us while this kernel ran
+        print(f"   SM clock while the kernel ran: {clk:.0f} MHz; issuer {np.median(t[:, 12]) / max(1.0, float(np.median(t[:, 7]))):.0f} clk per tile")
         print(f"{tag}: {k} persistent CTAs x {np.median(t[:, 7]):.0f} tiles, kernel span {span:.1f} us; "
               f"mode={'res' if cfg.a_mode == 0 else 'tap'} ck={cfg.ck} tile={cfg.bh}x{cfg.bw} mt={cfg.m_tiles} "
               f"n_pad={cfg.n_pad}x{cfg.n_tiles} stages={cfg.a_stages}/{cfg.b_stages} smem={cfg.smem_bytes >> 10}K "
               f"tmem={cfg.tmem_cols}")
         print(f"   MMA warp busy span       median {np.median(mma):9.1f} us")
-        print(f"   ... waiting for operands median {np.median(t[:, 4]) / clk:9.1f} us")
-        print(f"   ... waiting for epilogue median {np.median(t[:, 5]) / clk:9.1f} us")
+        print(f"   issuer waiting for weight/pixel stages median {np.median(t[:, 4]) / clk:9.1f} us")
+        print(f"   producer waiting for free weight stages median {np.median(t[:, 5]) / clk:9.1f} us")
+        print(f"   issuer waiting for a drained accumulator median {np.median(t[:, 8]) / clk:9.1f} us")
+        print(f"   swapped epilogue (warp 2): barrier {np.median(t[:, 9]) / clk:.1f} us, finish+store {np.median(t[:, 10]) / clk:.1f} us, "
+              f"ld wait+stage {np.median(t[:, 11]) / clk:.1f} us")
         print(f"   epilogue waiting for MMA median {np.median(t[:, 6]) / clk:9.1f} us")
         print(f"   epilogue end - MMA end   median {np.median(t[:, 3] - t[:, 2]) / 1e3:9.1f} us")
 
