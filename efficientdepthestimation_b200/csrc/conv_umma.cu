@@ -214,24 +214,31 @@ __device__ __forceinline__ void epilogue_row(const UmmaParams& p, uint32_t t_row
 // The four warps of a half-set (one per TMEM lane quarter) stage 16 window positions at a time in a shared
 // [16][128] fp32 tile -- the warp that holds tap slot j reads its columns j further right, so row k of the tile
 // holds, for every j, the partial sum that belongs to output position c0 + k -- and after one named barrier all
-// 128 threads finish 8-channel vectors of one pixel: sum over the tap slots, folded BN, residual, activation,
-// 16/32-byte stores that are contiguous along the channels of a pixel.  Two tiles alternate (one barrier/chunk).
+// 128 threads finish 4-channel units of one pixel: sum over the G tap slots, folded BN, residual, activation,
+// 8/16-byte stores that are contiguous along the channels of a pixel.  Two tiles alternate (one barrier/chunk).
+// A thread always finishes the same 4 channels (scale/shift live in registers) and finds its pixel through a
+// 256-entry window-position table built once per kernel: the finishing loop carries no divisions.
 constexpr int STG_PITCH = 132;               // floats per staged window position (128 lanes + 4: no bank conflicts)
 constexpr int STG_FLOATS = 16 * STG_PITCH;
 
-template <typename TY, int ACT, bool RES>
+template <typename TY, int ACT, bool RES, int G>
 __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const TileCoord& t, uint32_t t_base, int quarter,
                                                  int half, int lane, int tid_h, float* s_stage, const float* s_scale,
-                                                 const float* s_shift, long long* ph) {
-    const int wrap = p.a_mode == 0 ? p.pitch : p.bw;
-    const uint32_t wrap_inv = 65536u / (uint32_t)wrap + 1u;   // f / wrap for f < 256 (one correction step below)
-    const int cg = 128 / p.pack_g;                           // channels per tap slot (32 / 64 / 128)
-    const int j = (quarter * 32) / cg;                       // tap slot of this warp's 32 lanes
-    const bool live = quarter * 32 - j * cg < p.cout_p;      // do these lanes hold real output channels?
+                                                 const float* s_shift, const uint16_t* s_lut, long long* ph) {
+    constexpr int CG = 128 / G;                              // channels per tap slot (128 / 64 / 32)
+    constexpr int UPP = CG / 4;                              // 4-channel units per staged position: 32 / 16 / 8
+    constexpr int UPT = 16 * UPP / 128;                      // units per thread and chunk: 4 / 2 / 1
+    constexpr int PSTEP = 128 / UPP;                         // positions between two units of a thread: 4 / 8 / 16
+    const int j = (quarter * 32) / CG;                       // tap slot of this warp's 32 lanes
+    const bool live = quarter * 32 - j * CG < p.cout_p;      // do these lanes hold real output channels?
     const int r = quarter * 32 + lane;
-    const int upp = cg >> 2;                                 // 4-channel units per staged position: 8 / 16 / 32
-    const int upp_lg = 31 - __clz(upp);
-    const int upt = (16 * upp) >> 7;                         // units per thread and chunk: 1 / 2 / 4
+    const int c = (tid_h & (UPP - 1)) << 2;                  // this thread's four channels, the same for every unit
+    const int pj0 = tid_h / UPP;
+    const bool c_live = c < p.cout_p;
+    const float4 sc = *reinterpret_cast<const float4*>(s_scale + c), sf = *reinterpret_cast<const float4*>(s_shift + c);
+    const bool act_on = ACT != EDE_ACT_NONE && c < p.act_c_end;        // act_c_end is a multiple of 8
+    const float* const src0 = s_stage + pj0 * STG_PITCH + c;
+    const long long img_row0 = (long long)t.img * p.oh;
     const int step = 16 * (EPI_WARPS / 4);
     uint32_t acc[16];
     if (live) {                                              // chunk 0 -> staging tile 0
@@ -242,44 +249,40 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
     }
     int it = 0;
     for (int c0 = half * 16; c0 < p.n_cols; c0 += step, ++it) {
-        const float* const buf = s_stage + (it & 1) * STG_FLOATS;
+        const float* const buf = src0 + (it & 1) * STG_FLOATS;
         const bool next = live && c0 + step < p.n_cols;
         if (next) tc_ld16(t_base + (uint32_t)(c0 + step + j), acc);      // in flight across the barrier and phase 2
         const long long c_a = ph ? clock64() : 0;
         if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
         else asm volatile("bar.sync 3, 128;" ::: "memory");
         const long long c_b = ph ? clock64() : 0;
-        for (int k = 0; k < upt; ++k) {
-            const int u = tid_h + (k << 7);
-            const int pj = u >> upp_lg, c = (u & (upp - 1)) << 2;
-            if (c >= p.cout_p) continue;
-            int f = c0 + pj, owb = t.ow0;                    // window position -> output pixel
-            if (p.a_mode != 0) { owb += (f >> 7) * p.bw; f &= 127; }
-            int fr = (int)(((uint32_t)f * wrap_inv) >> 16);
-            if (fr * wrap > f) --fr;
-            const int fc = f - fr * wrap;
-            const int oh = t.oh0 + fr, ow = owb + fc;
-            if (!(fc < p.bw && fr < p.bh && oh < p.oh && ow < p.ow)) continue;
-            const long long pix = ((long long)t.img * p.oh + oh) * p.ow + ow;
-            const float* src = buf + pj * STG_PITCH + c;
-            float4 a4 = *reinterpret_cast<const float4*>(src);
-            for (int jj = 1; jj < p.pack_g; ++jj) {
-                const float4 b4 = *reinterpret_cast<const float4*>(src + jj * cg);
-                a4.x += b4.x; a4.y += b4.y; a4.z += b4.z; a4.w += b4.w;
-            }
-            const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c), f0 = *reinterpret_cast<const float4*>(s_shift + c);
-            float v[4] = {fmaf(a4.x, s0.x, f0.x), fmaf(a4.y, s0.y, f0.y), fmaf(a4.z, s0.z, f0.z), fmaf(a4.w, s0.w, f0.w)};
-            if (RES) {
-                float rs[4];
-                load4<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co, c, rs);
+        if (c_live) {
 #pragma unroll
-                for (int q = 0; q < 4; ++q) v[q] += rs[q];
-            }
-            if (ACT != EDE_ACT_NONE && c < p.act_c_end) {    // act_c_end is a multiple of 8
+            for (int k = 0; k < UPT; ++k) {
+                const uint32_t e = s_lut[c0 + pj0 + k * PSTEP];          // window position -> (row, column) of the tile
+                const int oh = t.oh0 + (int)(e >> 8), ow = t.ow0 + (int)(e & 255u);
+                if (e == 0xffffu || oh >= p.oh || ow >= p.ow) continue;
+                const long long pix = (img_row0 + oh) * p.ow + ow;
+                const float* src = buf + k * PSTEP * STG_PITCH;
+                float4 a4 = *reinterpret_cast<const float4*>(src);
 #pragma unroll
-                for (int q = 0; q < 4; ++q) v[q] = ACT == ACT_RUNTIME ? apply_act(v[q], p.act) : act_ct<ACT>(v[q]);
+                for (int jj = 1; jj < G; ++jj) {
+                    const float4 b4 = *reinterpret_cast<const float4*>(src + jj * CG);
+                    a4.x += b4.x; a4.y += b4.y; a4.z += b4.z; a4.w += b4.w;
+                }
+                float v[4] = {fmaf(a4.x, sc.x, sf.x), fmaf(a4.y, sc.y, sf.y), fmaf(a4.z, sc.z, sf.z), fmaf(a4.w, sc.w, sf.w)};
+                if (RES) {
+                    float rs[4];
+                    load4<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co, c, rs);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) v[q] += rs[q];
+                }
+                if (act_on) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) v[q] = ACT == ACT_RUNTIME ? apply_act(v[q], p.act) : act_ct<ACT>(v[q]);
+                }
+                store4<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co, c, v);
             }
-            store4<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co, c, v);
         }
         const long long c_c = ph ? clock64() : 0;
         if (ph) { ph[0] += c_b - c_a; ph[1] += c_c - c_b; }
@@ -313,6 +316,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
     const uint32_t tmem_slot = bar_base + 8u * (4 * MAX_STAGES + 4);
     float* const s_scale = reinterpret_cast<float*>(smem_raw + (bar_base - smem_u32(smem_raw)) + 512);
     float* const s_shift = s_scale + 256;
+    // swapped mode (n_pad = 128 uses half of the scale area): window position -> (tile row << 8 | tile column)
+    uint16_t* const s_lut = reinterpret_cast<uint16_t*>(s_scale + 128);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int sp_taps = p.kh * p.kw_steps;        // spatial steps (kw_steps = kw unless taps are packed on M)
@@ -334,6 +339,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                      "r"((uint32_t)p.tmem_cols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (p.swap) {
+        for (int f = threadIdx.x; f < 256; f += NUM_THREADS) {
+            int dy, dx;
+            bool ok = true;
+            if (p.a_mode == 0) { dy = f / p.pitch; dx = f - dy * p.pitch; ok = dx < p.bw && dy < p.bh; }
+            else { const int g = f & 127; dy = g / p.bw; dx = (f >> 7) * p.bw + g - dy * p.bw; }
+            s_lut[f] = ok ? (uint16_t)((dy << 8) | dx) : (uint16_t)0xffffu;
+        }
     }
     if (p.a_mode == 0) {
         // The shifted UMMA windows of the resident mode read past the TMA box (into the tail of the stage, never
@@ -588,14 +602,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
         long long w_full = 0, ph_clk[3] = {0, 0, 0};
         for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
             const TileCoord t = decode_tile(p, tile);
-            epi_bar_sync();                           // everyone is done with the previous tile's scale/shift
-            for (int e = et; e < p.n_pad; e += EPI_THREADS) {
-                const int c = t.ntile * p.n_pad + e;
-                const bool in = c < p.cout_p;
-                s_scale[e] = in ? __ldg(p.scale + c) : 0.f;
-                s_shift[e] = in ? __ldg(p.shift + c) : 0.f;
+            if (!p.swap || n_done == 0) {             // the swapped form has one n-tile: loaded once
+                epi_bar_sync();                       // everyone is done with the previous tile's scale/shift
+                for (int e = et; e < p.n_pad; e += EPI_THREADS) {
+                    const int c = t.ntile * p.n_pad + e;
+                    const bool in = c < p.cout_p;
+                    s_scale[e] = in ? __ldg(p.scale + c) : 0.f;
+                    s_shift[e] = in ? __ldg(p.shift + c) : 0.f;
+                }
+                epi_bar_sync();
             }
-            epi_bar_sync();
             const long long c0 = p.prof ? clock64() : 0;
             mbar_wait(acc_full(acc_st), acc_ph);
             if (p.prof) w_full += clock64() - c0;
@@ -606,8 +622,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                 float* const s_stage = s_shift + 256 + half * (2 * STG_FLOATS);
                 const int tid_h = (warp - 2 - 4 * half) * 32 + lane;
                 const uint32_t t_col = t_base;
-                epilogue_swapped<TY, ACT, RES>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift,
-                                               p.prof ? ph_clk : nullptr);
+                long long* const phc = p.prof ? ph_clk : nullptr;
+                if (p.pack_g == 4)
+                    epilogue_swapped<TY, ACT, RES, 4>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift, s_lut, phc);
+                else if (p.pack_g == 2)
+                    epilogue_swapped<TY, ACT, RES, 2>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift, s_lut, phc);
+                else
+                    epilogue_swapped<TY, ACT, RES, 1>(p, t, t_col, quarter, half, lane, tid_h, s_stage, s_scale, s_shift, s_lut, phc);
             } else {
                 const int nch = p.n_pad >> 4;         // 16-column chunks of one accumulator row (n_pad % 16 == 0)
                 for (int m = 0; m < p.m_tiles; ++m) {
