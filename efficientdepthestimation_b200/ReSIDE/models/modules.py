@@ -19,6 +19,7 @@ from ...engine import EdeModule, cat_views, emit
 
 _LOWRES_UPCONV = os.environ.get("EDE_LOWRES_UPCONV", "1") != "0"
 _LOWRES_MIN_CIN = int(os.environ.get("EDE_LOWRES_MIN_CIN", "192"))        # for moderate upsampling (4x in area)
+_ADD_AS_TAP_MAX_LANES = 64     # [x1 | bran2] lanes up to which conv1_2 + add run as one GEMM (fits one 64-channel chunk)
 _LOWRES_MIN_CIN_BIG = int(os.environ.get("EDE_LOWRES_MIN_CIN_BIG", "32"))  # for >= 8x in area: z is tiny
 
 
@@ -47,6 +48,9 @@ class _UpProjection(EdeModule, nn.Sequential):
             x = g.resize(x, size, tag=tag + ".resize")
             pair = g.conv(x, parts, 1, (2, 2, 2, 2), A.ACT_RELU, tag=tag + ".conv1+conv2")
         half = pair.c_p // 2
+        if g.precision != "fp32" and pair.c_p <= _ADD_AS_TAP_MAX_LANES:
+            # narrow projection: the bran2 half rides along as extra input channels with an identity centre tap
+            return g.conv_bn_act_add(pair, self.conv1_2, self.bn1_2, A.ACT_RELU, out=out, tag=tag + ".conv1_2")
         return g.conv_bn_act(pair.slice(0, half), self.conv1_2, self.bn1_2, A.ACT_RELU,
                              res=pair.slice(half, half), out=out, tag=tag + ".conv1_2")
 

@@ -240,6 +240,24 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
     const float* const src0 = s_stage + pj0 * STG_PITCH + c;
     const long long img_row0 = (long long)t.img * p.oh;
     const int step = 16 * (EPI_WARPS / 4);
+    // where the units of chunk c0 go; the residual is fetched one chunk ahead so that its latency hides behind the
+    // staging barrier and the previous chunk's stores
+    long long pix[UPT];
+    uint32_t okm = 0;
+    float rs[UPT][4];
+    auto locate = [&](int c0) {
+        okm = 0;
+#pragma unroll
+        for (int k = 0; k < UPT; ++k) {
+            const uint32_t e = c_live && c0 < p.n_cols ? s_lut[c0 + pj0 + k * PSTEP] : 0xffffu;   // position -> tile (row, col)
+            const int oh = t.oh0 + (int)(e >> 8), ow = t.ow0 + (int)(e & 255u);
+            const bool in = e != 0xffffu && oh < p.oh && ow < p.ow;
+            okm |= in ? 1u << k : 0u;
+            pix[k] = (img_row0 + oh) * p.ow + ow;
+            if (RES && in) load4<TY>(reinterpret_cast<const TY*>(p.res) + pix[k] * p.res_cs + p.res_co, c, rs[k]);
+        }
+    };
+    locate(half * 16);
     uint32_t acc[16];
     if (live) {                                              // chunk 0 -> staging tile 0
         tc_ld16(t_base + (uint32_t)(half * 16 + j), acc);
@@ -256,13 +274,10 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
         if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
         else asm volatile("bar.sync 3, 128;" ::: "memory");
         const long long c_b = ph ? clock64() : 0;
-        if (c_live) {
+        {
 #pragma unroll
             for (int k = 0; k < UPT; ++k) {
-                const uint32_t e = s_lut[c0 + pj0 + k * PSTEP];          // window position -> (row, column) of the tile
-                const int oh = t.oh0 + (int)(e >> 8), ow = t.ow0 + (int)(e & 255u);
-                if (e == 0xffffu || oh >= p.oh || ow >= p.ow) continue;
-                const long long pix = (img_row0 + oh) * p.ow + ow;
+                if (!(okm >> k & 1u)) continue;
                 const float* src = buf + k * PSTEP * STG_PITCH;
                 float4 a4 = *reinterpret_cast<const float4*>(src);
 #pragma unroll
@@ -272,17 +287,16 @@ __device__ __forceinline__ void epilogue_swapped(const UmmaParams& p, const Tile
                 }
                 float v[4] = {fmaf(a4.x, sc.x, sf.x), fmaf(a4.y, sc.y, sf.y), fmaf(a4.z, sc.z, sf.z), fmaf(a4.w, sc.w, sf.w)};
                 if (RES) {
-                    float rs[4];
-                    load4<TY>(reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co, c, rs);
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) v[q] += rs[q];
+                    for (int q = 0; q < 4; ++q) v[q] += rs[k][q];
                 }
                 if (act_on) {
 #pragma unroll
                     for (int q = 0; q < 4; ++q) v[q] = ACT == ACT_RUNTIME ? apply_act(v[q], p.act) : act_ct<ACT>(v[q]);
                 }
-                store4<TY>(reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co, c, v);
+                store4<TY>(reinterpret_cast<TY*>(p.y) + pix[k] * p.y_cs + p.y_co, c, v);
             }
+            locate(c0 + step);
         }
         const long long c_c = ph ? clock64() : 0;
         if (ph) { ph[0] += c_b - c_a; ph[1] += c_c - c_b; }
@@ -877,7 +891,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                 const double mma = (double)steps * ks_total * t_mma;
                 const double w_rows = G > 1 ? 128.0 : (double)std::min(128, round_up(a.cout_p, 8));
                 const double mem = (a_bytes_tile + (double)steps * n_chunks * w_rows * ck_bytes) / L2_BYTES_PER_CLK_PER_SM;
-                const double epi = 16.0 * 220.0 + 600.0;
+                const double epi = 16.0 * 350.0 + 600.0;      // 2 x 8 staged chunks, each a ~500-cycle dependent chain (measured)
                 const double per_stage = mma / std::max(1, n_chunks * steps);
                 const double lat = std::max(0.0, 1500.0 - cand.b_stages * per_stage) * 0.15 * n_chunks * steps /
                                    std::max(1, cand.b_stages);

@@ -330,6 +330,27 @@ class Graph:
         self.exec_flops += fl
         return out
 
+    def conv_bn_act_add(self, pair: View, conv, bn, act, out: Optional[View] = None, tag="conv") -> View:
+        """act(bn(conv(pair[:, :cin])) + pair[:, cin:]) -- the tail of an _UpProjection (modules.py:38-45 of the
+        reference) -- as ONE GEMM without a residual read in the epilogue: the branch to add enters as `cout` extra
+        input channels whose only non-zero weight is an exact 1.0 on the centre tap.  For that the BN scale moves
+        from the epilogue into the conv weights (rounded to bf16 like the weights themselves).  The extra K is free
+        while cin + cout still fits the channel chunk the conv would use anyway, so callers use it for narrow convs."""
+        wt = conv.weight
+        co, ci, kh, kw = (int(v) for v in wt.shape)
+        if pair.c != ci + co or conv.stride[0] != 1 or kh % 2 == 0 or kw % 2 == 0:
+            raise RuntimeError(f"{tag}: conv_bn_act_add needs [conv input | branch] channels and an odd stride-1 kernel")
+        sc, sf = P.fold_bn(co, _bn_dict(bn), conv.bias, wt.device)
+        w = torch.zeros(co, ci + co, kh, kw, dtype=torch.float32, device=wt.device)
+        w[:, :ci] = wt.detach().float() * sc.view(-1, 1, 1, 1)
+        idx = torch.arange(co, device=wt.device)
+        w[idx, ci + idx, kh // 2, kw // 2] = 1.0
+        before = self.flops
+        y = self.conv(pair, [(w, None, sf, act != A.ACT_NONE)], 1, _pad4(conv), act, None, out, tag=tag)
+        if self.count_ref_flops:                  # the reference does a cin-channel conv and an elementwise add
+            self.flops = before + 2.0 * pair.n * y.h * y.w * co * ci * kh * kw
+        return y
+
     def conv_bn_act(self, x: View, conv, bn=None, act=A.ACT_NONE, res=None, out=None, relu_in=False,
                     out_dtype=None, tag="conv") -> View:
         """nn.Conv2d (+ nn.BatchNorm2d) (+ activation) as one fused operator."""
