@@ -475,8 +475,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
             long long w_ops = 0, w_acc = 0;
             const long long c_start = prof ? clock64() : 0;
             if (prof) t_start = gtime();
-            if (swap && a_mode == 0) {
-                // ---- operand-swapped, resident pixel tile: a weight stage holds b_group taps, so one wait and one
+            if (a_mode == 0) {
+                // ---- resident pixel tile (either orientation): a weight stage holds b_group taps, so one wait and one
                 // commit cover b_group * ks MMAs (the per-step bookkeeping of this thread, not the tensor pipe, was
                 // the limit of the 5x5 decoder convs: tools/micro/mma_contend.cu, profiles/r01_issue_overhead.md)
                 const int T = p.b_group;
@@ -503,15 +503,34 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                             for (int t = 0; t < nt; ++t) {
                                 const uint32_t a0 = a_cur + shift16;
                                 if (leader) {
-                                    if (ks == 4) {
-                                        tc_mma_bf16_w(d_base, bt, a0, desc_hi, idesc, accum);
-                                        tc_mma_bf16_w(d_base, bt + 2u, a0 + 2u, desc_hi, idesc, 1u);
-                                        tc_mma_bf16_w(d_base, bt + 4u, a0 + 4u, desc_hi, idesc, 1u);
-                                        tc_mma_bf16_w(d_base, bt + 6u, a0 + 6u, desc_hi, idesc, 1u);
+                                    if (swap) {
+                                        // D[cout lanes][pixel columns] += W[128 x 16] . X[n_cols x 16]^T
+                                        if (ks == 4) {
+                                            tc_mma_bf16_w(d_base, bt, a0, desc_hi, idesc, accum);
+                                            tc_mma_bf16_w(d_base, bt + 2u, a0 + 2u, desc_hi, idesc, 1u);
+                                            tc_mma_bf16_w(d_base, bt + 4u, a0 + 4u, desc_hi, idesc, 1u);
+                                            tc_mma_bf16_w(d_base, bt + 6u, a0 + 6u, desc_hi, idesc, 1u);
+                                        } else {
+                                            tc_mma_bf16_w(d_base, bt, a0, desc_hi, idesc, accum);
+                                            if (ks > 1) tc_mma_bf16_w(d_base, bt + 2u, a0 + 2u, desc_hi, idesc, 1u);
+                                            if (ks > 2) tc_mma_bf16_w(d_base, bt + 4u, a0 + 4u, desc_hi, idesc, 1u);
+                                        }
                                     } else {
-                                        tc_mma_bf16_w(d_base, bt, a0, desc_hi, idesc, accum);
-                                        if (ks > 1) tc_mma_bf16_w(d_base, bt + 2u, a0 + 2u, desc_hi, idesc, 1u);
-                                        if (ks > 2) tc_mma_bf16_w(d_base, bt + 4u, a0 + 4u, desc_hi, idesc, 1u);
+                                        uint32_t am = a0, dm = d_base;
+                                        for (int m = 0; m < m_tiles; ++m) {
+                                            if (ks == 4) {
+                                                tc_mma_bf16_w(dm, am, bt, desc_hi, idesc, accum);
+                                                tc_mma_bf16_w(dm, am + 2u, bt + 2u, desc_hi, idesc, 1u);
+                                                tc_mma_bf16_w(dm, am + 4u, bt + 4u, desc_hi, idesc, 1u);
+                                                tc_mma_bf16_w(dm, am + 6u, bt + 6u, desc_hi, idesc, 1u);
+                                            } else {
+                                                tc_mma_bf16_w(dm, am, bt, desc_hi, idesc, accum);
+                                                if (ks > 1) tc_mma_bf16_w(dm, am + 2u, bt + 2u, desc_hi, idesc, 1u);
+                                                if (ks > 2) tc_mma_bf16_w(dm, am + 4u, bt + 4u, desc_hi, idesc, 1u);
+                                            }
+                                            am += m_step16;
+                                            dm += (uint32_t)n_pad;
+                                        }
                                     }
                                 }
                                 accum = 1;
@@ -751,6 +770,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     const int force_mode = env_int("EDE_UMMA_MODE", -1);
     const int force_ck = env_int("EDE_UMMA_CK", 0);
     const int force_npad = env_int("EDE_UMMA_NPAD", 0);
+    const int force_group = env_int("EDE_UMMA_GROUP", 0);
     const int n16 = round_up(a.cout_p, 16);
     const bool is_1x1 = a.kh == 1 && a.kw == 1 && a.sh == 1 && a.pt == 0 && a.pl == 0 && a.oh == a.h && a.ow == a.w;
     const int OH = is_1x1 ? 1 : a.oh;
@@ -802,7 +822,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                     best_time = t;
                     best = cand;
                     best.ck = ck; best.swizzle = ck_bytes; best.n_pad = n_pad; best.n_tiles = n_tiles;
-                    best.b_stage_bytes = b_bytes;
+                    if (best.b_stage_bytes == 0) best.b_stage_bytes = b_bytes;
                     const double kfrac = (double)a.cin_p / (n_chunks * ck);
                     const double nfrac = (double)a.cout_p / ((double)n_tiles * n_pad);
                     best.useful_frac = cand.useful_frac * kfrac * nfrac;
@@ -843,11 +863,21 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                         if (T > max_t) break;
                         const int rows_alloc = std::max(box_rows * P, T * 128 + (a.kh - 1) * P + a.kw - 1);
                         const int a_bytes = round_up(rows_alloc * ck_bytes, 1024);
-                        const int b_stages = fit_stages(2 * a_bytes, b_bytes, 4);
-                        if (b_stages < 3) continue;
+                        if (fit_stages(2 * a_bytes, b_bytes, 4) < 3) continue;
+                        // taps per weight stage (see the swapped candidates): three stages, or two that each hold
+                        // at least ~1500 cycles of MMAs (the load of one hides behind the other)
+                        int grp = 1;
+                        const int tap_bytes = n_pad * ck_bytes;
+                        for (int t = tap_bytes % 1024 ? 1 : std::min(taps_w, force_group > 0 ? force_group : 6); t > 1; --t) {
+                            const int st = fit_stages(2 * a_bytes, t * tap_bytes, 4);
+                            if (st >= 3 || (st == 2 && t * T * ceil_div(ck, 16) * t_mma >= 1500.0)) { grp = t; break; }
+                        }
+                        const int b_grp_bytes = grp > 1 ? grp * tap_bytes : b_bytes;
+                        const int b_stages = fit_stages(2 * a_bytes, b_grp_bytes, 4);
                         EdeUmmaCfg cand{};
                         cand.a_mode = 0; cand.bh = bh; cand.bw = bw; cand.pitch = P; cand.box_rows = box_rows;
                         cand.m_tiles = T; cand.a_stages = 2; cand.b_stages = b_stages; cand.a_stage_bytes = a_bytes;
+                        cand.b_stage_bytes = b_grp_bytes;
                         cand.tiles_w = ceil_div(OW, bw); cand.tiles_h = ceil_div(OH, bh);
                         cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * T * 128);
                         consider(cand, (double)n_chunks * box_rows * P * ck_bytes,
@@ -864,7 +894,6 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     // Packed tiles use N = 240 so that those shifted reads stay inside the 256-column accumulator stage.
     const int force_swap = env_int("EDE_UMMA_SWAP", -1);
     const int force_pack = env_int("EDE_UMMA_PACK", -1);
-    const int force_group = env_int("EDE_UMMA_GROUP", 0);
     if (n16 <= 128 && force_swap != 0) {
         if (force_swap == 1) best_time = 1e300;
         const int gs[3] = {4, 2, 1};
@@ -1032,7 +1061,7 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
         cuuint64_t strides[2] = {(cuuint64_t)a.w_umma_cin_p * 2, (cuuint64_t)a.w_umma_cin_p * 2 * a.w_umma_cout_p};
         const int w_rows_box = c.swap ? (c.pack_g > 1 ? 128 : std::min(128, round_up(a.cout_p, 8))) : c.n_pad;
         // taps per weight stage: the stage size the tile picker chose, in units of one tap's box
-        const int b_group = (c.swap && c.a_mode == 0 && (w_rows_box * c.ck * 2) % 1024 == 0)
+        const int b_group = (c.a_mode == 0 && (w_rows_box * c.ck * 2) % 1024 == 0)
                                 ? std::max(1, c.b_stage_bytes / (w_rows_box * c.ck * 2)) : 1;
         p.b_group = b_group;
         cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)w_rows_box, (cuuint32_t)b_group};
