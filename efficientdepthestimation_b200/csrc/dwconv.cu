@@ -6,10 +6,11 @@
 //   * One producer warp streams input rows through a ring of smem row slots with TMA (tensor map over the NHWC
 //     tensor, box = 64 channels x (cols*S + K - S) pixels x 1 row).  Zero padding, ragged right/bottom edges and
 //     channel tails are TMA out-of-bounds fill: the compute loop has no bounds checks on its inputs.
-//   * Consumer warp w owns output column w of the tile; lane l owns two channels.  The K x K window and the
-//     K x K weights of those two channels live in registers; per output row a thread reads only the S new
-//     input rows (K pixels each) from the ring.  Window slots rotate by compile-time indices because the walk
-//     is unrolled K rows at a time.
+//   * Consumer warp w owns NC adjacent output columns of the tile (NC = 2 where the registers allow: the walk is
+//     instruction-issue bound, and two columns share the row wait, the addressing and K - S of their K input
+//     pixels); lane l owns two channels.  The K x (K + (NC-1) S) window and the K x K weights of those two
+//     channels live in registers; per output row a thread reads only the S new input rows from the ring.
+//     Window slots rotate by compile-time indices because the walk is unrolled K rows at a time.
 //   * The squeeze (per-(n, c) sum of the STORED activations) is a per-thread running sum, one smem reduction
 //     over the block's columns and one atomicAdd per channel per block.
 #include <stdlib.h>
@@ -28,6 +29,14 @@ __device__ __forceinline__ float2 bf16pair_to_f2(uint32_t u) {
 __device__ __forceinline__ uint32_t f2_to_bf16pair(float2 v) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
     return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// x * sigmoid(x) with the two SFU approximations (ftz: a flushed exp only matters where the result is ~0 anyway)
+__device__ __forceinline__ float swish_fast(float v) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(v * -1.4426950408889634f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
+    return v * r;
 }
 
 // two consecutive channels (2*lane, 2*lane+1) of one pixel: smem read (64-channel slice at `px`), global store
@@ -90,10 +99,11 @@ template <int K> struct DwCols { static constexpr int value = K >= 5 ? 11 : DW_M
 // CH = channel lanes per block: 64 (lane = channel pair, warp = one output column) or 32 (half-warp = channel
 // pairs, the two halves of a warp own two adjacent output columns) -- the latter when c_p % 64 is in (0, 32],
 // e.g. the 32 / 96 / 144 / 480 / 672-channel stages of EfficientNet-B0, so that no lane idles.
-template <typename T, int K, int S, int CH>
+template <typename T, int K, int S, int CH, int NC>
 __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_kernel(const __grid_constant__ DwParams p) {
     constexpr int DEPTH = DwDepth<K>::value;
-    constexpr int SUB = 64 / CH;                           // output columns per warp
+    constexpr int SUB = 64 / CH;                           // column groups per warp (each NC output columns)
+    constexpr int NI = (NC - 1) * S + K;                   // input pixels of a row one thread reads
     constexpr int PB = Pair<T>::kPixelBytes * CH / 64;     // bytes of one staged pixel
     extern __shared__ uint8_t smem_raw[];
     __shared__ alignas(8) unsigned long long bars[2 * DEPTH];
@@ -106,9 +116,9 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
     auto empty = [&](int s) { return bar0 + 8u * (DEPTH + s); };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int ow0 = blockIdx.x * p.cols * SUB;
+    const int ow0 = blockIdx.x * p.cols * SUB * NC;
     const int c0 = blockIdx.y * CH;
-    const int n_act = min(p.cols, (a.ow - ow0 + SUB - 1) / SUB);   // consumer warps that own a real output column
+    const int n_act = min(p.cols, (a.ow - ow0 + SUB * NC - 1) / (SUB * NC));   // consumer warps that own a real output column
     const int rows_in = (a.oh - 1) * S + K;               // input rows (incl. padding rows) one image's walk touches
 
     if (threadIdx.x == 0) {
@@ -136,8 +146,9 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
         // ===================== consumers
         const int sub = lane / (CH / 2), cl = lane % (CH / 2);     // column within the warp, channel pair
         const int c = c0 + 2 * cl;
-        const int col = warp * SUB + sub, ow = ow0 + col;
+        const int col = (warp * SUB + sub) * NC, ow = ow0 + col;   // first of this thread's NC output columns
         const bool ok = c < a.c_p && ow < a.ow;
+        const bool swish = a.act == EDE_ACT_SWISH;
         const int cw = c < a.c_p ? c : 0;                  // idle lanes compute on channel 0 and never store
         float2 w[K * K];
 #pragma unroll
@@ -146,22 +157,23 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
         const float2 sf = *reinterpret_cast<const float2*>(a.shift + cw);
         const uint8_t* const colbase = ring_g + (size_t)(col * S) * PB;
         const int n_cons = n_act * 32, ctid = threadIdx.x;     // consumer warps are warps 0 .. n_act-1
-        int g = 0;                                         // ring position of the next row this warp loads
+        int slot = 0;                                      // ring slot of the next row this warp loads ...
+        uint32_t phase = 0;                                // ... and its barrier phase
+        const long long y_row = (long long)a.ow * a.y_cs;  // elements between two output rows
         for (int n = blockIdx.z; n < a.n; n += p.zsplit) {
-            T* const ycol = reinterpret_cast<T*>(a.y) + ((long long)n * a.oh * a.ow + (ok ? ow : 0)) * a.y_cs + a.y_co;
+            T* yrow = reinterpret_cast<T*>(a.y) + ((long long)n * a.oh * a.ow + (ok ? ow : 0)) * a.y_cs + a.y_co;
             float2 psum = make_float2(0.f, 0.f);
-            float2 xw[K][K];                               // [row slot][kx]
-            auto load_row = [&](float2 (&row)[K]) {
-                const int slot = g & (DEPTH - 1);
-                mbar_wait(full(slot), (g / DEPTH) & 1);
-                ++g;
-                const uint8_t* px = colbase + (size_t)slot * p.row_bytes;
+            float2 xw[K][NI];                              // [row slot][input column]
+            auto load_row = [&](float2 (&row)[NI]) {
+                mbar_wait(full(slot), phase);
+                const uint8_t* px = colbase + slot * p.row_bytes;
 #pragma unroll
-                for (int kx = 0; kx < K; ++kx) row[kx] = Pair<T>::lds(px + kx * PB, cl);
+                for (int kx = 0; kx < NI; ++kx) row[kx] = Pair<T>::lds(px + kx * PB, cl);
                 // the row now lives in registers of every lane: hand the slot back to the producer at once
                 // (the arrive has release semantics, so the reads above are ordered before the TMA refill)
                 __syncwarp();
                 if (lane == 0) mbar_arrive(empty(slot));
+                if (++slot == DEPTH) { slot = 0; phase ^= 1u; }
             };
 #pragma unroll
             for (int ky = 0; ky < K - S; ++ky) load_row(xw[ky]);
@@ -173,28 +185,33 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
                         // window row ky of output row oh lives in slot (ky + S*u) % K; the S new rows arrive now
 #pragma unroll
                         for (int j = 0; j < S; ++j) load_row(xw[(K - S + j + S * u) % K]);
-                        float2 acc0 = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
 #pragma unroll
-                        for (int ky = 0; ky < K; ++ky)
+                        for (int j = 0; j < NC; ++j) {
+                            float2 acc0 = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
 #pragma unroll
-                            for (int kx = 0; kx < K; ++kx) {
-                                const float2 xv = xw[(ky + S * u) % K][kx], wv = w[ky * K + kx];
-                                if ((ky * K + kx) & 1) { acc1.x = fmaf(xv.x, wv.x, acc1.x); acc1.y = fmaf(xv.y, wv.y, acc1.y); }
-                                else { acc0.x = fmaf(xv.x, wv.x, acc0.x); acc0.y = fmaf(xv.y, wv.y, acc0.y); }
+                            for (int ky = 0; ky < K; ++ky)
+#pragma unroll
+                                for (int kx = 0; kx < K; ++kx) {
+                                    const float2 xv = xw[(ky + S * u) % K][kx + j * S], wv = w[ky * K + kx];
+                                    if ((ky * K + kx) & 1) { acc1.x = fmaf(xv.x, wv.x, acc1.x); acc1.y = fmaf(xv.y, wv.y, acc1.y); }
+                                    else { acc0.x = fmaf(xv.x, wv.x, acc0.x); acc0.y = fmaf(xv.y, wv.y, acc0.y); }
+                                }
+                            float2 v = make_float2(fmaf(acc0.x + acc1.x, sc.x, sf.x), fmaf(acc0.y + acc1.y, sc.y, sf.y));
+                            if (swish) v = make_float2(swish_fast(v.x), swish_fast(v.y));
+                            else v = make_float2(apply_act(v.x, a.act), apply_act(v.y, a.act));
+                            if (ok && ow + j < a.ow) {
+                                v = Pair<T>::st(yrow + j * a.y_cs, c, v);       // the squeeze sums what is stored
+                                psum.x += v.x;
+                                psum.y += v.y;
                             }
-                        float2 v = make_float2(apply_act(fmaf(acc0.x + acc1.x, sc.x, sf.x), a.act),
-                                               apply_act(fmaf(acc0.y + acc1.y, sc.y, sf.y), a.act));
-                        if (ok) {
-                            v = Pair<T>::st(ycol + (long long)oh * a.ow * a.y_cs, c, v);   // the squeeze sums what is stored
-                            psum.x += v.x;
-                            psum.y += v.y;
                         }
+                        yrow += y_row;
                     }
                 }
             }
             if (a.pool_sum) {                              // per-image squeeze: reduce over the tile's columns
-                pool_s[col * CH + 2 * cl] = psum.x;
-                pool_s[col * CH + 2 * cl + 1] = psum.y;
+                pool_s[(col / NC) * CH + 2 * cl] = psum.x;
+                pool_s[(col / NC) * CH + 2 * cl + 1] = psum.y;
                 asm volatile("bar.sync 1, %0;" ::"r"(n_cons) : "memory");
                 for (int ch = ctid; ch < CH; ch += n_cons) {
                     if (c0 + ch < a.c_p) {
@@ -221,7 +238,7 @@ static int pick_cols(int ow_units, int max_cols) {
     return best;
 }
 
-template <typename T, int K, int S, int CH>
+template <typename T, int K, int S, int CH, int NC>
 static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) return 1;
@@ -230,9 +247,9 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
     DwParams p;
     memset(&p, 0, sizeof(p));
     p.a = a;
-    p.cols = pick_cols(ceil_div(a.ow, SUB), DwCols<K>::value);
+    p.cols = pick_cols(ceil_div(a.ow, SUB * NC), DwCols<K>::value);
     const int esz = a.dtype == EDE_BF16 ? 2 : 4;
-    const int box_w = p.cols * SUB * S + K - S;
+    const int box_w = p.cols * SUB * NC * S + K - S;
     if (box_w > 256) return 1;
     p.tx_bytes = box_w * CH * esz;
     p.row_bytes = round_up(box_w * CH * esz, 128);          // TMA shared-memory destinations are 128-byte aligned
@@ -253,7 +270,7 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
     (void)cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
     if (!attr_set[dev]) {
-        if (cudaFuncSetAttribute(dwconv_tma_kernel<T, K, S, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(dwconv_tma_kernel<T, K, S, CH, NC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  200 * 1024) != cudaSuccess ||
             cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
             (void)cudaGetLastError();
@@ -264,7 +281,7 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
     // One block per SM is resident (registers).  A block's fixed cost (weights, barrier init, ring fill) is a few
     // rows' worth of work, so small maps let one block walk several images: pick the z split that minimises
     // waves x (images per block x rows + fixed cost).
-    const int units = ceil_div(a.ow, p.cols * SUB) * ceil_div(a.c_p, CH);
+    const int units = ceil_div(a.ow, p.cols * SUB * NC) * ceil_div(a.c_p, CH);
     const int sms = std::max(1, sm_count[dev]);
     int best_z = a.n;
     double best_cost = 1e30;
@@ -276,17 +293,23 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
     static const char* z_env = getenv("EDE_DW_ZSPLIT");       // debug / tests: force the number of image groups
     if (z_env && *z_env) best_z = std::max(1, std::min(a.n, atoi(z_env)));
     p.zsplit = best_z;
-    dim3 grid((unsigned)ceil_div(a.ow, p.cols * SUB), (unsigned)ceil_div(a.c_p, CH), (unsigned)p.zsplit);
+    dim3 grid((unsigned)ceil_div(a.ow, p.cols * SUB * NC), (unsigned)ceil_div(a.c_p, CH), (unsigned)p.zsplit);
     if (grid.y > 65535u || grid.z > 65535u || smem > 200 * 1024) return 1;
-    dwconv_tma_kernel<T, K, S, CH><<<grid, 32 * (p.cols + 1), smem, st>>>(p);
+    dwconv_tma_kernel<T, K, S, CH, NC><<<grid, 32 * (p.cols + 1), smem, st>>>(p);
     return 0;
 }
 
 template <typename T, int K, int S>
 static int dwconv_tma_launch_ks(const EdeDwConv& a, cudaStream_t st) {
     // 32-lane chunks when they cut the idle lanes of the last chunk by a quarter or more (c_p = 32, 96, ...)
-    if (4 * round_up(a.c_p, 32) <= 3 * round_up(a.c_p, 64)) return dwconv_tma_launch_ch<T, K, S, 32>(a, st);
-    return dwconv_tma_launch_ch<T, K, S, 64>(a, st);
+    // two output columns per thread except where the window would not fit the registers (5x5 stride 2) or the map
+    // is so narrow that half of the column pairs would be padding
+    constexpr int NC = (K >= 5 && S == 2) ? 1 : 2;
+    static const char* nc_env = getenv("EDE_DW_NC");          // debug / tests: force one column per thread
+    const bool one = NC == 1 || (nc_env && atoi(nc_env) == 1);
+    const bool ch32 = 4 * round_up(a.c_p, 32) <= 3 * round_up(a.c_p, 64);
+    if (one) return ch32 ? dwconv_tma_launch_ch<T, K, S, 32, 1>(a, st) : dwconv_tma_launch_ch<T, K, S, 64, 1>(a, st);
+    return ch32 ? dwconv_tma_launch_ch<T, K, S, 32, NC>(a, st) : dwconv_tma_launch_ch<T, K, S, 64, NC>(a, st);
 }
 
 // returns 0 when the TMA kernel was launched, 1 when this (k, s) / device has no TMA path (caller falls back)

@@ -83,6 +83,14 @@ def main():
         if kind == A.OP_STEM:
             fl = 2.0 * s.n * s.oh * s.ow * s.cout_p * s.cin * s.k * s.k
             desc = f"{s.k}x{s.k}s{s.s} {s.cin}->{s.cout_p}@{s.oh}x{s.ow} CUDA-core stem from NCHW fp32"
+        if kind == A.OP_DWCONV:
+            desc = f"{s.k}x{s.k}s{s.s} c{s.c_p} {s.h}x{s.w_}->{s.oh}x{s.ow} {'+pool' if s.pool_sum else ''} dt{s.dtype}"
+        if kind == A.OP_UPCONV:
+            desc = f"{s.kh}x{s.kw} taps, {s.cgrp} lanes, {s.h}x{s.w}->{s.oh}x{s.ow}"
+        if kind == A.OP_SE_SCALE:
+            desc = f"c{s.c_p} hw{s.hw} dt{s.dtype}"
+        if kind == A.OP_RESIZE:
+            desc = f"c{s.c_p} {s.h}x{s.w}->{s.oh}x{s.ow}"
         by = op_bytes(kind, s)
         rows.append(dict(i=i, tag=plan.tags[i], kind=A.OP_FIELD[kind], ms=ms, tflops=fl / ms / 1e9 if fl else 0.0,
                          gbs=by / ms / 1e6, desc=desc, flops=fl, bytes=by))

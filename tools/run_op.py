@@ -27,7 +27,7 @@ def main():
     plan, _, _ = m.plan_for(x)
     lib, st = A.lib(), torch.cuda.current_stream().cuda_stream
     base, size = C.addressof(plan.ops), C.sizeof(A.EdeOp)
-    i = plan.tags.index(tag)
+    i = int(tag[1:]) if tag.startswith('#') else plan.tags.index(tag)      # '#21' = op number 21 of the plan
     one = C.cast(base + i * size, C.POINTER(A.EdeOp))
     torch.cuda.profiler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
