@@ -25,6 +25,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <cmath>
 
 #include "common.cuh"
 #include "tma.cuh"
@@ -764,6 +765,19 @@ static bool narrow_pays(int cin_p, double gain) {
     return k32 < k64 && (double)(k64 - k32) >= gain * k64;
 }
 
+// Taps per weight stage of the resident modes.  Few large stages pipeline worse than many small ones (the issuer
+// starts a stage only when all of it has landed, the producer refills it only when all of it is consumed), but a
+// stage must carry enough MMAs to hide the issuing thread's per-stage bookkeeping (`target_clk`, measured): group
+// just enough taps for that, judged on the chunk with the fewest K steps (the trimmed last one).
+static int group_want(double mma_clk_per_kstep, int cin_p, int ck, int force_group, double target_clk,
+                      double pair_below_clk) {
+    if (force_group > 0) return force_group;
+    const int tail = cin_p % ck ? ceil_div(cin_p % ck, 16) : ck / 16;        // K steps of the last chunk
+    const double stage_clk = std::max(1.0, tail * mma_clk_per_kstep);
+    const int t = std::max(1, std::min(6, (int)std::ceil(target_clk / stage_clk - 0.2)));
+    return t == 1 && stage_clk < pair_below_clk ? 2 : t;
+}
+
 static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     memset(&c, 0, sizeof(c));
     if (!umma_eligible(a)) return;
@@ -868,7 +882,8 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                         // at least ~1500 cycles of MMAs (the load of one hides behind the other)
                         int grp = 1;
                         const int tap_bytes = n_pad * ck_bytes;
-                        for (int t = tap_bytes % 1024 ? 1 : std::min(taps_w, force_group > 0 ? force_group : 6); t > 1; --t) {
+                        const int want = group_want(T * mma_cycles(ck_bytes, n_pad), a.cin_p, ck, force_group, 776.0, 1000.0);   // m-tile loop: more bookkeeping per tap, pairs pay up to ~1000 clk
+                        for (int t = tap_bytes % 1024 ? 1 : std::min(taps_w, want); t > 1; --t) {
                             const int st = fit_stages(2 * a_bytes, t * tap_bytes, 4);
                             if (st >= 3 || (st == 2 && t * T * ceil_div(ck, 16) * t_mma >= 1500.0)) { grp = t; break; }
                         }
@@ -968,7 +983,8 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                         // taps per weight stage: as many as still leave three stages (one wait + one commit per
                         // stage; the issuing thread's bookkeeping per stage costs about as much as four MMAs)
                         int grp = 1;
-                        for (int t = (w_rows_box * ck_bytes) % 1024 ? 1 : std::min(steps, force_group > 0 ? force_group : 6); t > 1; --t)
+                        const int want = group_want(mma_cycles(ck_bytes, n_cols), a.cin_p, ck, force_group, 500.0, 0.0);
+                        for (int t = (w_rows_box * ck_bytes) % 1024 ? 1 : std::min(steps, want); t > 1; --t)
                             if (fit_stages(2 * a_bytes, round_up(t * w_rows_box * ck_bytes, 1024), 4) >= 3) { grp = t; break; }
                         const int b_grp_bytes = round_up(grp * w_rows_box * ck_bytes, 1024);
                         const int b_stages = fit_stages(2 * a_bytes, b_grp_bytes, 4);
