@@ -181,6 +181,14 @@ template <> __device__ __forceinline__ float round_as<bf16x2_t>(float v) {
     return h + __bfloat162float(__float2bfloat16_rn(v - h));
 }
 
+// x * sigmoid(x) with the two SFU approximations (ftz: a flushed exp only matters where the result is ~0 anyway)
+__device__ __forceinline__ float swish_fast(float v) {
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(v * -1.4426950408889634f));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
+    return v * r;
+}
+
 __device__ __forceinline__ float apply_act(float v, int act) {
     switch (act) {
         case EDE_ACT_RELU: return fmaxf(v, 0.f);

@@ -144,7 +144,7 @@ __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) 
 template <int ACT>
 __device__ __forceinline__ float act_ct(float v) {
     if (ACT == EDE_ACT_RELU) return fmaxf(v, 0.f);
-    if (ACT == EDE_ACT_SWISH) return __fdividef(v, 1.f + __expf(-v));
+    if (ACT == EDE_ACT_SWISH) return swish_fast(v);
     return v;
 }
 #ifndef EDE_UNIFORM_ISSUER

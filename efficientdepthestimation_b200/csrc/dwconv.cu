@@ -31,14 +31,6 @@ __device__ __forceinline__ uint32_t f2_to_bf16pair(float2 v) {
     return *reinterpret_cast<const uint32_t*>(&h);
 }
 
-// x * sigmoid(x) with the two SFU approximations (ftz: a flushed exp only matters where the result is ~0 anyway)
-__device__ __forceinline__ float swish_fast(float v) {
-    float e, r;
-    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(v * -1.4426950408889634f));
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.f + e));
-    return v * r;
-}
-
 // two consecutive channels (2*lane, 2*lane+1) of one pixel: smem read (64-channel slice at `px`), global store
 template <typename T> struct Pair;
 template <> struct Pair<float> {
