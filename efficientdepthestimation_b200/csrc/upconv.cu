@@ -8,6 +8,8 @@
 // 25 taps: for every output pixel and tap it bilinearly samples (align_corners=True) the tap's z-plane at
 // the tap-shifted position, sums, applies the folded BatchNorm / ReLU and stores NHWC.  Exact in real
 // arithmetic; fp32 z keeps it at least as accurate as convolving a bf16 upsampled map.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace ede {
@@ -116,10 +118,15 @@ __global__ void __launch_bounds__(256) upconv_rows_kernel(const EdeUpConv a, flo
     }
 }
 
-template <int K, typename TY>
+// Pass 2.  A thread finishes R vertically adjacent outputs of one (column, 8-lane group): for one tap row ty their
+// 2R lerp operands are only three distinct `rows` vectors (the map is upsampled >= 3x for R = 4, >= 1x for R = 2),
+// loaded once and combined with per-output weights (zero where a vector does not take part).  The pass was bound
+// by L2 bandwidth -- every `rows` vector was re-read by all the output rows that interpolate it.
+template <int K, typename TY, int R>
 __global__ void __launch_bounds__(256) upconv_cols_kernel(const EdeUpConv a, float scale_h) {
     const int ngrp = a.cgrp >> 3;
-    const long long total = (long long)a.n * a.oh * a.ow * ngrp;
+    const int oyb = (a.oh + R - 1) / R;                      // bands of R output rows
+    const long long total = (long long)a.n * oyb * a.ow * ngrp;
     const float* __restrict__ rows = a.rows;
     const long long ty_stride = (long long)a.ow * a.cgrp, y_stride = ty_stride * K;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -128,34 +135,54 @@ __global__ void __launch_bounds__(256) upconv_cols_kernel(const EdeUpConv a, flo
         long long pix = i / ngrp;
         const int ox = (int)(pix % a.ow);
         pix /= a.ow;
-        const int oy = (int)(pix % a.oh);
-        const int n = (int)(pix / a.oh);
+        const int oy0 = (int)(pix % oyb) * R;
+        const int n = (int)(pix / oyb);
         const float* base = rows + (long long)n * a.h * y_stride + (long long)ox * a.cgrp + c;
-        float acc[8];
+        float acc[R][8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[r][j] = 0.f;
 #pragma unroll
         for (int ty = 0; ty < K; ++ty) {
-            const int qy = oy + ty - a.pt;
-            if (qy < 0 || qy >= a.oh) continue;              // tap row in the zero padding
-            const float sy = scale_h * qy;
-            const int y0 = (int)sy, y1 = y0 + (y0 < a.h - 1 ? 1 : 0);
-            const float ly = sy - y0, hy = 1.f - ly;
-            float v0[8], v1[8];
-            load8<float>(base + y0 * y_stride + ty * ty_stride, v0);
-            load8<float>(base + y1 * y_stride + ty * ty_stride, v1);
+            const int q0 = oy0 + ty - a.pt;
+            const int qlo = max(q0, 0), qhi = min(q0 + R - 1, a.oh - 1);
+            if (qlo > qhi) continue;                         // the whole band's tap row lies in the zero padding
+            const int yb = (int)(scale_h * qlo);             // first low-resolution row the band touches
+            float va[8], vb[8], vc[8];
+            const float* p = base + ty * ty_stride;
+            load8<float>(p + (long long)yb * y_stride, va);
+            load8<float>(p + (long long)min(yb + 1, a.h - 1) * y_stride, vb);
+            load8<float>(p + (long long)min(yb + 2, a.h - 1) * y_stride, vc);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] = fmaf(hy, v0[j], fmaf(ly, v1[j], acc[j]));
+            for (int r = 0; r < R; ++r) {
+                const int q = q0 + r;
+                if (q < 0 || q >= a.oh) continue;            // tap row in the zero padding
+                const float sy = scale_h * q;
+                const int y0 = (int)sy, y1 = y0 + (y0 < a.h - 1 ? 1 : 0);
+                const float ly = sy - y0, hy = 1.f - ly;
+                const int d0 = y0 - yb, d1 = y1 - yb;        // 0..2 by the choice of R
+                const float wa = (d0 == 0 ? hy : 0.f) + (d1 == 0 ? ly : 0.f);
+                const float wb = (d0 == 1 ? hy : 0.f) + (d1 == 1 ? ly : 0.f);
+                const float wc = (d0 == 2 ? hy : 0.f) + (d1 == 2 ? ly : 0.f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[r][j] = fmaf(wa, va[j], fmaf(wb, vb[j], fmaf(wc, vc[j], acc[r][j])));
+            }
         }
         float sc[8], sf[8];
         load8<float>(a.scale + c, sc);
         load8<float>(a.shift + c, sf);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            acc[j] = fmaf(acc[j], sc[j], sf[j]);
-            if (c < a.act_c_end) acc[j] = apply_act(acc[j], a.act);
+        for (int r = 0; r < R; ++r) {
+            const int oy = oy0 + r;
+            if (oy >= a.oh) break;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                acc[r][j] = fmaf(acc[r][j], sc[j], sf[j]);
+                if (c < a.act_c_end) acc[r][j] = apply_act(acc[r][j], a.act);
+            }
+            store8<TY>(reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oy) * a.ow + ox) * a.y_cs + a.y_co + c, acc[r]);
         }
-        store8<TY>(reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oy) * a.ow + ox) * a.y_cs + a.y_co + c, acc);
     }
 }
 
@@ -182,10 +209,17 @@ extern "C" int ede_upconv_taps(const EdeUpConv* a, void* stream) {
         if (a->kh == 5) upconv_rows_kernel<5><<<(unsigned)g1, 256, 0, st>>>(*a, sw);
         else upconv_rows_kernel<3><<<(unsigned)g1, 256, 0, st>>>(*a, sw);
         EDE_LAUNCH_CHECK("upconv_rows_kernel");
+        // output rows per thread: 4 when the map is upsampled >= 3x (three low-res rows cover a band), else 2
+        const int R = sh <= 1.f / 3.f ? 4 : 2;
+        const long long total2 = (long long)a->n * ((a->oh + R - 1) / R) * a->ow * (a->cgrp >> 3);
+        const unsigned g2 = (unsigned)std::min<long long>((total2 + 255) / 256, 148LL * 64);
+        EDE_REQUIRE(sh < 1.f, "ede_upconv_taps: the separable form needs an upsampled map (h < oh)");
         if (a->kh == 5) {
-            EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<5, TY><<<(unsigned)g, 256, 0, st>>>(*a, sh)));
+            if (R == 4) { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<5, TY, 4><<<g2, 256, 0, st>>>(*a, sh))); }
+            else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<5, TY, 2><<<g2, 256, 0, st>>>(*a, sh))); }
         } else {
-            EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<3, TY><<<(unsigned)g, 256, 0, st>>>(*a, sh)));
+            if (R == 4) { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<3, TY, 4><<<g2, 256, 0, st>>>(*a, sh))); }
+            else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<3, TY, 2><<<g2, 256, 0, st>>>(*a, sh))); }
         }
         EDE_LAUNCH_CHECK("upconv_cols_kernel");
         return EDE_OK;
