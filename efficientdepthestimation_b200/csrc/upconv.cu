@@ -82,107 +82,108 @@ __global__ void __launch_bounds__(256) upconv_taps_kernel(const EdeUpConv a, flo
 //   rows[n][y][ty][px][c] = sum_tx inside_x(px+tx-pl) * lerp_x(z[n][y][.][(ty,tx),c], px+tx-pl)      (pass 1)
 //   y[n][py][px][c]       = act(scale * sum_ty inside_y(py+ty-pt) * lerp_y(rows[n][.][ty][px][c], py+ty-pt) + shift)
 // Pass 1 runs on the h low-resolution rows only; pass 2 reads 2*K vectors per output instead of 4*K*K.
+// grid = (n * h * K low-resolution (row, tap row) pairs, column blocks): no 64-bit index arithmetic per thread
 template <int K>
 __global__ void __launch_bounds__(256) upconv_rows_kernel(const EdeUpConv a, float scale_w) {
     const int ngrp = a.cgrp >> 3;
-    const long long total = (long long)a.n * a.h * K * a.ow * ngrp;
-    const float* __restrict__ z = a.z;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(i % ngrp) << 3;
-        long long r = i / ngrp;
-        const int px = (int)(r % a.ow);
-        r /= a.ow;
-        const int ty = (int)(r % K);
-        const long long ny = r / K;                          // n * h + y
-        const float* zrow = z + ny * a.w * (long long)a.z_cs + a.z_co + (long long)ty * K * a.cgrp + c;
-        float acc[8];
+    const int t = blockIdx.y * 256 + threadIdx.x;            // (output column, 8-lane group)
+    if (t >= a.ow * ngrp) return;
+    const int px = t / ngrp, c = (t - px * ngrp) << 3;
+    const int r = blockIdx.x;                                // (n * h + y) * K + ty
+    const int ny = r / K, ty = r - ny * K;
+    const float* zrow = a.z + (long long)ny * a.w * a.z_cs + a.z_co + ty * K * a.cgrp + c;
+    float acc[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
 #pragma unroll
-        for (int tx = 0; tx < K; ++tx) {
-            const int qx = px + tx - a.pl;
-            if (qx < 0 || qx >= a.ow) continue;              // tap column in the zero padding
-            const float sx = scale_w * qx;
-            const int x0 = (int)sx, x1 = x0 + (x0 < a.w - 1 ? 1 : 0);
-            const float lx = sx - x0, hx = 1.f - lx;
-            float v0[8], v1[8];
-            load8<float>(zrow + (long long)x0 * a.z_cs + tx * a.cgrp, v0);
-            load8<float>(zrow + (long long)x1 * a.z_cs + tx * a.cgrp, v1);
+    for (int tx = 0; tx < K; ++tx) {
+        const int qx = px + tx - a.pl;
+        if (qx < 0 || qx >= a.ow) continue;                  // tap column in the zero padding
+        const float sx = scale_w * qx;
+        const int x0 = (int)sx, x1 = x0 + (x0 < a.w - 1 ? 1 : 0);
+        const float lx = sx - x0, hx = 1.f - lx;
+        float v0[8], v1[8];
+        load8<float>(zrow + x0 * a.z_cs + tx * a.cgrp, v0);
+        load8<float>(zrow + x1 * a.z_cs + tx * a.cgrp, v1);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[j] = fmaf(hx, v0[j], fmaf(lx, v1[j], acc[j]));
-        }
-        float* dst = a.rows + i * 8;                         // [n*h + y][ty][px][cgrp] is exactly the thread order
-        *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(hx, v0[j], fmaf(lx, v1[j], acc[j]));
     }
+    float* dst = a.rows + ((long long)r * a.ow * ngrp + t) * 8;     // [n*h + y][ty][px][cgrp]
+    *reinterpret_cast<float4*>(dst) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
 }
 
 // Pass 2.  A thread finishes R vertically adjacent outputs of one (column, 8-lane group): for one tap row ty their
 // 2R lerp operands are only three distinct `rows` vectors (the map is upsampled >= 3x for R = 4, >= 1x for R = 2),
-// loaded once and combined with per-output weights (zero where a vector does not take part).  The pass was bound
-// by L2 bandwidth -- every `rows` vector was re-read by all the output rows that interpolate it.
+// loaded once and combined with per-output weights (zero where a vector does not take part).  The weights depend on
+// the band of output rows only: a block (= one band of one image) computes them once into shared memory.
+// grid = (n * bands, column blocks).
 template <int K, typename TY, int R>
 __global__ void __launch_bounds__(256) upconv_cols_kernel(const EdeUpConv a, float scale_h) {
+    __shared__ float w_s[K][R][3];
+    __shared__ int yb_s[K];                                  // first low-resolution row of tap row ty, -1 = all padding
     const int ngrp = a.cgrp >> 3;
-    const int oyb = (a.oh + R - 1) / R;                      // bands of R output rows
-    const long long total = (long long)a.n * oyb * a.ow * ngrp;
-    const float* __restrict__ rows = a.rows;
-    const long long ty_stride = (long long)a.ow * a.cgrp, y_stride = ty_stride * K;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(i % ngrp) << 3;
-        long long pix = i / ngrp;
-        const int ox = (int)(pix % a.ow);
-        pix /= a.ow;
-        const int oy0 = (int)(pix % oyb) * R;
-        const int n = (int)(pix / oyb);
-        const float* base = rows + (long long)n * a.h * y_stride + (long long)ox * a.cgrp + c;
-        float acc[R][8];
-#pragma unroll
-        for (int r = 0; r < R; ++r)
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[r][j] = 0.f;
-#pragma unroll
-        for (int ty = 0; ty < K; ++ty) {
-            const int q0 = oy0 + ty - a.pt;
-            const int qlo = max(q0, 0), qhi = min(q0 + R - 1, a.oh - 1);
-            if (qlo > qhi) continue;                         // the whole band's tap row lies in the zero padding
-            const int yb = (int)(scale_h * qlo);             // first low-resolution row the band touches
-            float va[8], vb[8], vc[8];
-            const float* p = base + ty * ty_stride;
-            load8<float>(p + (long long)yb * y_stride, va);
-            load8<float>(p + (long long)min(yb + 1, a.h - 1) * y_stride, vb);
-            load8<float>(p + (long long)min(yb + 2, a.h - 1) * y_stride, vc);
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const int q = q0 + r;
-                if (q < 0 || q >= a.oh) continue;            // tap row in the zero padding
-                const float sy = scale_h * q;
-                const int y0 = (int)sy, y1 = y0 + (y0 < a.h - 1 ? 1 : 0);
-                const float ly = sy - y0, hy = 1.f - ly;
-                const int d0 = y0 - yb, d1 = y1 - yb;        // 0..2 by the choice of R
-                const float wa = (d0 == 0 ? hy : 0.f) + (d1 == 0 ? ly : 0.f);
-                const float wb = (d0 == 1 ? hy : 0.f) + (d1 == 1 ? ly : 0.f);
-                const float wc = (d0 == 2 ? hy : 0.f) + (d1 == 2 ? ly : 0.f);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) acc[r][j] = fmaf(wa, va[j], fmaf(wb, vb[j], fmaf(wc, vc[j], acc[r][j])));
-            }
+    const int bands = (a.oh + R - 1) / R;
+    const int n = blockIdx.x / bands, oy0 = (blockIdx.x - n * bands) * R;
+    if (threadIdx.x < K * R) {
+        const int ty = threadIdx.x / R, r = threadIdx.x - ty * R;
+        const int q0 = oy0 + ty - a.pt;
+        const int qlo = max(q0, 0), qhi = min(q0 + R - 1, a.oh - 1);
+        const int yb = qlo > qhi ? -1 : (int)(scale_h * qlo);
+        if (r == 0) yb_s[ty] = yb;
+        const int q = q0 + r;
+        float wa = 0.f, wb = 0.f, wc = 0.f;
+        if (yb >= 0 && q >= 0 && q < a.oh) {                 // else: tap row in the zero padding
+            const float sy = scale_h * q;
+            const int y0 = (int)sy, y1 = y0 + (y0 < a.h - 1 ? 1 : 0);
+            const float ly = sy - y0, hy = 1.f - ly;
+            const int d0 = y0 - yb, d1 = y1 - yb;            // 0..2 by the choice of R
+            wa = (d0 == 0 ? hy : 0.f) + (d1 == 0 ? ly : 0.f);
+            wb = (d0 == 1 ? hy : 0.f) + (d1 == 1 ? ly : 0.f);
+            wc = (d0 == 2 ? hy : 0.f) + (d1 == 2 ? ly : 0.f);
         }
-        float sc[8], sf[8];
-        load8<float>(a.scale + c, sc);
-        load8<float>(a.shift + c, sf);
+        w_s[ty][r][0] = wa; w_s[ty][r][1] = wb; w_s[ty][r][2] = wc;
+    }
+    __syncthreads();
+    const int t = blockIdx.y * 256 + threadIdx.x;            // (output column, 8-lane group)
+    if (t >= a.ow * ngrp) return;
+    const int ox = t / ngrp, c = (t - ox * ngrp) << 3;
+    const long long ty_stride = (long long)a.ow * a.cgrp, y_stride = ty_stride * K;
+    const float* base = a.rows + (long long)n * a.h * y_stride + (long long)t * 8;
+    float acc[R][8];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[r][j] = 0.f;
+#pragma unroll
+    for (int ty = 0; ty < K; ++ty) {
+        const int yb = yb_s[ty];
+        if (yb < 0) continue;                                // the whole band's tap row lies in the zero padding
+        float va[8], vb[8], vc[8];
+        const float* p = base + ty * ty_stride;
+        load8<float>(p + yb * y_stride, va);
+        load8<float>(p + min(yb + 1, a.h - 1) * y_stride, vb);
+        load8<float>(p + min(yb + 2, a.h - 1) * y_stride, vc);
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const int oy = oy0 + r;
-            if (oy >= a.oh) break;
+            const float wa = w_s[ty][r][0], wb = w_s[ty][r][1], wc = w_s[ty][r][2];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                acc[r][j] = fmaf(acc[r][j], sc[j], sf[j]);
-                if (c < a.act_c_end) acc[r][j] = apply_act(acc[r][j], a.act);
-            }
-            store8<TY>(reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oy) * a.ow + ox) * a.y_cs + a.y_co + c, acc[r]);
+            for (int j = 0; j < 8; ++j) acc[r][j] = fmaf(wa, va[j], fmaf(wb, vb[j], fmaf(wc, vc[j], acc[r][j])));
         }
+    }
+    float sc[8], sf[8];
+    load8<float>(a.scale + c, sc);
+    load8<float>(a.shift + c, sf);
+    TY* yout = reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oy0) * a.ow + ox) * a.y_cs + a.y_co + c;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        if (oy0 + r >= a.oh) break;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            acc[r][j] = fmaf(acc[r][j], sc[j], sf[j]);
+            if (c < a.act_c_end) acc[r][j] = apply_act(acc[r][j], a.act);
+        }
+        store8<TY>(yout + (long long)r * a.ow * a.y_cs, acc[r]);
     }
 }
 
@@ -203,17 +204,17 @@ extern "C" int ede_upconv_taps(const EdeUpConv* a, void* stream) {
     if (g > 148LL * 64) g = 148LL * 64;
     cudaStream_t st = (cudaStream_t)stream;
     if (a->rows) {                                           // separable two-pass form
-        const long long total1 = (long long)a->n * a->h * a->kh * a->ow * (a->cgrp >> 3);
-        long long g1 = (total1 + 255) / 256;
-        if (g1 > 148LL * 64) g1 = 148LL * 64;
-        if (a->kh == 5) upconv_rows_kernel<5><<<(unsigned)g1, 256, 0, st>>>(*a, sw);
-        else upconv_rows_kernel<3><<<(unsigned)g1, 256, 0, st>>>(*a, sw);
+        EDE_REQUIRE(sh < 1.f, "ede_upconv_taps: the separable form needs an upsampled map (h < oh)");
+        const unsigned col_blocks = (unsigned)((a->ow * (a->cgrp >> 3) + 255) / 256);
+        const long long r1 = (long long)a->n * a->h * a->kh;
+        EDE_REQUIRE(r1 < 0x7fffffffLL && col_blocks <= 65535u, "ede_upconv_taps: map too large");
+        const dim3 g1((unsigned)r1, col_blocks);
+        if (a->kh == 5) upconv_rows_kernel<5><<<g1, 256, 0, st>>>(*a, sw);
+        else upconv_rows_kernel<3><<<g1, 256, 0, st>>>(*a, sw);
         EDE_LAUNCH_CHECK("upconv_rows_kernel");
         // output rows per thread: 4 when the map is upsampled >= 3x (three low-res rows cover a band), else 2
         const int R = sh <= 1.f / 3.f ? 4 : 2;
-        const long long total2 = (long long)a->n * ((a->oh + R - 1) / R) * a->ow * (a->cgrp >> 3);
-        const unsigned g2 = (unsigned)std::min<long long>((total2 + 255) / 256, 148LL * 64);
-        EDE_REQUIRE(sh < 1.f, "ede_upconv_taps: the separable form needs an upsampled map (h < oh)");
+        const dim3 g2((unsigned)(a->n * ((a->oh + R - 1) / R)), col_blocks);
         if (a->kh == 5) {
             if (R == 4) { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<5, TY, 4><<<g2, 256, 0, st>>>(*a, sh))); }
             else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<5, TY, 2><<<g2, 256, 0, st>>>(*a, sh))); }
