@@ -136,12 +136,22 @@ __global__ void __launch_bounds__(256) resize_kernel(const EdeResize a, float sc
     TY* __restrict__ y = reinterpret_cast<TY*>(a.y);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
-        const int c = (int)(i % cg) << 3;
-        long long pix = i / cg;
-        const int ow = (int)(pix % a.ow);
-        pix /= a.ow;
-        const int oh = (int)(pix % a.oh);
-        const int n = (int)(pix / a.oh);
+        int c, ow, oh, n;
+        if (total <= 0x7fffffffLL) {                         // 32-bit divisions (64-bit ones cost ~10x as much)
+            unsigned pix = (unsigned)i / (unsigned)cg;
+            c = (int)((unsigned)i - pix * (unsigned)cg) << 3;
+            const unsigned row = pix / (unsigned)a.ow;
+            ow = (int)(pix - row * (unsigned)a.ow);
+            n = (int)(row / (unsigned)a.oh);
+            oh = (int)(row - (unsigned)n * (unsigned)a.oh);
+        } else {
+            c = (int)(i % cg) << 3;
+            long long pix = i / cg;
+            ow = (int)(pix % a.ow);
+            pix /= a.ow;
+            oh = (int)(pix % a.oh);
+            n = (int)(pix / a.oh);
+        }
         // ATen upsample_bilinear2d (align_corners): src = scale * dst, lambda in fp32
         const float sy = scale_h * oh, sx = scale_w * ow;
         const int y0 = (int)sy, x0 = (int)sx;

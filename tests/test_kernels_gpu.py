@@ -62,6 +62,8 @@ CONV_CASES = [
     ("3x3_40_to_40_pack2_res", 2, 28, 38, 40, 40, 3, 1, (1, 1, 1, 1), True, A.ACT_RELU),
     ("3x3_16_to_8_pack4_wide", 1, 114, 152, 16, 8, 3, 1, (1, 1, 1, 1), True, A.ACT_SWISH),
     ("5x5_74_to_1_pack4_bias", 1, 114, 152, 74, 1, 5, 1, (2, 2, 2, 2), False, A.ACT_NONE),
+    ("5x5_74_to_74_k64_plus_16", 2, 57, 76, 74, 74, 5, 1, (2, 2, 2, 2), False, A.ACT_RELU),     # K = 64 + 16
+    ("3x3_90_to_40_k64_plus_32_pack2", 2, 40, 50, 90, 40, 3, 1, (1, 1, 1, 1), True, A.ACT_RELU),  # K = 64 + 32
 ]
 
 
