@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const EdeDwConv a) {
 int dwconv_tma_launch(const EdeDwConv& a, cudaStream_t st);      // dwconv.cu
 
 // ------------------------------------------------------------------ squeeze-excite FCs
-__global__ void __launch_bounds__(256) se_fc_kernel(const EdeSeFc a) {
+__global__ void __launch_bounds__(1024) se_fc_kernel(const EdeSeFc a) {
     extern __shared__ float sm[];                          // mean[c_p] | hidden[csq]
     float* mean = sm;
     float* hid = sm + a.c_p;
@@ -316,7 +316,8 @@ int ede_se_fc(const EdeSeFc* a, void* stream) {
     EDE_REQUIRE(a->n > 0 && a->c > 0 && a->c <= a->c_p && a->csq > 0, "ede_se_fc: bad shape");
     const size_t smem = (size_t)(a->c_p + a->csq) * sizeof(float);
     EDE_REQUIRE(smem <= 48 * 1024, "ede_se_fc: too many channels (%d)", a->c_p);
-    se_fc_kernel<<<a->n, 256, smem, (cudaStream_t)stream>>>(*a);
+    // latency bound (one block per image, three dependent phases): wide blocks for the wide late stages
+    se_fc_kernel<<<a->n, a->c_p >= 512 ? 1024 : (a->c_p >= 192 ? 512 : 256), smem, (cudaStream_t)stream>>>(*a);
     EDE_LAUNCH_CHECK("se_fc_kernel");
     return EDE_OK;
 }
