@@ -81,6 +81,8 @@ __global__ void __launch_bounds__(1024) se_fc_kernel(const EdeSeFc a) {
     float* mean = sm;
     float* hid = sm + a.c_p;
     const int n = blockIdx.x;
+    pdl_trigger();
+    pdl_wait();
     for (int i = threadIdx.x; i < a.c_p; i += blockDim.x) {
         float* ps = a.pool_sum + (long long)n * a.c_p + i;
         mean[i] = i < a.c ? *ps * a.inv_hw : 0.f;
@@ -113,6 +115,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) se_scale_kernel(const EdeSeScale a) {
     const int cg = a.c_p >> 3;
     const long long total = (long long)a.n * a.hw * cg;
+    pdl_trigger();
+    pdl_wait();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
         const int c = (int)(i % cg) << 3;
@@ -134,6 +138,8 @@ __global__ void __launch_bounds__(256) resize_kernel(const EdeResize a, float sc
     const long long total = (long long)a.n * a.oh * a.ow * cg;
     const TX* __restrict__ x = reinterpret_cast<const TX*>(a.x);
     TY* __restrict__ y = reinterpret_cast<TY*>(a.y);
+    pdl_trigger();
+    pdl_wait();
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
         int c, ow, oh, n;
@@ -317,7 +323,8 @@ int ede_se_fc(const EdeSeFc* a, void* stream) {
     const size_t smem = (size_t)(a->c_p + a->csq) * sizeof(float);
     EDE_REQUIRE(smem <= 48 * 1024, "ede_se_fc: too many channels (%d)", a->c_p);
     // latency bound (one block per image, three dependent phases): wide blocks for the wide late stages
-    se_fc_kernel<<<a->n, a->c_p >= 512 ? 1024 : (a->c_p >= 192 ? 512 : 256), smem, (cudaStream_t)stream>>>(*a);
+    (void)launch_pdl(se_fc_kernel, dim3(a->n), dim3(a->c_p >= 512 ? 1024 : (a->c_p >= 192 ? 512 : 256)), smem,
+                     (cudaStream_t)stream, *a);
     EDE_LAUNCH_CHECK("se_fc_kernel");
     return EDE_OK;
 }
@@ -326,7 +333,7 @@ int ede_se_scale(const EdeSeScale* a, void* stream) {
     EDE_REQUIRE(a && a->x && a->y && a->gate, "ede_se_scale: null argument");
     EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_se_scale: channel counts must be multiples of 8");
     const long long total = (long long)a->n * a->hw * (a->c_p >> 3);
-    EDE_DISPATCH_DTYPE(a->dtype, T, (se_scale_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(*a)));
+    EDE_DISPATCH_DTYPE(a->dtype, T, ((void)launch_pdl(se_scale_kernel<T>, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream, *a)));
     EDE_LAUNCH_CHECK("se_scale_kernel");
     return EDE_OK;
 }
@@ -341,7 +348,7 @@ int ede_resize_bilinear_ac(const EdeResize* a, void* stream) {
     const unsigned g = grid_for(total, 256);
     cudaStream_t st = (cudaStream_t)stream;
     EDE_DISPATCH_DTYPE(a->x_dtype, TX,
-                       EDE_DISPATCH_DTYPE(a->y_dtype, TY, (resize_kernel<TX, TY><<<g, 256, 0, st>>>(*a, sh, sw))));
+                       EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(resize_kernel<TX, TY>, dim3(g), dim3(256), 0, st, *a, sh, sw))));
     EDE_LAUNCH_CHECK("resize_kernel");
     return EDE_OK;
 }

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -179,6 +180,31 @@ template <> __device__ __forceinline__ float round_as<__nv_bfloat16>(float v) {
 template <> __device__ __forceinline__ float round_as<bf16x2_t>(float v) {
     const float h = __bfloat162float(__float2bfloat16_rn(v));
     return h + __bfloat162float(__float2bfloat16_rn(v - h));
+}
+
+// ---- programmatic dependent launch.  Kernels of a forward plan are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization: the next kernel's CTAs may become resident (and run their
+// prologue: barrier init, TMEM allocation, weight staging) while the current kernel drains.  Every such kernel calls
+// pdl_trigger() first and pdl_wait() before it reads activations or writes anything -- the wait returns when all
+// prerequisite grids have completed and their memory is visible, so RAW and WAR hazards on the arena are excluded.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+    static const bool on = [] { const char* e = getenv("EDE_PDL"); return !(e && e[0] == '0'); }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = on ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 // x * sigmoid(x) with the two SFU approximations (ftz: a flushed exp only matters where the result is ~0 anyway)

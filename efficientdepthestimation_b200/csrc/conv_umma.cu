@@ -339,6 +339,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
     const int taps = sp_taps * p.w_passes;        // weight tiles per channel chunk ([w_hi taps ; w_lo taps])
     unsigned long long prof_t0 = 0;
     if (p.prof && threadIdx.x == 0) prof_t0 = gtime();
+    pdl_trigger();
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < MAX_STAGES; ++s) {
@@ -378,6 +379,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    pdl_wait();            // the prologue above overlapped the previous kernel's tail; its outputs are visible now
     uint32_t tmem_addr;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_addr) : "r"(tmem_slot) : "memory");
 
@@ -1026,8 +1028,8 @@ static int launch_variant(const UmmaParams& p, int n_cta, int smem, int dev, cud
         if (rc) return rc;
         attr_set[dev] = true;
     }
-    conv_umma_kernel<TY, ACT, RES><<<n_cta, NUM_THREADS, smem, st>>>(p);
-    return EDE_OK;
+    return check_cuda(launch_pdl(conv_umma_kernel<TY, ACT, RES>, dim3(n_cta), dim3(NUM_THREADS), (size_t)smem, st, p),
+                      "launch(conv_umma_kernel)");
 }
 
 static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t st) {

@@ -120,7 +120,9 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    pdl_trigger();
     __syncthreads();
+    pdl_wait();
 
     if (warp == p.cols) {
         // ===================== producer: one TMA row per ring slot, images back to back
@@ -287,7 +289,10 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
     p.zsplit = best_z;
     dim3 grid((unsigned)ceil_div(a.ow, p.cols * SUB * NC), (unsigned)ceil_div(a.c_p, CH), (unsigned)p.zsplit);
     if (grid.y > 65535u || grid.z > 65535u || smem > 200 * 1024) return 1;
-    dwconv_tma_kernel<T, K, S, CH, NC><<<grid, 32 * (p.cols + 1), smem, st>>>(p);
+    if (launch_pdl(dwconv_tma_kernel<T, K, S, CH, NC>, grid, dim3(32 * (p.cols + 1)), (size_t)smem, st, p) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 1;
+    }
     return 0;
 }
 

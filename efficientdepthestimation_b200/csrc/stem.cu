@@ -30,11 +30,13 @@ __global__ void __launch_bounds__(256) stem_conv_kernel(const EdeStem a, const S
     float* const xs = sm + K * K * cin * COUT;                   // [cin][ih][S][idx_w]
     const int t = threadIdx.x;
     const int n = blockIdx.z, oh0 = blockIdx.y * tl.th, ow0 = blockIdx.x * (2 * tl.lw);
+    pdl_trigger();
 
     for (int i = t; i < K * K * cin * COUT; i += 256) {
         const int r = i / COUT, c = i - r * COUT;
         ws[i] = c < a.cout_p ? a.w[(long long)r * a.cout_p + c] : 0.f;
     }
+    pdl_wait();                                                  // (the weights above are static; x and y are not)
     const int iw_span = tl.idx_w * S;
     const int ih_base = oh0 * S - a.pt, iw_base = ow0 * S - a.pl;
     for (int i = t; i < cin * tl.ih * iw_span; i += 256) {
@@ -117,7 +119,10 @@ static int stem_launch_t(const EdeStem& a, cudaStream_t st) {
     }
     dim3 grid((unsigned)ceil_div(a.ow, 2 * tl.lw), (unsigned)ceil_div(a.oh, tl.th), (unsigned)a.n);
     if (grid.y > 65535u || grid.z > 65535u) return 1;
-    stem_conv_kernel<TY, K, S, COUT><<<grid, 256, smem, st>>>(a, tl);
+    if (launch_pdl(stem_conv_kernel<TY, K, S, COUT>, grid, dim3(256), smem, st, a, tl) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 1;
+    }
     return 0;
 }
 

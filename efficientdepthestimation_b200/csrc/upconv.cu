@@ -86,6 +86,8 @@ __global__ void __launch_bounds__(256) upconv_taps_kernel(const EdeUpConv a, flo
 template <int K>
 __global__ void __launch_bounds__(256) upconv_rows_kernel(const EdeUpConv a, float scale_w) {
     const int ngrp = a.cgrp >> 3;
+    pdl_trigger();
+    pdl_wait();
     const int t = blockIdx.y * 256 + threadIdx.x;            // (output column, 8-lane group)
     if (t >= a.ow * ngrp) return;
     const int px = t / ngrp, c = (t - px * ngrp) << 3;
@@ -125,6 +127,7 @@ __global__ void __launch_bounds__(256) upconv_cols_kernel(const EdeUpConv a, flo
     const int ngrp = a.cgrp >> 3;
     const int bands = (a.oh + R - 1) / R;
     const int n = blockIdx.x / bands, oy0 = (blockIdx.x - n * bands) * R;
+    pdl_trigger();
     if (threadIdx.x < K * R) {
         const int ty = threadIdx.x / R, r = threadIdx.x - ty * R;
         const int q0 = oy0 + ty - a.pt;
@@ -145,6 +148,7 @@ __global__ void __launch_bounds__(256) upconv_cols_kernel(const EdeUpConv a, flo
         w_s[ty][r][0] = wa; w_s[ty][r][1] = wb; w_s[ty][r][2] = wc;
     }
     __syncthreads();
+    pdl_wait();
     const int t = blockIdx.y * 256 + threadIdx.x;            // (output column, 8-lane group)
     if (t >= a.ow * ngrp) return;
     const int ox = t / ngrp, c = (t - ox * ngrp) << 3;
@@ -209,18 +213,18 @@ extern "C" int ede_upconv_taps(const EdeUpConv* a, void* stream) {
         const long long r1 = (long long)a->n * a->h * a->kh;
         EDE_REQUIRE(r1 < 0x7fffffffLL && col_blocks <= 65535u, "ede_upconv_taps: map too large");
         const dim3 g1((unsigned)r1, col_blocks);
-        if (a->kh == 5) upconv_rows_kernel<5><<<g1, 256, 0, st>>>(*a, sw);
-        else upconv_rows_kernel<3><<<g1, 256, 0, st>>>(*a, sw);
+        if (a->kh == 5) (void)launch_pdl(upconv_rows_kernel<5>, g1, dim3(256), 0, st, *a, sw);
+        else (void)launch_pdl(upconv_rows_kernel<3>, g1, dim3(256), 0, st, *a, sw);
         EDE_LAUNCH_CHECK("upconv_rows_kernel");
         // output rows per thread: 4 when the map is upsampled >= 3x (three low-res rows cover a band), else 2
         const int R = sh <= 1.f / 3.f ? 4 : 2;
         const dim3 g2((unsigned)(a->n * ((a->oh + R - 1) / R)), col_blocks);
         if (a->kh == 5) {
-            if (R == 4) { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<5, TY, 4><<<g2, 256, 0, st>>>(*a, sh))); }
-            else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<5, TY, 2><<<g2, 256, 0, st>>>(*a, sh))); }
+            if (R == 4) { EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(upconv_cols_kernel<5, TY, 4>, g2, dim3(256), 0, st, *a, sh))); }
+            else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(upconv_cols_kernel<5, TY, 2>, g2, dim3(256), 0, st, *a, sh))); }
         } else {
-            if (R == 4) { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<3, TY, 4><<<g2, 256, 0, st>>>(*a, sh))); }
-            else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, (upconv_cols_kernel<3, TY, 2><<<g2, 256, 0, st>>>(*a, sh))); }
+            if (R == 4) { EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(upconv_cols_kernel<3, TY, 4>, g2, dim3(256), 0, st, *a, sh))); }
+            else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(upconv_cols_kernel<3, TY, 2>, g2, dim3(256), 0, st, *a, sh))); }
         }
         EDE_LAUNCH_CHECK("upconv_cols_kernel");
         return EDE_OK;
