@@ -82,6 +82,18 @@ class EdeStem(Structure):
         "n", "cin", "h", "w_", "oh", "ow", "cout_p", "y_cs", "y_co", "k", "s", "pt", "pl", "act", "y_dtype")
 
 
+class EdeDepthEpilogue(Structure):
+    _fields_ = [("pred", c_void_p), ("label", c_void_p), ("resized", c_void_p), ("depth_mm", c_void_p),
+                ("sums16", c_void_p), ("edges4", c_void_p)] + _ints("n", "h", "w", "oh", "ow") + [
+        ("edge_thr", c_float), ("cap", c_float), ("mm_scale", c_float)]
+
+
+class EdePreprocess(Structure):
+    _fields_ = [("frames", c_void_p), ("y", c_void_p), ("xb", c_void_p), ("xk", c_void_p), ("yb", c_void_p),
+                ("yk", c_void_p)] + _ints("n", "ih", "iw", "ch", "cw", "xks", "yks", "band", "span") + [
+        ("mean", c_float * 3), ("std", c_float * 3)]
+
+
 class _Zero(Structure):
     _fields_ = [("p", c_void_p), ("bytes", c_int64)]
 
@@ -103,7 +115,7 @@ OP_FIELD = {OP_CONV: "conv", OP_DWCONV: "dw", OP_SE_FC: "se_fc", OP_SE_SCALE: "s
 # every symbol include/ede.h declares (checked by tests/test_cabi.py without a GPU)
 EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_stem_conv", "ede_stem_supported", "ede_dwconv2d", "ede_se_fc", "ede_se_scale",
            "ede_resize_bilinear_ac", "ede_resize_planes_f32", "ede_maxpool3x3s2", "ede_eltwise", "ede_nchw_to_nhwc", "ede_nhwc_to_nchw",
-           "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_plan_run",
+           "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_depth_epilogue", "ede_resample_coeffs", "ede_preprocess_frames", "ede_plan_run",
            "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof"]
 
 _lib = None
@@ -123,7 +135,8 @@ def lib():
                      ("ede_se_scale", EdeSeScale), ("ede_resize_bilinear_ac", EdeResize),
                      ("ede_maxpool3x3s2", EdeMaxPool), ("ede_eltwise", EdeEltwise),
                      ("ede_nchw_to_nhwc", EdeLayout), ("ede_nhwc_to_nchw", EdeLayout),
-                     ("ede_upconv_taps", EdeUpConv), ("ede_stem_conv", EdeStem)):
+                     ("ede_upconv_taps", EdeUpConv), ("ede_stem_conv", EdeStem),
+                     ("ede_depth_epilogue", EdeDepthEpilogue), ("ede_preprocess_frames", EdePreprocess)):
         f = getattr(L, name)
         f.argtypes = [POINTER(st), c_void_p]
         f.restype = c_int32
@@ -141,6 +154,8 @@ def lib():
     L.ede_sobel_loss_metrics.restype = c_int32
     L.ede_edge_counts.argtypes = [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_float, c_void_p, c_void_p]
     L.ede_edge_counts.restype = c_int32
+    L.ede_resample_coeffs.argtypes = [c_int32, c_int32, c_int32, c_int32, c_void_p, c_void_p]
+    L.ede_resample_coeffs.restype = c_int32
     L.ede_plan_run.argtypes = [POINTER(EdeOp), c_int32, c_void_p]
     L.ede_plan_run.restype = c_int32
     L.ede_launch_count.argtypes = [c_int32]

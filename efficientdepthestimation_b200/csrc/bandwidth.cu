@@ -188,13 +188,7 @@ __global__ void __launch_bounds__(256) resize_planes_kernel(const float* __restr
         const long long r = i / ow;
         const int oy = (int)(r % oh);
         const long long pl = r / oh;
-        const float sy = scale_h * oy, sx = scale_w * ox;
-        const int y0 = (int)sy, x0 = (int)sx;
-        const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
-        const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
-        const float* p = x + pl * h * w;
-        y[i] = hy * (hx * p[(long long)y0 * w + x0] + lx * p[(long long)y0 * w + x1]) +
-               ly * (hx * p[(long long)y1 * w + x0] + lx * p[(long long)y1 * w + x1]);
+        y[i] = bilerp_ac_plane(x + pl * h * w, h, w, scale_h, scale_w, oy, ox);
     }
 }
 

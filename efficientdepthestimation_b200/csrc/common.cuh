@@ -224,6 +224,20 @@ __device__ __forceinline__ float apply_act(float v, int act) {
     }
 }
 
+// One sample of ATen's upsample_bilinear2d (align_corners=True) on an fp32 plane [h][w]: src = scale * dst, the
+// lambdas in fp32, the same expression tree in every kernel that resizes a depth map (bit-identical results).
+__device__ __forceinline__ float bilerp_ac_plane(const float* __restrict__ p, int h, int w, float scale_h, float scale_w,
+                                                 int oy, int ox) {
+    const float sy = scale_h * oy, sx = scale_w * ox;
+    const int y0 = (int)sy, x0 = (int)sx;
+    const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
+    const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
+    // explicit roundings (no compiler-chosen FMA contraction): the value does not depend on the surrounding kernel
+    const float top = __fmaf_rn(hx, p[(long long)y0 * w + x0], __fmul_rn(lx, p[(long long)y0 * w + x1]));
+    const float bot = __fmaf_rn(hx, p[(long long)y1 * w + x0], __fmul_rn(lx, p[(long long)y1 * w + x1]));
+    return __fmaf_rn(hy, top, __fmul_rn(ly, bot));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -49,6 +49,60 @@ def edge_counts(pred: torch.Tensor, label: torch.Tensor, threshold: float = 0.25
     return out
 
 
+def depth_epilogue(pred: torch.Tensor, size=None, label: torch.Tensor = None, *, want_resized: bool = False,
+                   want_depth_mm: bool = False, want_sums: bool = None, want_edges: bool = False,
+                   edge_threshold: float = 0.25, cap: float = 10.0, mm_scale: float = 1000.0,
+                   sums: torch.Tensor = None, edges: torch.Tensor = None) -> Dict[str, torch.Tensor]:
+    """ONE pass for everything the reference's eval callers do right after ``model(image)``:
+    ``F.interpolate(output, size, 'bilinear', align_corners=True)`` (train.py:273-276, test.py:49-52,
+    test_nyu.py:85) -> MetricsTracker sums + Sobel loss sums (util.py:39-83, train.py:216-236) and
+    edge counts (test.py:56-76) against ``label`` -> cap / x1000 / uint16 (test_nyu.py:87-88).
+    Returns the requested device tensors {"resized", "depth_mm", "sums", "edges"}; async, no host sync."""
+    if pred.device.type != "cuda":
+        raise RuntimeError("efficientdepthestimation_b200.loss: CUDA tensors required (no CPU fallback)")
+    if pred.dim() != 4 or pred.size(1) != 1:
+        raise RuntimeError(f"expected pred of shape [N,1,h,w], got {tuple(pred.shape)}")
+    pred = pred.detach().float().contiguous()
+    n, _, h, w = pred.shape
+    if label is not None:
+        if label.device != pred.device or label.dim() != 4 or label.size(0) != n or label.size(1) != 1:
+            raise RuntimeError(f"expected label of shape [{n},1,H,W] on {pred.device}, got {tuple(label.shape)}")
+        label = label.detach().float().contiguous()
+        if size is None:
+            size = tuple(label.shape[2:])
+        elif tuple(size) != tuple(label.shape[2:]):
+            raise RuntimeError(f"size {tuple(size)} does not match the label {tuple(label.shape[2:])}")
+    if size is None:
+        raise RuntimeError("depth_epilogue needs `size` or `label`")
+    oh, ow = int(size[0]), int(size[1])
+    if want_sums is None:
+        want_sums = label is not None
+    if (want_sums or want_edges) and label is None:
+        raise RuntimeError("metric sums / edge counts need a label")
+    out = {}
+    dev = pred.device
+    if want_resized:
+        out["resized"] = torch.empty(n, 1, oh, ow, dtype=torch.float32, device=dev)
+    if want_depth_mm:
+        out["depth_mm"] = torch.empty(n, oh, ow, dtype=torch.uint16, device=dev)
+    if want_sums:
+        out["sums"] = sums if sums is not None else torch.zeros(16, dtype=torch.float64, device=dev)
+    if want_edges:
+        out["edges"] = edges if edges is not None else torch.zeros(4, dtype=torch.float64, device=dev)
+    if not out:
+        raise RuntimeError("depth_epilogue: no output requested")
+    ptr = lambda k: out[k].data_ptr() if k in out else None  # noqa: E731
+    a = A.EdeDepthEpilogue(pred=pred.data_ptr(), label=label.data_ptr() if label is not None else None,
+                           resized=ptr("resized"), depth_mm=ptr("depth_mm"), sums16=ptr("sums"), edges4=ptr("edges"),
+                           n=n, h=h, w=w, oh=oh, ow=ow, edge_thr=float(edge_threshold), cap=float(cap),
+                           mm_scale=float(mm_scale))
+    import ctypes
+    with torch.cuda.device(dev):
+        A.check(A.lib().ede_depth_epilogue(ctypes.byref(a), torch.cuda.current_stream(dev).cuda_stream),
+                "ede_depth_epilogue")
+    return out
+
+
 def loss_from_sums(s) -> Dict[str, float]:
     """train.py:231-236 from global sums: every term is a mean over N*H*W pixels."""
     s = [float(v) for v in s]

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 4
+#define EDE_ABI_VERSION 5
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
@@ -205,6 +205,43 @@ int ede_sobel_loss_metrics(const float* pred, const float* label, int32_t n, int
  * out: 4 doubles accumulated: [0] #pred edges [1] #label edges [2] #both [3] #equal. */
 int ede_edge_counts(const float* pred, const float* label, int32_t n, int32_t h, int32_t w,
                     float thr, double* out4, void* stream);
+
+/* Fused post-forward epilogue: bilinear align_corners resize of the depth map to the label / image
+ * size, consumed in the same pass -- nothing but the requested outputs is written.
+ * replaces: F.interpolate(output, size, 'bilinear', align_corners=True) + MetricsTracker.update at
+ *   ReSIDE/train.py:273-278, ReSIDE/test.py:49-54; edge_detection + thresholds at ReSIDE/test.py:56-76,94-102;
+ *   the cap / millimetre / uint16 conversion at ReSIDE/test_nyu.py:85-88; the loss of train.py:216-236 when the
+ *   label is at the resized size.
+ * pred: fp32 [n,1,h,w].  Optional (NULL = skip): label fp32 [n,1,oh,ow]; resized fp32 [n,1,oh,ow]; depth_mm
+ * uint16 [n,oh,ow] = (uint16)(int32)((r > cap ? 0 : r) * mm_scale); sums16 (layout of ede_sobel_loss_metrics,
+ * accumulated) and edges4 (layout of ede_edge_counts, accumulated) both need `label`. */
+typedef struct EdeDepthEpilogue {
+    const float* pred; const float* label;
+    float* resized; uint16_t* depth_mm; double* sums16; double* edges4;
+    int32_t n, h, w, oh, ow;
+    float edge_thr, cap, mm_scale;
+} EdeDepthEpilogue;
+int ede_depth_epilogue(const EdeDepthEpilogue* a, void* stream);
+
+/* Video-frame preprocessing in front of the forward path, one kernel, bit-exact against Pillow:
+ * uint8 HWC RGB frames [n,ih,iw,3] -> Scale to (sw,sh) with Image.BILINEAR -> CenterCrop (cw,ch) -> /255 ->
+ * (x-mean)/std -> fp32 NCHW [n,3,ch,cw].
+ * replaces: transforms.Compose([Scale([320,240]), CenterCrop([304,228]), ToTensor(), Normalize(mean,std)]) at
+ *   ReSIDE/inference_benchmark.py:46-52, ReSIDE/demo.py / demo_transform.py:23-127 (PIL + torch on the CPU).
+ * ede_resample_coeffs (HOST function, no GPU): Pillow's fixed-point coefficient table for output samples
+ *   [first, first+count) of an in_size -> out_size BILINEAR resample; returns ksize (> 0), or < 0 on error; with
+ *   NULL tables it only returns ksize.  bounds[2*i] = first input sample, bounds[2*i+1] = tap count,
+ *   kk[i*ksize + t] = weights scaled by 2^22.
+ * ede_preprocess_frames: xb/xk = DEVICE copies of the tables of the cropped columns, yb/yk of the cropped rows;
+ *   band = output rows per block; span >= input rows any band touches (shared memory = span*cw*3 bytes). */
+typedef struct EdePreprocess {
+    const uint8_t* frames; float* y;
+    const int32_t* xb; const int32_t* xk; const int32_t* yb; const int32_t* yk;
+    int32_t n, ih, iw, ch, cw, xks, yks, band, span;
+    float mean[3], std[3];
+} EdePreprocess;
+int ede_resample_coeffs(int32_t in_size, int32_t out_size, int32_t first, int32_t count, int32_t* bounds, int32_t* kk);
+int ede_preprocess_frames(const EdePreprocess* a, void* stream);
 
 /* Run a pre-built operator list ("forward plan") back to back on one stream. */
 enum { EDE_OP_CONV = 1, EDE_OP_DWCONV = 2, EDE_OP_SE_FC = 3, EDE_OP_SE_SCALE = 4, EDE_OP_RESIZE = 5,

@@ -327,3 +327,25 @@ def relative_l1(y_new, y_ref) -> float:
     """Parity metric of SURVEY.md 8c: max over images of sum|new-ref| / sum|ref|."""
     d = (y_new.double() - y_ref.double()).abs().flatten(1).sum(1)
     return float((d / y_ref.double().abs().flatten(1).sum(1)).max())
+
+
+# --------------------------------------------------------------------------- post-forward epilogue (SURVEY 8f-1)
+def post_resize(output, size_hw):
+    """ReSIDE/train.py:273-276, test.py:49-52, test_nyu.py:85: bilinear, align_corners=True."""
+    return _interp(output, tuple(int(v) for v in size_hw))
+
+
+def depth_to_mm_u16(resized):
+    """ReSIDE/test_nyu.py:86-88: squeeze -> numpy; >10 m -> 0; x1000; astype(uint16).  [N,1,H,W] -> uint16 [N,H,W]."""
+    import numpy as np
+    a = resized[:, 0].detach().cpu().numpy().copy()
+    a[a > 10.0] = 0.0
+    with np.errstate(invalid="ignore"):
+        # numpy's float32 -> uint16 cast is the C conversion through int32 on x86-64 for in-range values
+        return (a * 1000.0).astype(np.int32).astype(np.uint16)
+
+
+def edge_counts(output, depth, threshold=0.25):
+    """ReSIDE/test.py:56-76: [#pred edges, #label edges, #both, #equal] summed over the batch."""
+    e1, e2 = edge_magnitude(depth) > threshold, edge_magnitude(output) > threshold
+    return [float(e2.sum()), float(e1.sum()), float((e1 & e2).sum()), float((e1 == e2).sum())]
