@@ -6,8 +6,10 @@
 // every pixel to a 128-byte row and was TMA-bound), so this is a CUDA-core kernel shaped for bandwidth:
 //   * a block stages its input patch (3 x rows x cols, zero padded, columns de-interleaved by stride phase so that
 //     stride-2 reads are bank-conflict free) and all weights in shared memory;
-//   * a thread owns two output pixels and ALL output channels (2 x COUT fp32 accumulators): per tap it reads two
-//     inputs and COUT/4 broadcast weight vectors for 2*COUT FMAs;
+//   * a thread owns FOUR output pixels and HALF the output channels (4 x COUT/2 fp32 accumulators; the two channel
+//     halves are warp-uniform): per tap it reads four inputs and COUT/8 broadcast weight vectors for 2*COUT FMAs --
+//     shared-memory reads, not FMAs, bounded the 2-pixel x all-channel form (a broadcast LDS.128 still moves 512 B
+//     into the register file);
 //   * folded BN + activation, then each pixel's channels leave as contiguous 32-byte vectors in NHWC.
 // fp32 inputs and weights, fp32 accumulation: exact in every precision mode.
 #include <algorithm>
@@ -17,19 +19,34 @@
 namespace ede {
 
 struct StemTile {
-    int lw, th;            // column pairs per tile row (tile width = 2*lw), tile rows; lw*th <= 256
+    int lw, th;            // column quads per tile row (tile width = 4*lw), tile rows; lw*th <= 128
     int idx_w;             // staged columns per stride phase
     int ih;                // staged input rows
 };
 
+// 4-byte asynchronous copy global -> shared; src_bytes = 0 zero-fills (padding) without touching global memory
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, int src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gsrc), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Persistent blocks walk the tiles.  The input patch of tile i+1 streams into the second staging buffer with
+// cp.async (every load of the patch in flight at once, padding zero-filled by the copy itself) while tile i is being
+// computed; the weights are staged once per block.  Before this the kernel staged with plain loads, one dependent
+// batch after the other in front of every tile, and at 1-2 resident blocks per SM (109-190 registers for the
+// 2 x COUT accumulators) nothing hid that latency: 1.25 ms for the ResNet stem at batch 64.
 template <typename TY, int K, int S, int COUT>
-__global__ void __launch_bounds__(256) stem_conv_kernel(const EdeStem a, const StemTile tl) {
+__global__ void __launch_bounds__(256, (COUT <= 32 ? 2 : 1)) stem_conv_kernel(const EdeStem a, const StemTile tl, int tiles_x, int tiles_y) {
     extern __shared__ float sm[];
     const int cin = a.cin;
     float* const ws = sm;                                        // [K*K*cin][COUT]
-    float* const xs = sm + K * K * cin * COUT;                   // [cin][ih][S][idx_w]
-    const int t = threadIdx.x;
-    const int n = blockIdx.z, oh0 = blockIdx.y * tl.th, ow0 = blockIdx.x * (2 * tl.lw);
+    const int xs_elems = cin * tl.ih * S * tl.idx_w;
+    float* const xs0 = sm + K * K * cin * COUT;                  // 2 x [cin][ih][S][idx_w]
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     pdl_trigger();
 
     for (int i = t; i < K * K * cin * COUT; i += 256) {
@@ -38,72 +55,108 @@ __global__ void __launch_bounds__(256) stem_conv_kernel(const EdeStem a, const S
     }
     pdl_wait();                                                  // (the weights above are static; x and y are not)
     const int iw_span = tl.idx_w * S;
-    const int ih_base = oh0 * S - a.pt, iw_base = ow0 * S - a.pl;
-    for (int i = t; i < cin * tl.ih * iw_span; i += 256) {
-        const int il = i % iw_span;
-        const int r = i / iw_span;
-        const int hl = r % tl.ih, ci = r / tl.ih;
-        const int ihh = ih_base + hl, iww = iw_base + il;
-        float v = 0.f;
-        if (ihh >= 0 && ihh < a.h && iww >= 0 && iww < a.w_)
-            v = a.x[(((long long)n * cin + ci) * a.h + ihh) * a.w_ + iww];
-        xs[((ci * tl.ih + hl) * S + (il % S)) * tl.idx_w + il / S] = v;
-    }
-    __syncthreads();
+    const int per_img = tiles_x * tiles_y, ntiles = per_img * a.n;
 
-    const int row = t / tl.lw, cp = t - row * tl.lw;
-    if (row >= tl.th) return;
-    float acc0[COUT], acc1[COUT];
+    // warps own staged rows (channel, input row), lanes sweep the columns, de-interleaved by stride phase
+    auto stage = [&](int tile, float* xs) {
+        const int n = tile / per_img, rem = tile - n * per_img;
+        const int by = rem / tiles_x, bx = rem - by * tiles_x;
+        const int ih_base = by * tl.th * S - a.pt, iw_base = bx * (4 * tl.lw) * S - a.pl;
+        const int nrows = cin * tl.ih;
+        for (int r = warp; r < nrows; r += 8) {
+            const int ci = r / tl.ih, hl = r - ci * tl.ih;
+            const int ihh = ih_base + hl;
+            const bool row_ok = ihh >= 0 && ihh < a.h;
+            const float* __restrict__ src = a.x + (((long long)n * cin + ci) * a.h + (row_ok ? ihh : 0)) * a.w_;
+            float* __restrict__ dst = xs + (ci * tl.ih + hl) * S * tl.idx_w;
+            for (int il = lane; il < iw_span; il += 32) {
+                const int iww = iw_base + il;
+                const bool ok = row_ok && iww >= 0 && iww < a.w_;
+                cp_async4(dst + (il % S) * tl.idx_w + il / S, src + (ok ? iww : 0), ok ? 4 : 0);
+            }
+        }
+    };
+
+    constexpr int PX = 4, CT = COUT / 2;                         // pixels and channels per thread
+    const int half = t >> 7, tt = t & 127;                       // channel half (warp-uniform), pixel-quad index
+    const int row = tt / tl.lw, cp = tt - row * tl.lw;
+    int buf = 0;
+    if ((int)blockIdx.x < ntiles) stage(blockIdx.x, xs0);
+    cp_async_commit();
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, buf ^= 1) {
+        const int next = tile + gridDim.x;
+        if (next < ntiles) stage(next, xs0 + (buf ^ 1) * xs_elems);
+        cp_async_commit();
+        cp_async_wait<1>();                                      // this tile's patch has landed (the next may be in flight)
+        __syncthreads();
+        const float* const xs = xs0 + buf * xs_elems;
+        const int n = tile / per_img, rem = tile - n * per_img;
+        const int by = rem / tiles_x, bx = rem - by * tiles_x;
+        const int oh = by * tl.th + row, ow0 = bx * (PX * tl.lw);
+        if (row < tl.th && oh < a.oh) {
+            float acc[PX][CT];
 #pragma unroll
-    for (int c = 0; c < COUT; ++c) { acc0[c] = 0.f; acc1[c] = 0.f; }
-    for (int ci = 0; ci < cin; ++ci) {
+            for (int j = 0; j < PX; ++j)
 #pragma unroll
-        for (int ky = 0; ky < K; ++ky) {
-            const float* xr = xs + ((ci * tl.ih + row * S + ky) * S) * tl.idx_w;
+                for (int c = 0; c < CT; ++c) acc[j][c] = 0.f;
+            for (int ci = 0; ci < cin; ++ci) {
+                // 7x7: the kernel rows stay a rolled loop -- fully unrolled the 49 taps are ~120 KB of straight-line
+                // code and the 8 resident warps stalled on instruction fetch (ncu: no_instruction 1.8 per issue)
+#pragma unroll(K > 3 ? 1 : K)
+                for (int ky = 0; ky < K; ++ky) {
+                    const float* xr = xs + ((ci * tl.ih + row * S + ky) * S) * tl.idx_w;
 #pragma unroll
-            for (int kx = 0; kx < K; ++kx) {
-                const float* xp = xr + (kx % S) * tl.idx_w + kx / S;
-                const float x0 = xp[cp], x1 = xp[cp + tl.lw];
-                const float4* wv = reinterpret_cast<const float4*>(ws + ((ky * K + kx) * cin + ci) * COUT);
+                    for (int kx = 0; kx < K; ++kx) {
+                        const float* xp = xr + (kx % S) * tl.idx_w + kx / S + cp;
+                        float x[PX];
 #pragma unroll
-                for (int c4 = 0; c4 < COUT / 4; ++c4) {
-                    const float4 w = wv[c4];
-                    acc0[4 * c4] = fmaf(x0, w.x, acc0[4 * c4]); acc0[4 * c4 + 1] = fmaf(x0, w.y, acc0[4 * c4 + 1]);
-                    acc0[4 * c4 + 2] = fmaf(x0, w.z, acc0[4 * c4 + 2]); acc0[4 * c4 + 3] = fmaf(x0, w.w, acc0[4 * c4 + 3]);
-                    acc1[4 * c4] = fmaf(x1, w.x, acc1[4 * c4]); acc1[4 * c4 + 1] = fmaf(x1, w.y, acc1[4 * c4 + 1]);
-                    acc1[4 * c4 + 2] = fmaf(x1, w.z, acc1[4 * c4 + 2]); acc1[4 * c4 + 3] = fmaf(x1, w.w, acc1[4 * c4 + 3]);
+                        for (int j = 0; j < PX; ++j) x[j] = xp[j * tl.lw];
+                        const float4* wv = reinterpret_cast<const float4*>(ws + ((ky * K + kx) * cin + ci) * COUT + half * CT);
+#pragma unroll
+                        for (int c4 = 0; c4 < CT / 4; ++c4) {
+                            const float4 w = wv[c4];
+#pragma unroll
+                            for (int j = 0; j < PX; ++j) {
+                                acc[j][4 * c4] = fmaf(x[j], w.x, acc[j][4 * c4]);
+                                acc[j][4 * c4 + 1] = fmaf(x[j], w.y, acc[j][4 * c4 + 1]);
+                                acc[j][4 * c4 + 2] = fmaf(x[j], w.z, acc[j][4 * c4 + 2]);
+                                acc[j][4 * c4 + 3] = fmaf(x[j], w.w, acc[j][4 * c4 + 3]);
+                            }
+                        }
+                    }
+                }
+            }
+            const int c_base = half * CT;
+#pragma unroll
+            for (int j = 0; j < PX; ++j) {
+                const int ow = ow0 + cp + j * tl.lw;
+                if (ow >= a.ow) continue;
+                TY* yrow = reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oh) * a.ow + ow) * a.y_cs + a.y_co;
+#pragma unroll
+                for (int c = 0; c < CT; c += 8) {
+                    if (c_base + c >= a.cout_p) break;
+                    float v[8];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        v[q] = apply_act(fmaf(acc[j][c + q], __ldg(a.scale + c_base + c + q), __ldg(a.shift + c_base + c + q)), a.act);
+                    store8<TY>(yrow + c_base + c, v);
                 }
             }
         }
+        __syncthreads();                                         // everyone is done with `buf` before it is refilled
     }
-    const int oh = oh0 + row;
-    if (oh >= a.oh) return;
-#pragma unroll
-    for (int px = 0; px < 2; ++px) {
-        const int ow = ow0 + cp + px * tl.lw;
-        if (ow >= a.ow) continue;
-        TY* yrow = reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oh) * a.ow + ow) * a.y_cs + a.y_co;
-#pragma unroll
-        for (int c = 0; c < COUT; c += 8) {
-            if (c >= a.cout_p) break;
-            float v[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-                v[j] = apply_act(fmaf(px ? acc1[c + j] : acc0[c + j], __ldg(a.scale + c + j), __ldg(a.shift + c + j)), a.act);
-            store8<TY>(yrow + c, v);
-        }
-    }
+    cp_async_wait<0>();
 }
 
 template <typename TY, int K, int S, int COUT>
 static int stem_launch_t(const EdeStem& a, cudaStream_t st) {
     StemTile tl;
     const int wt = ceil_div(a.ow, 64);                           // tiles across: widest tile is 64 columns
-    tl.lw = std::min(32, ceil_div(ceil_div(a.ow, wt), 2));
-    tl.th = std::max(1, std::min(256 / tl.lw, a.oh));
-    tl.idx_w = 2 * tl.lw + (K - 1) / S + 1;
+    tl.lw = std::min(16, ceil_div(ceil_div(a.ow, wt), 4));
+    tl.th = std::max(1, std::min(128 / tl.lw, a.oh));
+    tl.idx_w = 4 * tl.lw + (K - 1) / S + 1;
     tl.ih = tl.th * S + K - S;
-    const size_t smem = ((size_t)K * K * a.cin * COUT + (size_t)a.cin * tl.ih * S * tl.idx_w) * sizeof(float);
+    const size_t smem = ((size_t)K * K * a.cin * COUT + 2 * (size_t)a.cin * tl.ih * S * tl.idx_w) * sizeof(float);
     if (smem > 200 * 1024) return 1;
     static bool attr_set[64] = {};
     int dev = 0;
@@ -117,9 +170,23 @@ static int stem_launch_t(const EdeStem& a, cudaStream_t st) {
         }
         attr_set[dev] = true;
     }
-    dim3 grid((unsigned)ceil_div(a.ow, 2 * tl.lw), (unsigned)ceil_div(a.oh, tl.th), (unsigned)a.n);
-    if (grid.y > 65535u || grid.z > 65535u) return 1;
-    if (launch_pdl(stem_conv_kernel<TY, K, S, COUT>, grid, dim3(256), smem, st, a, tl) != cudaSuccess) {
+    const int tiles_x = ceil_div(a.ow, 4 * tl.lw), tiles_y = ceil_div(a.oh, tl.th);
+    const long long ntiles = (long long)tiles_x * tiles_y * a.n;
+    if (ntiles > 0x7fffffffLL) return 1;
+    static int blocks_per_sm[64] = {};
+    if (!blocks_per_sm[dev]) {
+        int b = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, stem_conv_kernel<TY, K, S, COUT>, 256, smem) != cudaSuccess) {
+            (void)cudaGetLastError();
+            b = 1;
+        }
+        blocks_per_sm[dev] = b > 0 ? b : 1;
+    }
+    int sms = 148;
+    (void)cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const long long resident = (long long)sms * blocks_per_sm[dev];
+    dim3 grid((unsigned)(ntiles < resident ? ntiles : resident));
+    if (launch_pdl(stem_conv_kernel<TY, K, S, COUT>, grid, dim3(256), smem, st, a, tl, tiles_x, tiles_y) != cudaSuccess) {
         (void)cudaGetLastError();
         return 1;
     }
