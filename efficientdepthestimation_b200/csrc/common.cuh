@@ -224,6 +224,20 @@ __device__ __forceinline__ float apply_act(float v, int act) {
     }
 }
 
+// Packed fp32 FMA (Blackwell FFMA2): two independent round-to-nearest fp32 FMAs per issued instruction -- the same
+// values as two fmaf(), half the issue slots.  Operands are register pairs (lo, hi).
+__device__ __forceinline__ unsigned long long pack_f32x2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack_f32x2(unsigned long long v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void ffma2(unsigned long long& acc, unsigned long long a, unsigned long long b) {
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+
 // One sample of ATen's upsample_bilinear2d (align_corners=True) on an fp32 plane [h][w]: src = scale * dst, the
 // lambdas in fp32, the same expression tree in every kernel that resizes a depth map (bit-identical results).
 __device__ __forceinline__ float bilerp_ac_plane(const float* __restrict__ p, int h, int w, float scale_h, float scale_w,

@@ -94,11 +94,11 @@ __global__ void __launch_bounds__(256, (COUT <= 32 ? 2 : 1)) stem_conv_kernel(co
         const int by = rem / tiles_x, bx = rem - by * tiles_x;
         const int oh = by * tl.th + row, ow0 = bx * (PX * tl.lw);
         if (row < tl.th && oh < a.oh) {
-            float acc[PX][CT];
+            unsigned long long acc[PX][CT / 2];                  // channel pairs: packed fp32 FMAs (FFMA2)
 #pragma unroll
             for (int j = 0; j < PX; ++j)
 #pragma unroll
-                for (int c = 0; c < CT; ++c) acc[j][c] = 0.f;
+                for (int c = 0; c < CT / 2; ++c) acc[j][c] = 0ull;
             for (int ci = 0; ci < cin; ++ci) {
                 // 7x7: the kernel rows stay a rolled loop -- fully unrolled the 49 taps are ~120 KB of straight-line
                 // code and the 8 resident warps stalled on instruction fetch (ncu: no_instruction 1.8 per issue)
@@ -108,19 +108,21 @@ __global__ void __launch_bounds__(256, (COUT <= 32 ? 2 : 1)) stem_conv_kernel(co
 #pragma unroll
                     for (int kx = 0; kx < K; ++kx) {
                         const float* xp = xr + (kx % S) * tl.idx_w + kx / S + cp;
-                        float x[PX];
+                        unsigned long long x[PX];
 #pragma unroll
-                        for (int j = 0; j < PX; ++j) x[j] = xp[j * tl.lw];
+                        for (int j = 0; j < PX; ++j) {
+                            const float xv = xp[j * tl.lw];
+                            x[j] = pack_f32x2(xv, xv);
+                        }
                         const float4* wv = reinterpret_cast<const float4*>(ws + ((ky * K + kx) * cin + ci) * COUT + half * CT);
 #pragma unroll
                         for (int c4 = 0; c4 < CT / 4; ++c4) {
                             const float4 w = wv[c4];
+                            const unsigned long long w01 = pack_f32x2(w.x, w.y), w23 = pack_f32x2(w.z, w.w);
 #pragma unroll
                             for (int j = 0; j < PX; ++j) {
-                                acc[j][4 * c4] = fmaf(x[j], w.x, acc[j][4 * c4]);
-                                acc[j][4 * c4 + 1] = fmaf(x[j], w.y, acc[j][4 * c4 + 1]);
-                                acc[j][4 * c4 + 2] = fmaf(x[j], w.z, acc[j][4 * c4 + 2]);
-                                acc[j][4 * c4 + 3] = fmaf(x[j], w.w, acc[j][4 * c4 + 3]);
+                                ffma2(acc[j][2 * c4], x[j], w01);
+                                ffma2(acc[j][2 * c4 + 1], x[j], w23);
                             }
                         }
                     }
@@ -137,8 +139,10 @@ __global__ void __launch_bounds__(256, (COUT <= 32 ? 2 : 1)) stem_conv_kernel(co
                     if (c_base + c >= a.cout_p) break;
                     float v[8];
 #pragma unroll
+                    for (int q = 0; q < 8; q += 2) unpack_f32x2(acc[j][(c + q) / 2], v[q], v[q + 1]);
+#pragma unroll
                     for (int q = 0; q < 8; ++q)
-                        v[q] = apply_act(fmaf(acc[j][c + q], __ldg(a.scale + c_base + c + q), __ldg(a.shift + c_base + c + q)), a.act);
+                        v[q] = apply_act(fmaf(v[q], __ldg(a.scale + c_base + c + q), __ldg(a.shift + c_base + c + q)), a.act);
                     store8<TY>(yrow + c_base + c, v);
                 }
             }
