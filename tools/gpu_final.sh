@@ -12,6 +12,6 @@ timeout 300 python tools/profile_plan.py enb0-hu 64 --top 140 > gpurun_out/prof_
 timeout 300 python tools/profile_plan.py rn50-hu 32 --top 100 > gpurun_out/prof_rn50_full.log 2>&1
 timeout 120 tools/micro/mma_contend > gpurun_out/mma_contend.txt 2>&1
 timeout 600 python tools/bench_pipeline.py > gpurun_out/pipeline.jsonl 2> gpurun_out/pipeline.err; cat gpurun_out/pipeline.jsonl | cut -c1-220
-timeout 600 ncu --set full --import-source on --clock-control none -k regex:"preprocess_kernel|depth_epilogue_kernel|depth_resize_convert" -s 12 -c 3 -f -o gpurun_out/prof_pipeline python tools/bench_pipeline.py --no-cpu --kernels-only --steps 4 --warmup 4 > gpurun_out/ncu_pipeline.log 2>&1; tail -1 gpurun_out/ncu_pipeline.log | cut -c1-200
+for k in preprocess_kernel depth_epilogue_kernel depth_resize_convert_kernel; do timeout 300 ncu --set full --import-source on --clock-control none -k regex:$k -s 5 -c 1 -f -o gpurun_out/prof_$k python tools/bench_pipeline.py --no-cpu --kernels-only --steps 4 --warmup 4 > gpurun_out/ncu_$k.log 2>&1; done
 timeout 600 ncu --set full --import-source on --clock-control none -k regex:stem_conv -s 3 -c 1 -f -o gpurun_out/prof_stem_rn50 python bench.py --arch rn50-hu --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_stem_rn50.log 2>&1
 timeout 300 python tools/profile_plan.py rn50-hu 64 --top 100 > gpurun_out/prof_rn50_b64.log 2>&1
