@@ -350,6 +350,7 @@ int ede_resize_bilinear_ac(const EdeResize* a, void* stream) {
 int ede_resize_planes_f32(const float* x, float* y, int64_t planes, int32_t h, int32_t w, int32_t oh, int32_t ow,
                           void* stream) {
     EDE_REQUIRE(x && y && planes > 0 && h > 0 && w > 0 && oh > 0 && ow > 0, "ede_resize_planes_f32: bad arguments");
+    EDE_REQUIRE(h < (1 << 22) && w < (1 << 22) && (long long)h * w < 0x7fffffffLL, "ede_resize_planes_f32: plane too large");
     const float sh = oh > 1 ? (float)(h - 1) / (float)(oh - 1) : 0.f;
     const float sw = ow > 1 ? (float)(w - 1) / (float)(ow - 1) : 0.f;
     resize_planes_kernel<<<grid_for(planes * oh * ow, 256), 256, 0, (cudaStream_t)stream>>>(x, y, planes, h, w, oh, ow,

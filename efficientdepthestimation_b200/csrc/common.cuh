@@ -238,18 +238,35 @@ __device__ __forceinline__ void ffma2(unsigned long long& acc, unsigned long lon
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
 }
 
-// One sample of ATen's upsample_bilinear2d (align_corners=True) on an fp32 plane [h][w]: src = scale * dst, the
-// lambdas in fp32, the same expression tree in every kernel that resizes a depth map (bit-identical results).
+// floor and fraction of 0 <= s < 2^22 without the quarter-rate F2I / I2F conversions: adding 2^23 with round-toward-zero
+// leaves floor(s) in the low mantissa bits, and (t - 2^23) is that integer as a float, exactly.  Same values as
+// `i0 = (int)s; frac = s - i0`, which is how ATen's upsample_bilinear2d computes them.
+__device__ __forceinline__ void floor_split(float s, int& i0, float& frac) {
+    const float t = __fadd_rz(s, 8388608.f);
+    i0 = __float_as_int(t) & 0x7fffff;
+    frac = __fsub_rn(s, __fsub_rn(t, 8388608.f));
+}
+
+// One axis of ATen's upsample_bilinear2d (align_corners=True): source index pair and weights of output index `o`.
+struct LerpTap { int i0, i1; float w0, w1; };
+__device__ __forceinline__ LerpTap lerp_tap_ac(float scale, float o, int in_size) {
+    LerpTap t;
+    floor_split(__fmul_rn(scale, o), t.i0, t.w1);
+    t.i1 = t.i0 + (t.i0 < in_size - 1 ? 1 : 0);
+    t.w0 = __fsub_rn(1.f, t.w1);
+    return t;
+}
+// explicit roundings (no compiler-chosen FMA contraction): the value does not depend on the surrounding kernel
+__device__ __forceinline__ float bilerp_taps(const float* __restrict__ p, int w, const LerpTap& y, const LerpTap& x) {
+    const float top = __fmaf_rn(x.w0, p[y.i0 * w + x.i0], __fmul_rn(x.w1, p[y.i0 * w + x.i1]));
+    const float bot = __fmaf_rn(x.w0, p[y.i1 * w + x.i0], __fmul_rn(x.w1, p[y.i1 * w + x.i1]));
+    return __fmaf_rn(y.w0, top, __fmul_rn(y.w1, bot));
+}
+// One sample of ATen's upsample_bilinear2d (align_corners=True) on an fp32 plane [h][w] (h*w < 2^31): src = scale *
+// dst, the lambdas in fp32, the same expression tree in every kernel that resizes a depth map (bit-identical results).
 __device__ __forceinline__ float bilerp_ac_plane(const float* __restrict__ p, int h, int w, float scale_h, float scale_w,
                                                  int oy, int ox) {
-    const float sy = scale_h * oy, sx = scale_w * ox;
-    const int y0 = (int)sy, x0 = (int)sx;
-    const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
-    const float ly = sy - y0, lx = sx - x0, hy = 1.f - ly, hx = 1.f - lx;
-    // explicit roundings (no compiler-chosen FMA contraction): the value does not depend on the surrounding kernel
-    const float top = __fmaf_rn(hx, p[(long long)y0 * w + x0], __fmul_rn(lx, p[(long long)y0 * w + x1]));
-    const float bot = __fmaf_rn(hx, p[(long long)y1 * w + x0], __fmul_rn(lx, p[(long long)y1 * w + x1]));
-    return __fmaf_rn(hy, top, __fmul_rn(ly, bot));
+    return bilerp_taps(p, w, lerp_tap_ac(scale_h, (float)oy, h), lerp_tap_ac(scale_w, (float)ox, w));
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -48,34 +48,37 @@ __global__ void __launch_bounds__(256) sobel_kernel(const float* __restrict__ x,
 constexpr int NSUM = 13;
 
 // per-pixel terms of the loss (ReSIDE/train.py:231-234) and the metric sums (ReSIDE/util.py:46-73)
-__device__ __forceinline__ void accumulate_loss_metrics(double* s, float o, float d, float ox, float oy, float dx,
+// Accumulated in fp32 over the (at most four) pixels a thread owns in one tile, then added to the thread's fp64 sums:
+// the reference sums everything in fp32, so this is still the more accurate side, and it keeps the per-pixel work
+// free of fp32->fp64 conversions (quarter-rate) and fp64 adds.
+__device__ __forceinline__ void accumulate_loss_metrics(float* s, float o, float d, float ox, float oy, float dx,
                                                         float dy) {
     // loss terms, ReSIDE/train.py:231-234
-    s[0] += (double)logf(fabsf(o - d) + 0.5f);
+    s[0] += logf(fabsf(o - d) + 0.5f);
     const float dot = ox * dx + oy * dy + 1.f;
     const float no = sqrtf(ox * ox + oy * oy + 1.f), nd = sqrtf(dx * dx + dy * dy + 1.f);
-    s[1] += (double)fabsf(1.f - dot / (no * nd));
-    s[2] += (double)logf(fabsf(ox - dx) + 0.5f);
-    s[3] += (double)logf(fabsf(oy - dy) + 0.5f);
+    s[1] += fabsf(1.f - dot / (no * nd));
+    s[2] += logf(fabsf(ox - dx) + 0.5f);
+    s[3] += logf(fabsf(oy - dy) + 0.5f);
     // metric sums, ReSIDE/util.py:46-73
     const bool isnan_l = d != d;
     const bool invalid = !(d > 0.f);
     const float r = o - d;
-    s[4] += (double)fabsf(r);
-    s[5] += (double)r * (double)r;
+    s[4] += fabsf(r);
+    s[5] += r * r;
     if (!isnan_l && !invalid) {
-        s[6] += (double)(fabsf(r) / d);
-        s[7] += (double)fabsf(log10f(o) - log10f(d));
+        s[6] += fabsf(r) / d;
+        s[7] += fabsf(log10f(o) - log10f(d));
     }
     const float q1 = o / d, q2 = d / o;
     if (q1 == q1 && q2 == q2) {                    // torch.max propagates NaN -> comparison false
         const float ratio = fmaxf(q1, q2);
-        s[8] += ratio <= 1.25f ? 1.0 : 0.0;
-        s[9] += ratio <= 1.5625f ? 1.0 : 0.0;
-        s[10] += ratio <= 1.953125f ? 1.0 : 0.0;
+        s[8] += ratio <= 1.25f ? 1.f : 0.f;
+        s[9] += ratio <= 1.5625f ? 1.f : 0.f;
+        s[10] += ratio <= 1.953125f ? 1.f : 0.f;
     }
-    s[11] += isnan_l ? 0.0 : 1.0;
-    s[12] += 1.0;
+    s[11] += isnan_l ? 0.f : 1.f;
+    s[12] += 1.f;
 }
 
 __global__ void __launch_bounds__(256) sobel_loss_metrics_kernel(const float* __restrict__ pred,
@@ -91,6 +94,9 @@ __global__ void __launch_bounds__(256) sobel_loss_metrics_kernel(const float* __
     double s[NSUM];
 #pragma unroll
     for (int k = 0; k < NSUM; ++k) s[k] = 0.0;
+    float sf[NSUM];
+#pragma unroll
+    for (int k = 0; k < NSUM; ++k) sf[k] = 0.f;
     for (int i = threadIdx.x; i < STH * STW; i += blockDim.x) {
         const int ty = i / STW, tx = i - ty * STW;
         if (y0 + ty >= h || x0 + tx >= w) continue;
@@ -98,8 +104,10 @@ __global__ void __launch_bounds__(256) sobel_loss_metrics_kernel(const float* __
         float ox, oy, dx, dy;
         sobel_at(tp, ty + 1, tx + 1, ox, oy);
         sobel_at(tl, ty + 1, tx + 1, dx, dy);
-        accumulate_loss_metrics(s, o, d, ox, oy, dx, dy);
+        accumulate_loss_metrics(sf, o, d, ox, oy, dx, dy);
     }
+#pragma unroll
+    for (int k = 0; k < NSUM; ++k) s[k] += (double)sf[k];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #pragma unroll
     for (int k = 0; k < NSUM; ++k) {
@@ -162,8 +170,11 @@ __global__ void __launch_bounds__(256) depth_resize_convert_kernel(const EdeDept
         const float* __restrict__ p = a.pred + (long long)n * a.h * a.w;
         const int x0 = (int)q * 4;
         float v[4];
+        const LerpTap ty = lerp_tap_ac(scale_h, (float)oy, a.h);         // one row per thread: the y taps are shared
+        const float fx0 = (float)x0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) v[j] = x0 + j < a.ow ? bilerp_ac_plane(p, a.h, a.w, scale_h, scale_w, (int)oy, x0 + j) : 0.f;
+        for (int j = 0; j < 4; ++j)
+            v[j] = x0 + j < a.ow ? bilerp_taps(p, a.w, ty, lerp_tap_ac(scale_w, fx0 + (float)j, a.w)) : 0.f;
         const long long base = (long long)row * a.ow + x0;
         const bool full = x0 + 4 <= a.ow;
         if (a.resized) {
@@ -186,7 +197,7 @@ __global__ void __launch_bounds__(256) depth_resize_convert_kernel(const EdeDept
 // shared memory and consumed in place -- metric / loss sums and edge counts against the label, the fp32 resized map
 // and the 16-bit millimetre map are all optional outputs of the same pass, so the full-resolution prediction never
 // has to exist in HBM when only the sums or the 16-bit map are wanted.
-__global__ void __launch_bounds__(256, 4) depth_epilogue_kernel(const EdeDepthEpilogue a, float scale_h, float scale_w,
+__global__ void __launch_bounds__(256, 3) depth_epilogue_kernel(const EdeDepthEpilogue a, float scale_h, float scale_w,
                                                              int tiles_x, int tiles_y) {
     __shared__ float tp[STH + 2][STW + 2];
     __shared__ float tl[STH + 2][STW + 2];
@@ -209,6 +220,9 @@ __global__ void __launch_bounds__(256, 4) depth_epilogue_kernel(const EdeDepthEp
         }
         if (a.label) load_tile(tl, a.label + (long long)n * a.oh * a.ow, a.oh, a.ow, y0, x0);
         __syncthreads();
+        float sf[NSUM + 4];
+#pragma unroll
+        for (int k = 0; k < NSUM + 4; ++k) sf[k] = 0.f;
         for (int i = threadIdx.x; i < STH * STW; i += blockDim.x) {
             const int ty = i / STW, tx = i - ty * STW;
             const int py = y0 + ty, px = x0 + tx;
@@ -226,13 +240,15 @@ __global__ void __launch_bounds__(256, 4) depth_epilogue_kernel(const EdeDepthEp
                 float ox, oy, dx, dy;
                 sobel_at(tp, ty + 1, tx + 1, ox, oy);
                 sobel_at(tl, ty + 1, tx + 1, dx, dy);
-                if (a.sums16) accumulate_loss_metrics(s, o, d, ox, oy, dx, dy);
+                if (a.sums16) accumulate_loss_metrics(sf, o, d, ox, oy, dx, dy);
                 if (a.edges4) {
                     const bool ep = sqrtf(ox * ox + oy * oy) > a.edge_thr, el = sqrtf(dx * dx + dy * dy) > a.edge_thr;
-                    s[NSUM + 0] += ep; s[NSUM + 1] += el; s[NSUM + 2] += (ep && el); s[NSUM + 3] += (ep == el);
+                    sf[NSUM + 0] += ep; sf[NSUM + 1] += el; sf[NSUM + 2] += (ep && el); sf[NSUM + 3] += (ep == el);
                 }
             }
         }
+#pragma unroll
+        for (int k = 0; k < NSUM + 4; ++k) s[k] += (double)sf[k];
         __syncthreads();
     }
     if (!a.label) return;
@@ -287,6 +303,7 @@ int ede_edge_counts(const float* pred, const float* label, int32_t n, int32_t h,
 int ede_depth_epilogue(const EdeDepthEpilogue* a, void* stream) {
     EDE_REQUIRE(a && a->pred, "ede_depth_epilogue: null argument");
     EDE_REQUIRE(a->n > 0 && a->h > 0 && a->w > 0 && a->oh > 0 && a->ow > 0, "ede_depth_epilogue: bad shape");
+    EDE_REQUIRE(a->h < (1 << 22) && a->w < (1 << 22) && (long long)a->h * a->w < 0x7fffffffLL, "ede_depth_epilogue: map too large");
     EDE_REQUIRE(a->label || (!a->sums16 && !a->edges4), "ede_depth_epilogue: sums / edge counts need a label");
     EDE_REQUIRE(a->resized || a->depth_mm || a->sums16 || a->edges4, "ede_depth_epilogue: no output requested");
     const float sh = a->oh > 1 ? (float)(a->h - 1) / (float)(a->oh - 1) : 0.f;
@@ -303,7 +320,7 @@ int ede_depth_epilogue(const EdeDepthEpilogue* a, void* stream) {
     const long long ntiles = (long long)tiles_x * tiles_y * a->n;
     EDE_REQUIRE(ntiles <= 0x7fffffffLL, "ede_depth_epilogue: too many tiles");
     static const char* knob = getenv("EDE_EPILOGUE_BLOCKS");              // tuning knob: blocks in the persistent grid
-    const long long cap = knob ? atoll(knob) : 148 * 4;
+    const long long cap = knob ? atoll(knob) : 148 * 3;
     const int grid = (int)(ntiles < cap ? ntiles : cap);
     depth_epilogue_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*a, sh, sw, tiles_x, tiles_y);
     EDE_LAUNCH_CHECK("depth_epilogue_kernel");
