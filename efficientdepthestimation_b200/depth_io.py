@@ -64,12 +64,12 @@ class AsyncDepthWriter:
     """Batched D2H into pinned staging buffers on a side stream + a pool of writer threads, so that file I/O never
     stalls the forward stream (the reference writes synchronously per image, benchmark.py:764-773)."""
 
-    def __init__(self, num_threads: int = 4, slots: int = 2):
+    def __init__(self, num_threads: int = 4):
         self._q = queue.Queue()
         self._threads = [threading.Thread(target=self._work, daemon=True) for _ in range(num_threads)]
         for t in self._threads:
             t.start()
-        self._slots, self._free, self._stream = slots, None, None
+        self._stream = None
         self._errors = []
 
     def _work(self):
