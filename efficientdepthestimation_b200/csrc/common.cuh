@@ -237,6 +237,14 @@ __device__ __forceinline__ void unpack_f32x2(unsigned long long v, float& lo, fl
 __device__ __forceinline__ void ffma2(unsigned long long& acc, unsigned long long a, unsigned long long b) {
     asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
 }
+// acc = a * b + acc on both lanes of a float2 (bit-identical to two fmaf)
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 acc) {
+    unsigned long long r = pack_f32x2(acc.x, acc.y);
+    ffma2(r, pack_f32x2(a.x, a.y), pack_f32x2(b.x, b.y));
+    float2 o;
+    unpack_f32x2(r, o.x, o.y);
+    return o;
+}
 
 // floor and fraction of 0 <= s < 2^22 without the quarter-rate F2I / I2F conversions: adding 2^23 with round-toward-zero
 // leaves floor(s) in the low mantissa bits, and (t - 2^23) is that integer as a float, exactly.  Same values as

@@ -187,8 +187,9 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
 #pragma unroll
                                 for (int kx = 0; kx < K; ++kx) {
                                     const float2 xv = xw[(ky + S * u) % K][kx + j * S], wv = w[ky * K + kx];
-                                    if ((ky * K + kx) & 1) { acc1.x = fmaf(xv.x, wv.x, acc1.x); acc1.y = fmaf(xv.y, wv.y, acc1.y); }
-                                    else { acc0.x = fmaf(xv.x, wv.x, acc0.x); acc0.y = fmaf(xv.y, wv.y, acc0.y); }
+                                    // the channel pair is one packed fp32 FMA (FFMA2): same values, half the issue slots
+                                    if ((ky * K + kx) & 1) acc1 = ffma2(xv, wv, acc1);
+                                    else acc0 = ffma2(xv, wv, acc0);
                                 }
                             float2 v = make_float2(fmaf(acc0.x + acc1.x, sc.x, sf.x), fmaf(acc0.y + acc1.y, sc.y, sf.y));
                             if (swish) v = make_float2(swish_fast(v.x), swish_fast(v.y));
