@@ -72,6 +72,24 @@ class E_resnet(EdeModule, nn.Module):
         return tuple(feats)
 
 
+class _UnsupportedEncoder(nn.Module):
+    """E_densenet / E_senet (modules.py:72-121 of the reference): importable -- Benchmark/reside_model.py:6 compares
+    encoder TYPES against these names -- but not constructible: those encoders are outside the B200 depth path."""
+
+    def __init__(self, original_model=None, num_features=None):
+        super().__init__()
+        raise RuntimeError(f"Unsupported encoder network '{type(self).__name__}': only E_resnet and E_efficientnet "
+                           "are implemented on the B200 depth path")
+
+
+class E_densenet(_UnsupportedEncoder):
+    pass
+
+
+class E_senet(_UnsupportedEncoder):
+    pass
+
+
 _EFFNET_SPLITS = {"efficientnet-b0": (3, 5, 8), "efficientnet-b1": (5, 8, 16), "efficient-b2": (5, 8, 16),
                   "efficientnet-b3": (5, 8, 18), "efficientnet-b4": (6, 10, 22), "efficientnet-b5": (8, 13, 27),
                   "efficientnet-b6": (9, 15, 31), "efficientnet-b7": (11, 18, 38)}

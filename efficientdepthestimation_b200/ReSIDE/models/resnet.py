@@ -75,22 +75,16 @@ class ResNet(EdeModule, nn.Module):
                            "wrap it in modules.E_resnet")
 
 
-def _offline(pretrained):
-    # The reference downloads ImageNet weights here (resnet.py:185-186); every caller then overwrites
-    # them with load_state_dict, so offline the random-init network is returned.
-    return None
-
-
+# `pretrained` is accepted for signature parity only: the reference downloads ImageNet weights there
+# (resnet.py:185-186) and every caller then overwrites them with load_state_dict; offline the random-init
+# network is returned.
 def resnet50(pretrained=False, **kwargs):
-    _offline(pretrained)
     return ResNet(Bottleneck, [3, 4, 6, 3], **kwargs)
 
 
 def resnet101(pretrained=False, **kwargs):
-    _offline(pretrained)
     return ResNet(Bottleneck, [3, 4, 23, 3], **kwargs)
 
 
 def resnet152(pretrained=False, **kwargs):
-    _offline(pretrained)
     return ResNet(Bottleneck, [3, 8, 36, 3], **kwargs)
