@@ -24,8 +24,11 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <stddef.h>
+
 #include <algorithm>
 #include <cmath>
+#include <unordered_map>
 
 #include "common.cuh"
 #include "tma.cuh"
@@ -1032,13 +1035,20 @@ static int launch_variant(const UmmaParams& p, int n_cta, int smem, int dev, cud
                       "launch(conv_umma_kernel)");
 }
 
-static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t st) {
+// Everything a launch needs, derived once per distinct EdeConv (ede_conv2d keeps these in a small cache keyed by
+// the struct's bytes: a forward plan replays the same structs, so per-forward host work is one hash + one launch).
+struct ConvLaunch {
+    UmmaParams p;
+    int n_cta, smem;
+};
+
+static int conv_umma_build(const EdeConv& a, const EdeUmmaCfg& c, ConvLaunch& L) {
+    UmmaParams& p = L.p;
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) {
         set_error("ede_conv2d: cuTensorMapEncodeTiled driver entry point unavailable");
         return EDE_E_DRIVER;
     }
-    UmmaParams p;
     memset(&p, 0, sizeof(p));
     const CUtensorMapSwizzle sw = c.swizzle == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                                   : c.swizzle == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
@@ -1129,7 +1139,17 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     }
     // persistent grid: one CTA per SM (the dynamic smem request is kept above half an SM so that two CTAs
     // can never share one SM and fight over the 512 TMEM columns)
-    const int n_cta = std::min(p.total_tiles, std::max(1, sm_count[dev]));
+    L.n_cta = std::min(p.total_tiles, std::max(1, sm_count[dev]));
+    L.smem = std::max(c.smem_bytes, 120 * 1024);
+    return EDE_OK;
+}
+
+static int conv_umma_launch(const EdeConv& a, ConvLaunch& L, cudaStream_t st) {
+    UmmaParams& p = L.p;
+    const int n_cta = L.n_cta, smem = L.smem;
+    int dev = 0;
+    (void)cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
     static unsigned long long* prof_buf = nullptr;
     static const int prof_on = env_int("EDE_UMMA_PROF", 0);
 
@@ -1140,7 +1160,6 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
         g_prof_last = p.prof;
         g_prof_ctas = p.prof ? (size_t)n_cta : 0;
     }
-    const int smem = std::max(c.smem_bytes, 120 * 1024);
     // one kernel instantiation per (output dtype, activation, residual): the epilogue has no per-element branches
     int rc = EDE_OK;
 #define EDE_UMMA_LAUNCH(TY, ACT, RES) rc = launch_variant<TY, ACT, RES>(p, n_cta, smem, dev, st)
@@ -1161,6 +1180,39 @@ static int conv_umma_launch(const EdeConv& a, const EdeUmmaCfg& c, cudaStream_t 
     if (rc) return rc;
     EDE_LAUNCH_CHECK("conv_umma_kernel");
     return EDE_OK;
+}
+
+// ---- launch cache: EdeConv bytes (pointers, shapes, flags) + device -> tile configuration + tensor maps
+constexpr size_t CONV_KEY_BYTES = offsetof(EdeConv, w_pack_g) + sizeof(int32_t);
+struct ConvCacheEntry {
+    unsigned char key[CONV_KEY_BYTES];
+    int dev;
+    bool eligible;
+    ConvLaunch launch;
+};
+static uint64_t conv_key_hash(const EdeConv& a, int dev) {
+    const unsigned char* b = reinterpret_cast<const unsigned char*>(&a);
+    uint64_t h = 1469598103934665603ull ^ (uint64_t)dev;
+    for (size_t i = 0; i < CONV_KEY_BYTES; ++i) h = (h ^ b[i]) * 1099511628211ull;
+    return h;
+}
+static ConvCacheEntry* conv_cache_find(const EdeConv& a, int dev, bool insert) {
+    // thread-local: DataParallel runs one host thread per device, no locking on the hot path
+    thread_local std::unordered_multimap<uint64_t, ConvCacheEntry*> cache;
+    const uint64_t h = conv_key_hash(a, dev);
+    auto range = cache.equal_range(h);
+    for (auto it = range.first; it != range.second; ++it)
+        if (it->second->dev == dev && memcmp(it->second->key, &a, CONV_KEY_BYTES) == 0) return it->second;
+    if (!insert) return nullptr;
+    if (cache.size() >= 8192) {                      // bounded: a process that keeps compiling new plans starts over
+        for (auto& kv : cache) delete kv.second;
+        cache.clear();
+    }
+    ConvCacheEntry* e = new ConvCacheEntry();
+    memcpy(e->key, &a, CONV_KEY_BYTES);
+    e->dev = dev;
+    cache.emplace(h, e);
+    return e;
 }
 
 }  // namespace ede
@@ -1199,11 +1251,31 @@ int ede_conv2d(const EdeConv* a, void* stream) {
                 "ede_conv2d: output size inconsistent with input size");
     EDE_REQUIRE(a->x_layout == EDE_NHWC || (a->x_dtype == EDE_F32 && a->x_layout == EDE_NCHW),
                 "ede_conv2d: NCHW input must be fp32");
-    EdeConv b = *a;
+    EdeConv b;
+    memset(&b, 0, sizeof(b));
+    memcpy(&b, a, ede::CONV_KEY_BYTES);
     if (b.w_passes == 0) b.w_passes = 1;
-    EdeUmmaCfg cfg;
-    ede::umma_config(b, cfg);
-    if (cfg.eligible) return ede::conv_umma_launch(b, cfg, (cudaStream_t)stream);
+    static const bool cache_on = ede::env_int("EDE_CONV_CACHE", 1) != 0;
+    int dev = 0;
+    (void)cudaGetDevice(&dev);
+    ede::ConvCacheEntry* e = cache_on ? ede::conv_cache_find(b, dev, false) : nullptr;
+    if (e == nullptr) {
+        EdeUmmaCfg cfg;
+        ede::umma_config(b, cfg);
+        ede::ConvLaunch tmp;
+        if (cfg.eligible) {
+            int rc = ede::conv_umma_build(b, cfg, tmp);
+            if (rc) return rc;
+        }
+        if (!cache_on) {
+            if (cfg.eligible) return ede::conv_umma_launch(b, tmp, (cudaStream_t)stream);
+            return ede::conv_direct_launch(b, (cudaStream_t)stream);
+        }
+        e = ede::conv_cache_find(b, dev, true);
+        e->eligible = cfg.eligible != 0;
+        if (e->eligible) e->launch = tmp;
+    }
+    if (e->eligible) return ede::conv_umma_launch(b, e->launch, (cudaStream_t)stream);
     return ede::conv_direct_launch(b, (cudaStream_t)stream);
 }
 

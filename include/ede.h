@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 5
+#define EDE_ABI_VERSION 6
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
@@ -71,6 +71,36 @@ typedef struct EdeConv {
                                prepack for?' (answer in EdeUmmaCfg.pack_g)                            */
 } EdeConv;
 int ede_conv2d(const EdeConv* a, void* stream);
+
+/* Weight prepacking: reference layout -> the operand layouts of ede_conv2d, one pass on the device.
+ * replaces: nothing the reference executes per forward -- cuDNN consumes OIHW weights and the reference evaluates
+ *   BatchNorm as a separate module (ReSIDE/models/modules.py:21-29, resnet.py:64-71); this is the load-time step
+ *   between `model.load_state_dict` (ReSIDE/test.py:22, Benchmark/reside_model.py:44) and the first forward.
+ * w_oihw: DEVICE fp32 [cout][cin][kh][kw] (nn.Conv2d.weight).  in_map / out_map: DEVICE int32 [cin_p] / [cout_p],
+ *   lane -> source channel, -1 = zero lane; NULL = identity (lanes beyond cin / cout are zero).  bn_*: DEVICE fp32
+ *   [cout] running statistics + affine (all four or none), bias: conv bias or NULL.  Outputs (DEVICE, any may be
+ *   NULL to skip): w_umma bf16 (layout of EdeConv.w_umma for `pack_g`, `passes`; dims from ede_prepack_conv_sizes),
+ *   w_direct fp32 [kh*kw][cin_p][cout_p], scale / shift fp32 [cout_p] with
+ *   scale = gamma / sqrt(var + eps), shift = beta - mean * scale + scale * bias (fp64 arithmetic, pad lanes 0).
+ * ede_prepack_conv_sizes (HOST, no GPU): byte sizes of {w_umma, w_direct, scale, shift}; dims2 = {w_umma_cout_p,
+ *   w_umma_cin_p}.  ede_prepack_conv_to: packs into caller-provided buffers (asynchronous, no allocation).
+ * ede_prepack_conv: allocates ONE device block for the four buffers and packs into it; ede_free releases it. */
+typedef struct EdePrepackConv {
+    const float* w_oihw; const int32_t* in_map; const int32_t* out_map;
+    const float* bn_weight; const float* bn_bias; const float* bn_mean; const float* bn_var; const float* bias;
+    void* w_umma; float* w_direct; float* scale; float* shift;
+    float bn_eps;
+    int32_t cout, cin, kh, kw, cin_p, cout_p, passes, pack_g;
+} EdePrepackConv;
+typedef struct EdePackedConv {
+    void* w_umma; float* w_direct; float* scale; float* shift;
+    int32_t w_umma_cout_p, w_umma_cin_p, w_pack_g, w_passes;
+    int64_t device_bytes;
+} EdePackedConv;
+int ede_prepack_conv_sizes(const EdePrepackConv* a, int64_t* bytes4, int32_t* dims2);
+int ede_prepack_conv_to(const EdePrepackConv* a, void* stream);
+int ede_prepack_conv(const EdePrepackConv* a, EdePackedConv** handle, void* stream);
+int ede_free(EdePackedConv* handle);
 
 /* Tile configuration the tcgen05 path would use for `a` (pure host function, no GPU). */
 typedef struct EdeUmmaCfg {
