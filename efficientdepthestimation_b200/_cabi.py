@@ -94,6 +94,18 @@ class EdePreprocess(Structure):
         ("mean", c_float * 3), ("std", c_float * 3)]
 
 
+class EdePrepackConv(Structure):
+    _fields_ = [("w_oihw", c_void_p), ("in_map", c_void_p), ("out_map", c_void_p), ("bn_weight", c_void_p),
+                ("bn_bias", c_void_p), ("bn_mean", c_void_p), ("bn_var", c_void_p), ("bias", c_void_p),
+                ("w_umma", c_void_p), ("w_direct", c_void_p), ("scale", c_void_p), ("shift", c_void_p),
+                ("bn_eps", c_float)] + _ints("cout", "cin", "kh", "kw", "cin_p", "cout_p", "passes", "pack_g")
+
+
+class EdePackedConv(Structure):
+    _fields_ = [("w_umma", c_void_p), ("w_direct", c_void_p), ("scale", c_void_p), ("shift", c_void_p)] + _ints(
+        "w_umma_cout_p", "w_umma_cin_p", "w_pack_g", "w_passes") + [("device_bytes", c_int64)]
+
+
 class _Zero(Structure):
     _fields_ = [("p", c_void_p), ("bytes", c_int64)]
 
@@ -116,7 +128,8 @@ OP_FIELD = {OP_CONV: "conv", OP_DWCONV: "dw", OP_SE_FC: "se_fc", OP_SE_SCALE: "s
 EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_stem_conv", "ede_stem_supported", "ede_dwconv2d", "ede_se_fc", "ede_se_scale",
            "ede_resize_bilinear_ac", "ede_resize_planes_f32", "ede_maxpool3x3s2", "ede_eltwise", "ede_nchw_to_nhwc", "ede_nhwc_to_nchw",
            "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_depth_epilogue", "ede_resample_coeffs", "ede_preprocess_frames", "ede_plan_run",
-           "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof"]
+           "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof",
+           "ede_prepack_conv_sizes", "ede_prepack_conv_to", "ede_prepack_conv", "ede_free"]
 
 _lib = None
 
@@ -163,6 +176,14 @@ def lib():
     L.ede_version.restype = c_int32
     L.ede_last_error.restype = C.c_char_p
     L.ede_umma_available.restype = c_int32
+    L.ede_prepack_conv_sizes.argtypes = [POINTER(EdePrepackConv), POINTER(c_int64), POINTER(c_int32)]
+    L.ede_prepack_conv_sizes.restype = c_int32
+    L.ede_prepack_conv_to.argtypes = [POINTER(EdePrepackConv), c_void_p]
+    L.ede_prepack_conv_to.restype = c_int32
+    L.ede_prepack_conv.argtypes = [POINTER(EdePrepackConv), POINTER(POINTER(EdePackedConv)), c_void_p]
+    L.ede_prepack_conv.restype = c_int32
+    L.ede_free.argtypes = [POINTER(EdePackedConv)]
+    L.ede_free.restype = c_int32
     L.ede_debug_umma_prof.argtypes = [c_void_p, c_int64]
     L.ede_debug_umma_prof.restype = c_int64
     _lib = L
@@ -178,3 +199,27 @@ def umma_config(conv: EdeConv) -> EdeUmmaCfg:
     cfg = EdeUmmaCfg()
     check(lib().ede_conv2d_umma_config(C.byref(conv), C.byref(cfg)), "ede_conv2d_umma_config")
     return cfg
+
+
+def _prepack_struct(job) -> EdePrepackConv:
+    """engine job (already lane-scattered host weight [cout_p][cin_p][kh][kw]) -> EdePrepackConv with identity maps."""
+    return EdePrepackConv(cout=job["cout"], cin=job["cin"], kh=job["kh"], kw=job["kw"], cin_p=job["cin"],
+                          cout_p=job["cout"], passes=job["passes"], pack_g=job["pack_g"], bn_eps=0.0)
+
+
+def prepack_sizes(job):
+    """(bytes of {w_umma, w_direct, scale, shift}, (w_umma_cout_p, w_umma_cin_p)) -- host function, no GPU."""
+    b, d = (c_int64 * 4)(), (c_int32 * 2)()
+    check(lib().ede_prepack_conv_sizes(C.byref(_prepack_struct(job)), b, d), "ede_prepack_conv_sizes")
+    return list(b), list(d)
+
+
+def prepack_to(job, stage_base: int, weight_base: int, stream) -> None:
+    """One ede_prepack_conv_to launch: staged fp32 weight -> w_umma / w_direct regions of the weight blob."""
+    a = _prepack_struct(job)
+    a.w_oihw = stage_base + job["full"].offset
+    if job["w_umma"] is not None:
+        a.w_umma = weight_base + job["w_umma"].offset
+    if job["w_direct"] is not None:
+        a.w_direct = weight_base + job["w_direct"].offset
+    check(lib().ede_prepack_conv_to(C.byref(a), stream), f"ede_prepack_conv_to({job.get('tag', '')})")

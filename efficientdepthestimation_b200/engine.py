@@ -98,6 +98,15 @@ class View:
         return View(self.buf, self.co + lo_p, lanes)
 
 
+class Stage:
+    """A region of the plan's weight blob.  `t` = CPU tensor uploaded into it (None: a region that a prepack kernel
+    or the forward itself writes); `temp` regions live in the staging blob that is freed after prepacking."""
+    __slots__ = ("t", "nbytes", "offset", "temp", "zero")
+
+    def __init__(self, t, nbytes, temp=False, zero=False):
+        self.t, self.nbytes, self.offset, self.temp, self.zero = t, int(nbytes), -1, temp, zero
+
+
 def cat_views(views: Sequence[View]) -> View:
     """torch.cat(dim=1) of views that already sit side by side in one buffer."""
     b, co, lanes, base = views[0].buf, views[0].co, [], 0
@@ -109,10 +118,17 @@ def cat_views(views: Sequence[View]) -> View:
     return View(b, co, lanes)
 
 
+def _cpu(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """Prepacking arithmetic runs on HOST copies of the parameters (no eager GPU tensor ops at plan-compile time):
+    the packed operands reach the device in one upload + one prepack kernel per conv (Plan.__init__)."""
+    return None if t is None else t.detach().to("cpu")
+
+
 def _bn_dict(bn):
     if bn is None:
         return None
-    return dict(weight=bn.weight, bias=bn.bias, mean=bn.running_mean, var=bn.running_var, eps=bn.eps)
+    return dict(weight=_cpu(bn.weight), bias=_cpu(bn.bias), mean=_cpu(bn.running_mean), var=_cpu(bn.running_var),
+                eps=bn.eps)
 
 
 def _pad4(conv) -> Tuple[int, int, int, int]:
@@ -143,7 +159,8 @@ class Graph:
         self.dry_no_lib = self.dry and not os.path.exists(A.LIB_PATH)
         self.ops: List[tuple] = []                # (kind, struct, [(field, Buf)], tag)
         self.bufs: List[Buf] = []
-        self.keep: List[torch.Tensor] = []        # prepacked weights etc.
+        self.stages: List[Stage] = []             # regions of the weight blob (host tensors, reserved outputs)
+        self.prepacks: List[dict] = []            # one ede_prepack_conv_to call per dense conv (Plan.__init__)
         self.inputs: List[dict] = []              # {shape, targets: [(op index, pointer field)], lazy: to_nhwc op}
         self.outputs: List[tuple] = []            # (op index, shape)
         self.flops = 0.0                          # algorithmic 2*MAC of the reference graph's convs
@@ -184,17 +201,21 @@ class Graph:
             co += cp
         return out
 
-    def _dev(self, t: torch.Tensor) -> torch.Tensor:
-        t = t.contiguous()
-        if not self.dry:
-            t = t.to(self.device)
-        self.keep.append(t)
-        return t
+    def _dev(self, t: torch.Tensor, temp=False) -> Stage:
+        """Host tensor -> a region of the weight blob (uploaded once in Plan.__init__)."""
+        t = t.detach().to("cpu").contiguous()
+        st = Stage(t, t.numel() * t.element_size(), temp=temp)
+        self.stages.append(st)
+        return st
 
-    def _ptr(self, t: Optional[torch.Tensor]):
-        return None if t is None else (t.data_ptr() if not self.dry else 1)
+    def _reserve(self, nbytes: int, zero=False) -> Stage:
+        """Device-only region: written by a prepack kernel, or (zero=True) zero-initialised state of the forward."""
+        st = Stage(None, nbytes, zero=zero)
+        self.stages.append(st)
+        return st
 
-    def _add(self, kind, st, refs, tag):
+    def _add(self, kind, st, refs, tag, wrefs=()):
+        st._wrefs = [(f, w) for f, w in wrefs if w is not None]      # weight-blob pointers, patched in Plan.__init__
         i = len(self.ops)
         for _, b in refs:
             if b.first < 0:
@@ -252,12 +273,13 @@ class Graph:
         out_lanes, fulls, scales, shifts, act_end = [], [], [], [], 0
         seen_plain = False
         for (wt, bn, bias, activated) in parts:
+            wt, bias = _cpu(wt), _cpu(bias)
             co = int(wt.shape[0])
             if int(wt.shape[1]) != cin:
                 raise RuntimeError(f"{tag}: weight expects {int(wt.shape[1])} input channels, view has {cin}")
             omap = P.identity_map(co)
             fulls.append(P.scatter_weight(wt, in_lanes, omap))
-            sc, sf = P.fold_bn(co, _bn_dict(bn), bias, wt.device)
+            sc, sf = P.fold_bn(co, bn if isinstance(bn, dict) or bn is None else _bn_dict(bn), bias, "cpu")
             scales.append(P.place_lanes(sc, omap))
             shifts.append(P.place_lanes(sf, omap))
             base = sum(1 for v in out_lanes if v >= 0)
@@ -271,7 +293,7 @@ class Graph:
             if self.count_ref_flops:
                 self.flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
             self.exec_flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
-        full = torch.cat(fulls, 0)
+        full = torch.cat(fulls, 0)                               # host fp32 [cout_p][cin lanes][kh][kw]
         cout_p = len(out_lanes)
         if out is None:
             out = View(self.new_buf(x.n, oh, ow, cout_p, out_dtype), 0, out_lanes)
@@ -281,13 +303,11 @@ class Graph:
                                    f"conv output {x.n, oh, ow, cout_p}")
         # hi+lo weights whenever the OUTPUT is kept at split precision (the accurate encoder path)
         passes = 2 if (out.dtype == A.BF16X2 and self.precision != "fp32") else 1
-        w_direct = self._dev(P.pack_direct(full))
         scale = self._dev(torch.cat(scales))
         shift = self._dev(torch.cat(shifts))
         if res is not None and res.dtype != out.dtype:
             res = self.resize(res, (res.h, res.w), out_dtype=out.dtype, force=True, tag=tag + ".res_cast")
-        st = A.EdeConv(x=None, y=None, res=None, scale=self._ptr(scale), shift=self._ptr(shift),
-                       w_umma=1, w_direct=self._ptr(w_direct),
+        st = A.EdeConv(x=None, y=None, res=None, scale=1, shift=1, w_umma=1, w_direct=None,
                        n=x.n, h=x.h, w=x.w, cin_p=x.c_p * mul, x_cs=x.buf.cs * mul, x_co=x.co * mul,
                        oh=oh, ow=ow, cout_p=cout_p, y_cs=out.buf.cs, y_co=out.co,
                        res_cs=res.buf.cs if res is not None else 0, res_co=res.co if res is not None else 0,
@@ -296,34 +316,41 @@ class Graph:
                        relu_in=1 if relu_in else 0, w_umma_cout_p=P.ceil_to(cout_p, 16),
                        w_umma_cin_p=P.ceil_to(x.c_p * mul, 64),
                        force_direct=1 if self.precision == "fp32" else 0, w_passes=passes, w_pack_g=-1)
-        # ask the tile picker how many kernel-row taps it wants on the 128 M rows, then prepack for exactly that
+        # ask the tile picker whether the tcgen05 path takes this conv and how many kernel-row taps it wants on the
+        # 128 M rows, then have ede_prepack_conv_to pack for exactly that (one kernel per conv, Plan.__init__)
         cfg = A.umma_config(st)
         pack_g = int(cfg.pack_g) if cfg.eligible and cfg.pack_g > 1 else 1
-        if pack_g > 1:
-            w_umma, co16, ci64 = P.pack_umma_taps(full, passes, pack_g)
-        else:
-            w_umma, co16, ci64 = P.pack_umma(full, passes)
-        w_umma = self._dev(w_umma)
-        st.w_umma, st.w_umma_cout_p, st.w_umma_cin_p, st.w_pack_g = self._ptr(w_umma), co16, ci64, pack_g
+        job = dict(full=self._dev(full, temp=True), cout=cout_p, cin=int(full.shape[1]), kh=kh, kw=kw, passes=passes,
+                   pack_g=pack_g, w_umma=None, w_direct=None, tag=tag)
+        bytes4, dims2 = A.prepack_sizes(job)
+        if cfg.eligible:
+            job["w_umma"] = self._reserve(bytes4[0])
+            st.w_umma_cout_p, st.w_umma_cin_p, st.w_pack_g = dims2[0], dims2[1], pack_g
+        else:                                                    # exact SIMT path (fp32 mode, shapes tcgen05 cannot take)
+            job["w_direct"] = self._reserve(bytes4[1])
+            st.w_umma, st.w_pack_g = None, 1
+        self.prepacks.append(job)
         refs = [("x", x.buf), ("y", out.buf)] + ([("res", res.buf)] if res is not None else [])
-        self._add(A.OP_CONV, st, refs, tag)
+        self._add(A.OP_CONV, st, refs, tag, [("scale", scale), ("shift", shift), ("w_umma", job["w_umma"]),
+                                             ("w_direct", job["w_direct"])])
         return out
 
     def _stem(self, x: View, part, stride, pad, act, out_dtype, tag) -> View:
         """First conv of the network straight from the fp32 NCHW input (EDE_OP_STEM, csrc/stem.cu)."""
         wt, bn, bias, _ = part
+        wt, bias = _cpu(wt), _cpu(bias)
         co, cin, k = int(wt.shape[0]), int(wt.shape[1]), int(wt.shape[2])
         pt, pl, pb, pr = pad
         oh, ow = (x.h + pt + pb - k) // stride + 1, (x.w + pl + pr - k) // stride + 1
         out = self.new_view(x.n, oh, ow, co, out_dtype)
-        w = torch.zeros(k * k * cin, out.c_p, dtype=torch.float32, device=wt.device)
-        w[:, :co] = wt.detach().float().permute(2, 3, 1, 0).reshape(k * k * cin, co)
-        sc, sf = P.fold_bn(co, _bn_dict(bn), bias, wt.device)
+        w = torch.zeros(k * k * cin, out.c_p, dtype=torch.float32)
+        w[:, :co] = wt.float().permute(2, 3, 1, 0).reshape(k * k * cin, co)
+        sc, sf = P.fold_bn(co, bn if isinstance(bn, dict) or bn is None else _bn_dict(bn), bias, "cpu")
         w, sc, sf = self._dev(w), self._dev(P.place_lanes(sc, out.lanes)), self._dev(P.place_lanes(sf, out.lanes))
-        st = A.EdeStem(x=None, y=None, w=self._ptr(w), scale=self._ptr(sc), shift=self._ptr(sf), n=x.n, cin=cin,
+        st = A.EdeStem(x=None, y=None, w=None, scale=None, shift=None, n=x.n, cin=cin,
                        h=x.h, w_=x.w, oh=oh, ow=ow, cout_p=out.c_p, y_cs=out.buf.cs, y_co=out.co, k=k, s=stride,
                        pt=pt, pl=pl, act=act, y_dtype=out.dtype)
-        i = self._add(A.OP_STEM, st, [("y", out.buf)], tag)
+        i = self._add(A.OP_STEM, st, [("y", out.buf)], tag, [("w", w), ("scale", sc), ("shift", sf)])
         self.inputs[x.input_index]["targets"].append((i, "x"))
         fl = 2.0 * x.n * oh * ow * co * cin * k * k
         self.flops += fl
@@ -336,14 +363,14 @@ class Graph:
         input channels whose only non-zero weight is an exact 1.0 on the centre tap.  For that the BN scale moves
         from the epilogue into the conv weights (rounded to bf16 like the weights themselves).  The extra K is free
         while cin + cout still fits the channel chunk the conv would use anyway, so callers use it for narrow convs."""
-        wt = conv.weight
+        wt = _cpu(conv.weight)
         co, ci, kh, kw = (int(v) for v in wt.shape)
         if pair.c != ci + co or conv.stride[0] != 1 or kh % 2 == 0 or kw % 2 == 0:
             raise RuntimeError(f"{tag}: conv_bn_act_add needs [conv input | branch] channels and an odd stride-1 kernel")
-        sc, sf = P.fold_bn(co, _bn_dict(bn), conv.bias, wt.device)
-        w = torch.zeros(co, ci + co, kh, kw, dtype=torch.float32, device=wt.device)
-        w[:, :ci] = wt.detach().float() * sc.view(-1, 1, 1, 1)
-        idx = torch.arange(co, device=wt.device)
+        sc, sf = P.fold_bn(co, _bn_dict(bn), _cpu(conv.bias), "cpu")
+        w = torch.zeros(co, ci + co, kh, kw, dtype=torch.float32)
+        w[:, :ci] = wt.float() * sc.view(-1, 1, 1, 1)
+        idx = torch.arange(co)
         w[idx, ci + idx, kh // 2, kw // 2] = 1.0
         before = self.flops
         y = self.conv(pair, [(w, None, sf, act != A.ACT_NONE)], 1, _pad4(conv), act, None, out, tag=tag)
@@ -368,22 +395,23 @@ class Graph:
         if conv.groups != c or int(conv.weight.shape[0]) != c:
             raise RuntimeError(f"{tag}: not a depthwise convolution over {c} channels")
         out = View(self.new_buf(x.n, oh, ow, x.c_p, x.dtype), 0, x.lanes)
-        wt = conv.weight.detach().float().reshape(c, k * k).t()            # [k*k][c]
-        w = torch.zeros(k * k, x.c_p, dtype=torch.float32, device=wt.device)
-        idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0], device=wt.device)
-        src = torch.tensor([v for v in x.lanes if v >= 0], device=wt.device)
+        wt = _cpu(conv.weight).float().reshape(c, k * k).t()               # [k*k][c]
+        w = torch.zeros(k * k, x.c_p, dtype=torch.float32)
+        idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0])
+        src = torch.tensor([v for v in x.lanes if v >= 0])
         w[:, idx] = wt[:, src]
-        sc, sf = P.fold_bn(c, _bn_dict(bn), conv.bias, wt.device)
+        sc, sf = P.fold_bn(c, _bn_dict(bn), _cpu(conv.bias), "cpu")
         w, sc, sf = self._dev(w), self._dev(P.place_lanes(sc, x.lanes)), self._dev(P.place_lanes(sf, x.lanes))
         pool_t = None
         if pool:
-            # zeroed once here; se_gate's FC kernel clears it again after reading (EdeSeFc.clear_pool), so a
-            # forward needs no fill launch
-            pool_t = self._dev(torch.zeros(x.n, x.c_p, dtype=torch.float32))
-        st = A.EdeDwConv(x=None, y=None, w=self._ptr(w), scale=self._ptr(sc), shift=self._ptr(sf),
-                         pool_sum=self._ptr(pool_t), n=x.n, h=x.h, w_=x.w, c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
+            # zeroed once at plan build; se_gate's FC kernel clears it again after reading (EdeSeFc.clear_pool), so a
+            # forward needs no fill launch (Plan.run re-zeroes the pools if a forward fails half way)
+            pool_t = self._reserve(x.n * x.c_p * 4, zero=True)
+        st = A.EdeDwConv(x=None, y=None, w=None, scale=None, shift=None, pool_sum=None, n=x.n, h=x.h, w_=x.w,
+                         c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
                          oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype)
-        self._add(A.OP_DWCONV, st, [("x", x.buf), ("y", out.buf)], tag)
+        self._add(A.OP_DWCONV, st, [("x", x.buf), ("y", out.buf)], tag,
+                  [("w", w), ("scale", sc), ("shift", sf), ("pool_sum", pool_t)])
         self.flops += 2.0 * x.n * oh * ow * c * k * k
         self.exec_flops += 2.0 * x.n * oh * ow * c * k * k
         return out, pool_t
@@ -391,28 +419,27 @@ class Graph:
     def se_gate(self, x: View, pool_t, reduce_conv, expand_conv, tag="se") -> View:
         """Squeeze-excite: gate = sigmoid(W2 swish(W1 mean + b1) + b2); returns x * gate."""
         c, csq = x.c, int(reduce_conv.weight.shape[0])
-        dev = reduce_conv.weight.device
-        idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0], device=dev)
-        src = torch.tensor([v for v in x.lanes if v >= 0], device=dev)
+        idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0])
+        src = torch.tensor([v for v in x.lanes if v >= 0])
         if idx.tolist() != list(range(c)):
             raise RuntimeError("se_gate: channels must occupy lanes 0..c-1")
-        w1 = torch.zeros(csq, x.c_p, dtype=torch.float32, device=dev)
-        w1[:, idx] = reduce_conv.weight.detach().float().reshape(csq, c)[:, src]
-        w2 = torch.zeros(csq, x.c_p, dtype=torch.float32, device=dev)              # [csq][c_p]: coalesced reads
-        w2[:, idx] = expand_conv.weight.detach().float().reshape(c, csq)[src].t()
-        b2 = torch.zeros(x.c_p, dtype=torch.float32, device=dev)
-        b2[idx] = expand_conv.bias.detach().float()[src]
+        w1 = torch.zeros(csq, x.c_p, dtype=torch.float32)
+        w1[:, idx] = _cpu(reduce_conv.weight).float().reshape(csq, c)[:, src]
+        w2 = torch.zeros(csq, x.c_p, dtype=torch.float32)                          # [csq][c_p]: coalesced reads
+        w2[:, idx] = _cpu(expand_conv.weight).float().reshape(c, csq)[src].t()
+        b2 = torch.zeros(x.c_p, dtype=torch.float32)
+        b2[idx] = _cpu(expand_conv.bias).float()[src]
         w1, w2, b2 = self._dev(w1), self._dev(w2), self._dev(b2)
-        b1 = self._dev(reduce_conv.bias.detach().float())
-        gate = self._dev(torch.zeros(x.n, x.c_p, dtype=torch.float32))
-        st = A.EdeSeFc(pool_sum=self._ptr(pool_t), w1=self._ptr(w1), b1=self._ptr(b1), w2=self._ptr(w2),
-                       b2=self._ptr(b2), gate=self._ptr(gate), n=x.n, c=c, c_p=x.c_p, csq=csq,
+        b1 = self._dev(_cpu(reduce_conv.bias).float())
+        gate = self._reserve(x.n * x.c_p * 4, zero=True)
+        st = A.EdeSeFc(pool_sum=None, w1=None, b1=None, w2=None, b2=None, gate=None, n=x.n, c=c, c_p=x.c_p, csq=csq,
                        inv_hw=1.0 / (x.h * x.w), clear_pool=1, w2_transposed=1)
-        self._add(A.OP_SE_FC, st, [], tag + ".fc")
+        self._add(A.OP_SE_FC, st, [], tag + ".fc",
+                  [("pool_sum", pool_t), ("w1", w1), ("b1", b1), ("w2", w2), ("b2", b2), ("gate", gate)])
         out = View(self.new_buf(x.n, x.h, x.w, x.c_p, x.dtype), 0, x.lanes)
-        st = A.EdeSeScale(x=None, y=None, gate=self._ptr(gate), n=x.n, hw=x.h * x.w, c_p=x.c_p,
+        st = A.EdeSeScale(x=None, y=None, gate=None, n=x.n, hw=x.h * x.w, c_p=x.c_p,
                           x_cs=x.buf.cs, x_co=x.co, y_cs=out.buf.cs, y_co=out.co, dtype=x.dtype)
-        self._add(A.OP_SE_SCALE, st, [("x", x.buf), ("y", out.buf)], tag + ".scale")
+        self._add(A.OP_SE_SCALE, st, [("x", x.buf), ("y", out.buf)], tag + ".scale", [("gate", gate)])
         return out
 
     def upconv(self, x: View, size, parts, pad, act, tag="upconv") -> View:
@@ -424,12 +451,13 @@ class Graph:
         cin = x.c
         rows, scales, shifts, out_lanes, act_end = [], [], [], [], 0
         for (wt, bn, bias, activated) in parts:
+            wt, bias = _cpu(wt), _cpu(bias)
             co = int(wt.shape[0])
             co_p = P.ceil8(co)
-            w = torch.zeros(co_p, cin, k, k, dtype=torch.float32, device=wt.device)
-            w[:co] = wt.detach().float()
+            w = torch.zeros(co_p, cin, k, k, dtype=torch.float32)
+            w[:co] = wt.float()
             rows.append(w)
-            sc, sf = P.fold_bn(co, _bn_dict(bn), bias, wt.device)
+            sc, sf = P.fold_bn(co, _bn_dict(bn), bias, "cpu")
             omap = P.identity_map(co)
             scales.append(P.place_lanes(sc, omap))
             shifts.append(P.place_lanes(sf, omap))
@@ -449,10 +477,11 @@ class Graph:
         scale, shift = self._dev(torch.cat(scales)), self._dev(torch.cat(shifts))
         # fp32 workspace of the separable gather: [n][h][k][ow][cgrp] (x-lerp of every tap on the low-res rows)
         rows = self.new_buf(x.n, x.h, k * ow, cgrp, A.F32)
-        st = A.EdeUpConv(z=None, y=None, scale=self._ptr(scale), shift=self._ptr(shift), rows=None, n=x.n, h=x.h, w=x.w,
+        st = A.EdeUpConv(z=None, y=None, scale=None, shift=None, rows=None, n=x.n, h=x.h, w=x.w,
                          z_cs=z.buf.cs, z_co=z.co, oh=oh, ow=ow, cgrp=cgrp, y_cs=out.buf.cs, y_co=out.co,
                          y_dtype=out.dtype, kh=k, kw=k, pt=pad[0], pl=pad[1], act=act, act_c_end=act_end)
-        self._add(A.OP_UPCONV, st, [("z", z.buf), ("y", out.buf), ("rows", rows)], tag + ".taps")
+        self._add(A.OP_UPCONV, st, [("z", z.buf), ("y", out.buf), ("rows", rows)], tag + ".taps",
+                  [("scale", scale), ("shift", shift)])
         self.exec_flops += 2.0 * x.n * oh * ow * cgrp * k * k * 4
         return out
 
@@ -534,32 +563,82 @@ class Graph:
 
 
 class Plan:
-    """A compiled forward: EdeOp array + arena + prepacked weights.  `run` is one C call."""
+    """A compiled forward: EdeOp array + arena + prepacked weights.  `run` is one C call (or one CUDA-graph launch).
+
+    Device state: `arena` (activations, laid out by liveness) and `weights` (ONE blob: folded-BN vectors, depthwise /
+    SE / stem weights, the conv operands written by ede_prepack_conv_to, and the zero-initialised squeeze-excite
+    state).  Building it issues one host->device copy per blob and one prepack kernel per dense conv -- no eager
+    tensor ops on the GPU."""
 
     def __init__(self, g: Graph, arena_bytes: int):
         self.device, self.precision, self.dry = g.device, g.precision, g.dry
         self.arena_bytes = arena_bytes
-        self.keep = g.keep
         self.flops = g.flops
         self.exec_flops = g.exec_flops
         self.tags = [t for (_, _, _, t) in g.ops]
         self.kinds = [k for (k, _, _, _) in g.ops]
         self.inputs, self.outputs = g.inputs, g.outputs
         self.n_ops = len(g.ops)
-        self.arena = None
-        base = 0
+        self.arena = self.weights = None
+        self.graph_ok = True
+        # ---- weight blob layout: uploaded regions first (one host image), then device-only regions
+        live = [st for st in g.stages if not st.temp]
+        temps = [st for st in g.stages if st.temp]
+        top = 0
+        for st in sorted(live, key=lambda st: st.t is None):
+            st.offset = top
+            top += (st.nbytes + 255) // 256 * 256
+        self.weight_bytes = top
+        upload_bytes = max([st.offset + st.nbytes for st in live if st.t is not None], default=0)
+        t_top = 0
+        for st in temps:
+            st.offset = t_top
+            t_top += (st.nbytes + 255) // 256 * 256
+        self._zero_regions = [(st.offset, st.nbytes) for st in live if st.zero]
+        base = wbase = 0
         if not self.dry:
-            self.arena = torch.empty(arena_bytes + _ALIGN, dtype=torch.uint8, device=self.device)
-            base = (self.arena.data_ptr() + _ALIGN - 1) // _ALIGN * _ALIGN
+            with torch.cuda.device(self.device):
+                self.arena = torch.empty(arena_bytes + _ALIGN, dtype=torch.uint8, device=self.device)
+                base = (self.arena.data_ptr() + _ALIGN - 1) // _ALIGN * _ALIGN
+                self.weights = torch.empty(max(top, 256), dtype=torch.uint8, device=self.device)
+                wbase = self.weights.data_ptr()
+                self._upload(self.weights, [st for st in live if st.t is not None], upload_bytes)
+                for off, nb in self._zero_regions:
+                    A.check(A.lib().ede_fill_zero(wbase + off, nb, self._stream()), "ede_fill_zero")
+                if g.prepacks:
+                    stage = torch.empty(max(t_top, 256), dtype=torch.uint8, device=self.device)
+                    self._upload(stage, temps, t_top)
+                    for job in g.prepacks:
+                        A.prepack_to(job, stage.data_ptr(), wbase, self._stream())
+                    stage.record_stream(torch.cuda.current_stream(self.device))
+                    del stage
         self.ops = (A.EdeOp * max(1, self.n_ops))()
         for i, (kind, st, refs, _) in enumerate(g.ops):
             for field, b in refs:
                 setattr(st, field, base + b.offset if not self.dry else 1 + b.offset)
+            for field, w in getattr(st, "_wrefs", ()):
+                setattr(st, field, wbase + w.offset if not self.dry else 1 + w.offset)
             self.ops[i].kind = kind
             setattr(self.ops[i].u, A.OP_FIELD[kind], st)
         self.structs = [st for (_, st, _, _) in g.ops]      # host copies (introspection / tests)
-        self._graph = None
+        for st in g.stages:                                  # host tensors are not needed any more
+            st.t = None
         self._lock = threading.Lock()
+        self._last = None                                    # (stream id, event) of the previous run
+        self._cg = None                                      # CUDA-graph replay state (enable_graph)
+
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    @staticmethod
+    def _upload(blob: torch.Tensor, stages, nbytes: int) -> None:
+        """One host image of the regions -> one host->device copy."""
+        if nbytes <= 0 or not stages:
+            return
+        host = torch.zeros(nbytes, dtype=torch.uint8)
+        for st in stages:
+            host[st.offset:st.offset + st.nbytes] = st.t.reshape(-1).view(torch.uint8)
+        blob[:nbytes].copy_(host)
 
     def conv_configs(self):
         """(tag, EdeConv, EdeUmmaCfg) of every dense conv -- which path each one takes."""
@@ -572,30 +651,90 @@ class Plan:
     def launches_per_run(self) -> int:
         return self.n_ops
 
-    def run(self, tensors: Sequence[torch.Tensor]) -> List[torch.Tensor]:
+    def _rezero_state(self):
+        """A forward that failed between a depthwise conv and its SE FC leaves dirty squeeze sums behind."""
+        wbase = self.weights.data_ptr()
+        for off, nb in self._zero_regions:
+            A.lib().ede_fill_zero(wbase + off, nb, self._stream())
+
+    def _guard_streams(self):
+        """The arena and the SE state are per-plan: a run on another stream waits for the previous run."""
+        cur = torch.cuda.current_stream(self.device)
+        if self._last is not None and self._last[0] != cur.cuda_stream:
+            cur.wait_event(self._last[1])
+        return cur
+
+    def _mark_done(self, cur):
+        if self._last is None or self._last[0] != cur.cuda_stream:
+            self._last = (cur.cuda_stream, torch.cuda.Event())
+        self._last[1].record(cur)
+
+    def _check_inputs(self, tensors):
         if self.dry:
             raise RuntimeError("efficientdepthestimation_b200: this plan was compiled without a CUDA device; "
                                "there is no CPU execution path")
         if len(tensors) != len(self.inputs):
             raise RuntimeError(f"plan expects {len(self.inputs)} input tensors, got {len(tensors)}")
-        outs = []
+        hold = []
+        for inp, t in zip(self.inputs, tensors):
+            if tuple(t.shape) != inp["shape"]:
+                raise RuntimeError(f"plan compiled for input {inp['shape']}, got {tuple(t.shape)}")
+            if t.dtype != torch.float32 or not t.is_contiguous():
+                t = t.float().contiguous()
+            hold.append(t)
+        return hold
+
+    def _enqueue(self, hold, outs):
+        for inp, t in zip(self.inputs, hold):
+            for i, field in inp["targets"]:
+                setattr(getattr(self.ops[i].u, A.OP_FIELD[self.kinds[i]]), field, t.data_ptr())
+        for (i, _), o in zip(self.outputs, outs):
+            self.ops[i].u.layout.dst = o.data_ptr()
+        rc = A.lib().ede_plan_run(self.ops, self.n_ops, self._stream())
+        if rc != 0:
+            msg = A.lib().ede_last_error().decode(errors="replace")
+            self._rezero_state()
+            raise RuntimeError(f"ede_plan_run failed (code {rc}): {msg}")
+
+    def run(self, tensors: Sequence[torch.Tensor]) -> List[torch.Tensor]:
+        hold = self._check_inputs(tensors)
         with self._lock, torch.cuda.device(self.device):
-            hold = []
-            for inp, t in zip(self.inputs, tensors):
-                if tuple(t.shape) != inp["shape"]:
-                    raise RuntimeError(f"plan compiled for input {inp['shape']}, got {tuple(t.shape)}")
-                if t.dtype != torch.float32 or not t.is_contiguous():
-                    t = t.float().contiguous()
-                hold.append(t)
-                for i, field in inp["targets"]:
-                    setattr(getattr(self.ops[i].u, A.OP_FIELD[self.kinds[i]]), field, t.data_ptr())
-            for (i, shape) in self.outputs:
-                o = torch.empty(shape, dtype=torch.float32, device=self.device)
-                self.ops[i].u.layout.dst = o.data_ptr()
-                outs.append(o)
-            st = torch.cuda.current_stream(self.device).cuda_stream
-            A.check(A.lib().ede_plan_run(self.ops, self.n_ops, st), "ede_plan_run")
+            cur = self._guard_streams()
+            if self._cg is not None:
+                outs = self._replay_graph(hold)
+            else:
+                outs = [torch.empty(shape, dtype=torch.float32, device=self.device) for _, shape in self.outputs]
+                self._enqueue(hold, outs)
+            self._mark_done(cur)
         return outs
+
+    # ------------------------------------------------------------------ CUDA-graph replay (launch-bound small batches)
+    def enable_graph(self) -> None:
+        """Capture the plan's launches once into a CUDA graph over STATIC input / output buffers; `run` then costs one
+        device-to-device input copy, one graph launch and one output copy.  Pays where the forward is launch-bound
+        (batch 1: ~110 kernels of a few microseconds each)."""
+        if self.dry or self._cg is not None:
+            return
+        with self._lock, torch.cuda.device(self.device):
+            ins = [torch.zeros(inp["shape"], dtype=torch.float32, device=self.device) for inp in self.inputs]
+            outs = [torch.empty(shape, dtype=torch.float32, device=self.device) for _, shape in self.outputs]
+            side = torch.cuda.Stream(self.device)
+            side.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(side):
+                self._enqueue(ins, outs)                       # warm-up outside capture (lazy attribute setting etc.)
+                side.synchronize()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, stream=side):
+                    self._enqueue(ins, outs)
+            torch.cuda.current_stream(self.device).wait_stream(side)
+            self._cg = (graph, ins, outs)
+
+    def _replay_graph(self, hold):
+        graph, ins, outs = self._cg
+        for dst, src in zip(ins, hold):
+            dst.copy_(src, non_blocking=True)
+        graph.replay()
+        return [o.clone() for o in outs]
 
 
 # ---------------------------------------------------------------------- module protocol

@@ -24,7 +24,7 @@ def test_header_symbols_are_exported(lib):
 
 
 def test_version_and_error_plumbing(lib):
-    assert lib.ede_version() == 5
+    assert lib.ede_version() == 6
     assert lib.ede_fill_zero(None, -1, None) == -1            # EDE_E_ARG, no GPU touched
     assert b"ede_fill_zero" in lib.ede_last_error()
     assert lib.ede_plan_run(None, 0, None) == 0
@@ -36,9 +36,10 @@ def test_struct_sizes_match_header():
     src = r'''
     #include <stdio.h>
     #include "ede.h"
-    int main(){ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(EdeConv), sizeof(EdeUmmaCfg),
+    int main(){ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(EdeConv), sizeof(EdeUmmaCfg),
       sizeof(EdeDwConv), sizeof(EdeSeFc), sizeof(EdeSeScale), sizeof(EdeResize), sizeof(EdeMaxPool),
-      sizeof(EdeEltwise), sizeof(EdeLayout), sizeof(EdeOp), sizeof(EdeUpConv)); return 0; }'''
+      sizeof(EdeEltwise), sizeof(EdeLayout), sizeof(EdeOp), sizeof(EdeUpConv), sizeof(EdePrepackConv),
+      sizeof(EdePackedConv)); return 0; }'''
     import tempfile
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "s.c")
@@ -47,7 +48,8 @@ def test_struct_sizes_match_header():
         subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), c, "-o", exe])
         sizes = [int(v) for v in subprocess.check_output([exe]).split()]
     mine = [ctypes.sizeof(t) for t in (A.EdeConv, A.EdeUmmaCfg, A.EdeDwConv, A.EdeSeFc, A.EdeSeScale, A.EdeResize,
-                                       A.EdeMaxPool, A.EdeEltwise, A.EdeLayout, A.EdeOp, A.EdeUpConv)]
+                                       A.EdeMaxPool, A.EdeEltwise, A.EdeLayout, A.EdeOp, A.EdeUpConv, A.EdePrepackConv,
+                                       A.EdePackedConv)]
     assert mine == sizes
 
 
@@ -61,3 +63,17 @@ def test_umma_config_is_pure_host(lib):
     assert 0.5 < cfg.useful_frac <= 1.0
     a.x_dtype = A.F32
     assert A.umma_config(a).eligible == 0                      # fp32 activations take the exact SIMT path
+
+
+def test_prepack_sizes_is_pure_host(lib):
+    """ede_prepack_conv_sizes: the buffer sizes a C caller must allocate (no GPU touched)."""
+    a = A.EdePrepackConv(cout=74, cin=74, kh=5, kw=5, cin_p=80, cout_p=80, passes=1, pack_g=1)
+    b, d = (ctypes.c_int64 * 4)(), (ctypes.c_int32 * 2)()
+    assert lib.ede_prepack_conv_sizes(ctypes.byref(a), b, d) == 0
+    assert list(d) == [80, 128] and list(b) == [25 * 80 * 128 * 2, 25 * 80 * 80 * 4, 320, 320]
+    a.pack_g, a.cout, a.cout_p, a.passes = 4, 16, 16, 2                  # 4 taps of a kernel row on the 128 M rows
+    assert lib.ede_prepack_conv_sizes(ctypes.byref(a), b, d) == 0
+    assert list(d) == [128, 128] and b[0] == 2 * 5 * 2 * 128 * 128 * 2
+    a.cout_p = 40                                                        # does not fit 4 taps
+    assert lib.ede_prepack_conv_sizes(ctypes.byref(a), b, d) == -1 and b"do not fit" in lib.ede_last_error()
+    assert lib.ede_prepack_conv(None, None, None) == -1 and lib.ede_free(None) == 0
