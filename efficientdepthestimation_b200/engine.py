@@ -844,11 +844,32 @@ def compile_module(module, args, device: torch.device, precision: Optional[str] 
     return g.finalize(), out_spec, tuple(spec)
 
 
+_WEIGHT_EPOCH = [0]        # bumped by load_state_dict / .to() / .train() of ANY EdeModule: plans of parents go stale too
+
+
+def _fingerprint(module):
+    """(storage address, in-place version counter) of every parameter and buffer: catches in-place writes and
+    re-assignments on any submodule (model.E.load_state_dict, p.data.copy_, optimiser steps) that no hook sees."""
+    fp = []
+    for t in module.parameters():
+        fp.append((t.data_ptr(), t._version))
+    for t in module.buffers():
+        fp.append((t.data_ptr(), t._version))
+    return tuple(fp)
+
+
 class EdeModule:
     """Mixin giving an nn.Module the B200 `forward`: compile once per signature, then replay.
 
     Mirrors the reference's calling convention (fp32 NCHW in, fp32 NCHW out, eval mode).
-    training=True, CPU tensors or a missing CUDA library raise -- there is no fallback."""
+    training=True, CPU tensors or a missing CUDA library raise -- there is no fallback.
+
+    Compiled plans hold PREPACKED COPIES of the weights.  They are keyed by (input signature, precision, encoder
+    precision, device) and validated on every call against (a) a process-wide epoch that any EdeModule's
+    load_state_dict / .to() / .train() bumps and (b) a fingerprint of the module's parameters and buffers, so a
+    weight change on any submodule recompiles instead of silently running old weights.  `freeze_plans()` skips (b)
+    for latency-critical loops that own their weights; DataParallel replicas (fresh broadcast copies of the source
+    module's weights on every call) are validated by epoch only."""
 
     def _ede_cache(self) -> dict:
         c = self.__dict__.get("_ede_plans")
@@ -860,9 +881,14 @@ class EdeModule:
     def invalidate_plans(self) -> None:
         """Drop compiled plans (weights changed: load_state_dict, .to(), .train())."""
         from torch import nn
+        _WEIGHT_EPOCH[0] += 1
         for m in self.modules() if isinstance(self, nn.Module) else [self]:
             if "_ede_plans" in m.__dict__:
                 m.__dict__["_ede_plans"] = {}
+
+    def freeze_plans(self, frozen: bool = True) -> None:
+        """Promise that weights only change through load_state_dict / .to() / .train(): skip the per-call fingerprint."""
+        self.__dict__["_ede_frozen"] = bool(frozen)
 
     def _apply(self, fn, *a, **kw):
         r = super()._apply(fn, *a, **kw)
@@ -889,20 +915,30 @@ class EdeModule:
             new.__dict__[k] = {} if k == "_ede_plans" else copy.deepcopy(v, memo)
         return new
 
-    def plan_for(self, *args, precision: Optional[str] = None) -> "Plan":
+    def plan_for(self, *args, precision: Optional[str] = None):
         tensors, spec = [], []
         for a in args:
             _flatten(a, tensors, spec)
         if not tensors:
             raise RuntimeError(f"{type(self).__name__}.forward needs at least one tensor argument")
         dev = tensors[0].device
-        key = (tuple(spec), precision or _PRECISION, str(dev))
+        key = (tuple(spec), precision or _PRECISION, _ENCODER_PRECISION, str(dev))
         cache = self._ede_cache()
         hit = cache.get(key)
+        replica = bool(getattr(self, "_is_replica", False))
+        check_fp = not replica and not self.__dict__.get("_ede_frozen", False)
+        if hit is not None:
+            stale = hit[3] != _WEIGHT_EPOCH[0] or (check_fp and hit[4] is not None and hit[4] != _fingerprint(self))
+            if stale:
+                hit = None
         if hit is None:
-            hit = compile_module(self, args, dev, precision)
+            plan, out_spec, in_spec = compile_module(self, args, dev, precision)
+            if os.environ.get("EDE_CUDA_GRAPH", "auto") == "1" or (
+                    os.environ.get("EDE_CUDA_GRAPH", "auto") == "auto" and not plan.dry and _graph_pays(plan)):
+                plan.enable_graph()
+            hit = (plan, out_spec, in_spec, _WEIGHT_EPOCH[0], None if replica else _fingerprint(self))
             cache[key] = hit
-        return hit
+        return hit[0], hit[1], hit[2]
 
     def forward(self, *args):
         if self.training:
@@ -920,3 +956,10 @@ class EdeModule:
         plan, out_spec, _ = self.plan_for(*args)
         outs = plan.run(tensors)
         return _rebuild_out(out_spec, iter(outs))
+
+
+def _graph_pays(plan: "Plan") -> bool:
+    """CUDA-graph replay for launch-bound plans: few images, so every kernel runs for only a few microseconds."""
+    n = max((inp["shape"][0] for inp in plan.inputs), default=0)
+    px = max((inp["shape"][0] * inp["shape"][2] * inp["shape"][3] for inp in plan.inputs), default=0)
+    return n > 0 and px <= 4 * 384 * 384

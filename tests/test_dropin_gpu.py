@@ -74,9 +74,7 @@ for encoder_type, variant, arch in ((E_efficientnet, "efficientnet-b0", "enb0-hu
         assert len(devs) >= 2, devs
         for key, entry in plans.items():
             plan = entry[0]
-            for t in plan.keep:
-                assert str(t.device) == key[-1], (key, t.device)
-            assert str(plan.arena.device) == key[-1]
+            assert str(plan.weights.device) == key[-1] and str(plan.arena.device) == key[-1], key
         single = define_model(is_resnet=encoder_type == E_resnet, is_efficientnet=encoder_type == E_efficientnet,
                               efficientnet_variant=variant or "efficientnet-b0")
         single.load_state_dict(state_dict)

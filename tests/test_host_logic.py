@@ -157,3 +157,52 @@ def test_metrics_from_sums_reproduce_reference_quirk():
     t.update_from_sums(s)
     d = t.to_dict()
     assert abs(d["mae"] - 0.2) < 1e-12 and abs(d["log10"] - m["log10"]) < 1e-12 and abs(d["rmse"] - 0.5 ** 0.5) < 1e-12
+
+
+def test_plan_cache_goes_stale_with_the_weights(lib):
+    """Compiled plans hold prepacked COPIES of the weights: any weight change on any submodule must recompile
+    (`model.E.load_state_dict`, in-place parameter writes, `set_precision(encoder=...)`)."""
+    from efficientdepthestimation_b200 import engine
+    m = factory.build_model("enb0-hu").eval()
+    x = torch.empty(1, 3, 64, 96)
+    p0 = m.plan_for(x)[0]
+    assert m.plan_for(x)[0] is p0                                   # cached
+    m.E.load_state_dict(m.E.state_dict())                           # submodule load: the PARENT's plan is stale too
+    p1 = m.plan_for(x)[0]
+    assert p1 is not p0 and m.plan_for(x)[0] is p1
+    with torch.no_grad():
+        m.R.conv2.bias.add_(1.0)                                    # in-place write on a plain nn.Conv2d child
+    p2 = m.plan_for(x)[0]
+    assert p2 is not p1
+    m.freeze_plans()                                                # opt out of the per-call fingerprint ...
+    with torch.no_grad():
+        m.R.conv2.bias.add_(1.0)
+    assert m.plan_for(x)[0] is p2
+    m.D.load_state_dict(m.D.state_dict())                           # ... the epoch still catches load_state_dict
+    p3 = m.plan_for(x)[0]
+    assert p3 is not p2
+    m.freeze_plans(False)
+    try:
+        engine.set_precision("bf16", encoder="bf16")
+        p4 = m.plan_for(x)[0]
+        assert p4 is not p3                                         # encoder precision is part of the key
+    finally:
+        engine.set_precision("bf16", encoder="bf16x2")
+    assert m.plan_for(x)[0] is p3
+
+
+def test_plan_build_packs_on_the_host_and_reserves_device_regions(lib):
+    """Dry compile: every conv has one prepack job (host fp32 weight staged, device region reserved), the SE state is
+    a zero-initialised region, and nothing of the plan refers to a torch GPU tensor."""
+    from efficientdepthestimation_b200.engine import Graph, emit
+    m = factory.build_model("enb0-hu").eval()
+    g = Graph(torch.device("cpu"), "bf16")
+    with torch.no_grad():
+        y = emit(m, g, g.input_nchw((1, 3, 228, 304)))
+        g.output_nchw(y)
+    n_conv = sum(1 for k, *_ in g.ops if k == A.OP_CONV)
+    assert len(g.prepacks) == n_conv >= 50
+    assert all(j["w_umma"] is not None and j["w_direct"] is None and j["full"].temp for j in g.prepacks)
+    assert sum(1 for st in g.stages if st.zero) == 2 * 16            # pool sums + gates of the 16 MBConv blocks
+    plan = g.finalize()
+    assert plan.weight_bytes > 0 and plan.weights is None and all(st.t is None for st in g.stages)
