@@ -416,3 +416,74 @@ def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, 
     assert got.shape == ref.shape
     # output stored as bf16 (2^-9) on top of bf16 weights (identical on both sides)
     assert bool(((got - ref).abs() <= 5e-3 * ref.abs() + 5e-3).all()), float((got - ref).abs().max())
+
+
+@pytest.mark.parametrize("cout,cin,k,passes,pack_g,use_maps,use_bn,use_bias", [
+    (74, 74, 5, 1, 1, False, True, False),        # R.conv0: identity lanes, BN
+    (136, 250, 1, 2, 1, True, True, False),       # split-precision encoder 1x1 with a scattered lane order
+    (16, 48, 3, 1, 4, True, False, True),         # 4 kernel-row taps on the 128 M rows, conv bias, no BN
+    (40, 40, 5, 2, 2, False, True, True),         # 2 taps, hi+lo passes, BN + bias
+    (1, 74, 5, 1, 1, False, False, True),         # R.conv2: one output channel + bias
+])
+def test_prepack_conv_behind_the_c_abi(cuda, lib, cout, cin, k, passes, pack_g, use_maps, use_bn, use_bias):
+    """ede_prepack_conv_to / ede_prepack_conv / ede_free: OIHW weight + BatchNorm vectors -> w_umma / w_direct / scale /
+    shift, bit-exact against the host packing functions (prepack.py) that the round-1 engine used."""
+    g = torch.Generator().manual_seed(cout * 131 + cin)
+    w = torch.randn(cout, cin, k, k, generator=g)
+    cin_p, cout_p = P.ceil8(cin) + (8 if use_maps else 0), P.ceil8(cout) + (8 if use_maps else 0)
+    if pack_g > 1:
+        cout_p = P.ceil8(cout)
+    if use_maps:
+        in_map = torch.full((cin_p,), -1, dtype=torch.int32)
+        in_map[torch.randperm(cin_p, generator=g)[:cin]] = torch.randperm(cin, generator=g).int()
+        out_map = torch.full((cout_p,), -1, dtype=torch.int32)
+        out_map[torch.randperm(cout_p, generator=g)[:cout]] = torch.randperm(cout, generator=g).int()
+    else:
+        in_map = torch.tensor(P.identity_map(cin, cin_p), dtype=torch.int32)
+        out_map = torch.tensor(P.identity_map(cout, cout_p), dtype=torch.int32)
+    bn = dict(weight=0.5 + torch.rand(cout, generator=g), bias=torch.randn(cout, generator=g),
+              mean=torch.randn(cout, generator=g), var=0.1 + torch.rand(cout, generator=g), eps=1e-3) if use_bn else None
+    bias = torch.randn(cout, generator=g) if use_bias else None
+    # expected: the host functions
+    full = P.scatter_weight(w, in_map.tolist(), out_map.tolist())
+    exp_umma, co16, ci64 = (P.pack_umma_taps(full, passes, pack_g) if pack_g > 1 else P.pack_umma(full, passes))
+    exp_direct = P.pack_direct(full)
+    sc, sf = P.fold_bn(cout, bn, bias, "cpu")
+    exp_scale, exp_shift = P.place_lanes(sc, out_map.tolist()), P.place_lanes(sf, out_map.tolist())
+    d = lambda t: None if t is None else t.cuda()                      # noqa: E731
+    wd, imd, omd, bd = d(w), d(in_map), d(out_map), d(bias)
+    bnd = {kk: d(v) for kk, v in bn.items() if kk != "eps"} if bn else {}
+    a = A.EdePrepackConv(w_oihw=wd.data_ptr(), in_map=imd.data_ptr() if use_maps else None,
+                         out_map=omd.data_ptr() if use_maps else None,
+                         bn_weight=bnd["weight"].data_ptr() if bn else None, bn_bias=bnd["bias"].data_ptr() if bn else None,
+                         bn_mean=bnd["mean"].data_ptr() if bn else None, bn_var=bnd["var"].data_ptr() if bn else None,
+                         bias=bd.data_ptr() if use_bias else None, bn_eps=1e-3, cout=cout, cin=cin, kh=k, kw=k,
+                         cin_p=cin_p, cout_p=cout_p, passes=passes, pack_g=pack_g)
+    b4, d2 = (C.c_int64 * 4)(), (C.c_int32 * 2)()
+    A.check(lib.ede_prepack_conv_sizes(C.byref(a), b4, d2))
+    assert list(d2) == [co16, ci64] and b4[0] == exp_umma.numel() * 2 and b4[1] == exp_direct.numel() * 4
+    # (1) caller-provided buffers
+    o_umma = torch.full((b4[0] // 2,), 7.0, dtype=torch.bfloat16, device="cuda")
+    o_direct = torch.full((b4[1] // 4,), 7.0, device="cuda")
+    o_scale, o_shift = torch.full((cout_p,), 7.0, device="cuda"), torch.full((cout_p,), 7.0, device="cuda")
+    a.w_umma, a.w_direct, a.scale, a.shift = o_umma.data_ptr(), o_direct.data_ptr(), o_scale.data_ptr(), o_shift.data_ptr()
+    A.check(lib.ede_prepack_conv_to(C.byref(a), stream()))
+    torch.cuda.synchronize()
+    assert torch.equal(o_umma.cpu().view(torch.int16), exp_umma.reshape(-1).view(torch.int16))
+    assert torch.equal(o_direct.cpu(), exp_direct.reshape(-1))
+    assert torch.allclose(o_scale.cpu(), exp_scale, rtol=2e-7, atol=0) and torch.allclose(o_shift.cpu(), exp_shift, rtol=4e-7, atol=1e-7)
+    # (2) the allocating form a C-only caller would use
+    a.w_umma = a.w_direct = a.scale = a.shift = None
+    h = C.POINTER(A.EdePackedConv)()
+    A.check(lib.ede_prepack_conv(C.byref(a), C.byref(h), stream()))
+    torch.cuda.synchronize()
+    hc = h.contents
+    assert (hc.w_umma_cout_p, hc.w_umma_cin_p, hc.w_passes, hc.w_pack_g) == (co16, ci64, passes, max(1, pack_g))
+    back = torch.empty(b4[0] // 2, dtype=torch.bfloat16, device="cuda")
+    try:
+        rt = C.CDLL("libcudart.so.12")
+    except OSError:
+        rt = C.CDLL("/usr/local/cuda/lib64/libcudart.so.12")
+    assert rt.cudaMemcpy(C.c_void_p(back.data_ptr()), C.c_void_p(hc.w_umma), C.c_size_t(b4[0]), 3) == 0   # D2D
+    assert torch.equal(back.cpu().view(torch.int16), exp_umma.reshape(-1).view(torch.int16))
+    assert lib.ede_free(h) == 0
