@@ -39,12 +39,13 @@ class EdeUmmaCfg(Structure):
 class EdeDwConv(Structure):
     _fields_ = [("x", c_void_p), ("y", c_void_p), ("w", c_void_p), ("scale", c_void_p), ("shift", c_void_p),
                 ("pool_sum", c_void_p)] + _ints(
-        "n", "h", "w_", "c_p", "x_cs", "x_co", "oh", "ow", "y_cs", "y_co", "k", "s", "pt", "pl", "act", "dtype")
+        "n", "h", "w_", "c_p", "x_cs", "x_co", "oh", "ow", "y_cs", "y_co", "k", "s", "pt", "pl", "act", "dtype",
+        "pool_parts")
 
 
 class EdeSeFc(Structure):
     _fields_ = [("pool_sum", c_void_p), ("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p),
-                ("gate", c_void_p)] + _ints("n", "c", "c_p", "csq") + [("inv_hw", c_float)] + _ints("clear_pool", "w2_transposed")
+                ("gate", c_void_p)] + _ints("n", "c", "c_p", "csq") + [("inv_hw", c_float)] + _ints("clear_pool", "w2_transposed", "pool_parts")
 
 
 class EdeSeScale(Structure):

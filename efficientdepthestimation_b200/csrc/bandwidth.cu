@@ -83,10 +83,15 @@ __global__ void __launch_bounds__(1024) se_fc_kernel(const EdeSeFc a) {
     const int n = blockIdx.x;
     pdl_trigger();
     pdl_wait();
+    const int parts = a.pool_parts > 1 ? a.pool_parts : 1;
     for (int i = threadIdx.x; i < a.c_p; i += blockDim.x) {
-        float* ps = a.pool_sum + (long long)n * a.c_p + i;
-        mean[i] = i < a.c ? *ps * a.inv_hw : 0.f;
-        if (a.clear_pool) *ps = 0.f;                       // ready for the next forward's squeeze
+        float sum = 0.f;
+        for (int s = 0; s < parts; ++s) {                  // slabs in order: the same rounding every forward
+            float* ps = a.pool_sum + ((long long)s * a.n + n) * a.c_p + i;
+            sum += *ps;
+            if (a.clear_pool) *ps = 0.f;                   // ready for the next forward's squeeze
+        }
+        mean[i] = i < a.c ? sum * a.inv_hw : 0.f;
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;

@@ -12,7 +12,8 @@
 //     channels live in registers; per output row a thread reads only the S new input rows from the ring.
 //     Window slots rotate by compile-time indices because the walk is unrolled K rows at a time.
 //   * The squeeze (per-(n, c) sum of the STORED activations) is a per-thread running sum, one smem reduction
-//     over the block's columns and one atomicAdd per channel per block.
+//     over the block's columns and one store per channel per block into the block's slab of pool_sum (atomicAdd
+//     only in the single-slab form).
 #include <stdlib.h>
 #include <string.h>
 
@@ -81,6 +82,7 @@ struct alignas(64) DwParams {
     int row_bytes;         // bytes of one ring slot: (cols * (64/CH) * S + K - S) pixels x CH lanes
     int tx_bytes;          // bytes one TMA row box delivers (row_bytes before the 128-byte rounding)
     int zsplit;            // grid.z: a block walks images blockIdx.z, blockIdx.z + zsplit, ...
+    int pool_write;        // 1: every column strip stores its squeeze sums into its own slab of pool_sum
 };
 
 template <int K> struct DwDepth { static constexpr int value = K >= 5 ? 16 : 8; };   // ring slots (power of 2)
@@ -212,7 +214,10 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
                     if (c0 + ch < a.c_p) {
                         float sum = 0.f;
                         for (int r = 0; r < n_act * SUB; ++r) sum += pool_s[r * CH + ch];
-                        atomicAdd(a.pool_sum + (long long)n * a.c_p + c0 + ch, sum);
+                        // one slab per column strip: plain stores, summed in slab order by se_fc (reproducible);
+                        // more strips than slabs (very wide maps): atomics on slab 0
+                        if (p.pool_write) a.pool_sum[((long long)blockIdx.x * a.n + n) * a.c_p + c0 + ch] = sum;
+                        else atomicAdd(a.pool_sum + (long long)n * a.c_p + c0 + ch, sum);
                     }
                 }
                 asm volatile("bar.sync 1, %0;" ::"r"(n_cons) : "memory");
@@ -290,6 +295,7 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
     p.zsplit = best_z;
     dim3 grid((unsigned)ceil_div(a.ow, p.cols * SUB * NC), (unsigned)ceil_div(a.c_p, CH), (unsigned)p.zsplit);
     if (grid.y > 65535u || grid.z > 65535u || smem > 200 * 1024) return 1;
+    p.pool_write = a.pool_sum != nullptr && a.pool_parts > 1 && (int)grid.x <= a.pool_parts;
     if (launch_pdl(dwconv_tma_kernel<T, K, S, CH, NC>, grid, dim3(32 * (p.cols + 1)), (size_t)smem, st, p) != cudaSuccess) {
         (void)cudaGetLastError();
         return 1;

@@ -27,6 +27,7 @@ _PRECISION = os.environ.get("EDE_PRECISION", "bf16")
 _ENCODER_PRECISION = os.environ.get("EDE_ENCODER_PRECISION", "bf16x2")
 _ELT = {A.F32: 4, A.BF16: 2, A.BF16X2: 4}
 _ALIGN = 1024
+_POOL_PARTS = 16           # slabs of the squeeze-excite sums: one per column strip of the depthwise kernel (include/ede.h)
 
 
 def set_precision(mode: str, encoder: Optional[str] = None) -> None:
@@ -165,6 +166,8 @@ class Graph:
         self.outputs: List[tuple] = []            # (op index, shape)
         self.flops = 0.0                          # algorithmic 2*MAC of the reference graph's convs
         self.exec_flops = 0.0                     # 2*MAC actually issued to the tensor cores / CUDA cores
+        self.conv_flops = 0.0                     # `flops` without the depthwise convs: the dense-conv roofline numerator
+        self.conv_exec_flops = 0.0                # `exec_flops` of the dense convs (tensor-core MMAs + tap gathers + stem)
         self.count_ref_flops = True
         self.tags: List[str] = []
 
@@ -292,7 +295,9 @@ class Graph:
                 seen_plain = True
             if self.count_ref_flops:
                 self.flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
+                self.conv_flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
             self.exec_flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
+            self.conv_exec_flops += 2.0 * x.n * oh * ow * co * cin * kh * kw
         full = torch.cat(fulls, 0)                               # host fp32 [cout_p][cin lanes][kh][kw]
         cout_p = len(out_lanes)
         if out is None:
@@ -355,6 +360,8 @@ class Graph:
         fl = 2.0 * x.n * oh * ow * co * cin * k * k
         self.flops += fl
         self.exec_flops += fl
+        self.conv_flops += fl
+        self.conv_exec_flops += fl
         return out
 
     def conv_bn_act_add(self, pair: View, conv, bn, act, out: Optional[View] = None, tag="conv") -> View:
@@ -372,10 +379,11 @@ class Graph:
         w[:, :ci] = wt.float() * sc.view(-1, 1, 1, 1)
         idx = torch.arange(co)
         w[idx, ci + idx, kh // 2, kw // 2] = 1.0
-        before = self.flops
+        before, before_c = self.flops, self.conv_flops
         y = self.conv(pair, [(w, None, sf, act != A.ACT_NONE)], 1, _pad4(conv), act, None, out, tag=tag)
         if self.count_ref_flops:                  # the reference does a cin-channel conv and an elementwise add
             self.flops = before + 2.0 * pair.n * y.h * y.w * co * ci * kh * kw
+            self.conv_flops = before_c + 2.0 * pair.n * y.h * y.w * co * ci * kh * kw
         return y
 
     def conv_bn_act(self, x: View, conv, bn=None, act=A.ACT_NONE, res=None, out=None, relu_in=False,
@@ -406,10 +414,11 @@ class Graph:
         if pool:
             # zeroed once at plan build; se_gate's FC kernel clears it again after reading (EdeSeFc.clear_pool), so a
             # forward needs no fill launch (Plan.run re-zeroes the pools if a forward fails half way)
-            pool_t = self._reserve(x.n * x.c_p * 4, zero=True)
+            pool_t = self._reserve(_POOL_PARTS * x.n * x.c_p * 4, zero=True)
         st = A.EdeDwConv(x=None, y=None, w=None, scale=None, shift=None, pool_sum=None, n=x.n, h=x.h, w_=x.w,
                          c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
-                         oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype)
+                         oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype,
+                         pool_parts=_POOL_PARTS if pool else 0)
         self._add(A.OP_DWCONV, st, [("x", x.buf), ("y", out.buf)], tag,
                   [("w", w), ("scale", sc), ("shift", sf), ("pool_sum", pool_t)])
         self.flops += 2.0 * x.n * oh * ow * c * k * k
@@ -433,7 +442,7 @@ class Graph:
         b1 = self._dev(_cpu(reduce_conv.bias).float())
         gate = self._reserve(x.n * x.c_p * 4, zero=True)
         st = A.EdeSeFc(pool_sum=None, w1=None, b1=None, w2=None, b2=None, gate=None, n=x.n, c=c, c_p=x.c_p, csq=csq,
-                       inv_hw=1.0 / (x.h * x.w), clear_pool=1, w2_transposed=1)
+                       inv_hw=1.0 / (x.h * x.w), clear_pool=1, w2_transposed=1, pool_parts=_POOL_PARTS)
         self._add(A.OP_SE_FC, st, [], tag + ".fc",
                   [("pool_sum", pool_t), ("w1", w1), ("b1", b1), ("w2", w2), ("b2", b2), ("gate", gate)])
         out = View(self.new_buf(x.n, x.h, x.w, x.c_p, x.dtype), 0, x.lanes)
@@ -466,6 +475,7 @@ class Graph:
             if activated and act != A.ACT_NONE:
                 act_end = len(out_lanes)
             self.flops += 2.0 * x.n * oh * ow * co * cin * k * k          # what the reference graph executes
+            self.conv_flops += 2.0 * x.n * oh * ow * co * cin * k * k
         cgrp = len(out_lanes)
         wz = torch.cat(rows, 0)                                            # [cgrp][cin][k][k]
         wz = wz.permute(2, 3, 0, 1).reshape(k * k * cgrp, cin, 1, 1)       # lanes [(ty*k+tx)*cgrp + c]
@@ -483,6 +493,7 @@ class Graph:
         self._add(A.OP_UPCONV, st, [("z", z.buf), ("y", out.buf), ("rows", rows)], tag + ".taps",
                   [("scale", scale), ("shift", shift)])
         self.exec_flops += 2.0 * x.n * oh * ow * cgrp * k * k * 4
+        self.conv_exec_flops += 2.0 * x.n * oh * ow * cgrp * k * k * 4
         return out
 
     def resize(self, x: View, size, out: Optional[View] = None, out_dtype=None, force=False, tag="resize") -> View:
@@ -575,6 +586,7 @@ class Plan:
         self.arena_bytes = arena_bytes
         self.flops = g.flops
         self.exec_flops = g.exec_flops
+        self.conv_flops, self.conv_exec_flops = g.conv_flops, g.conv_exec_flops
         self.tags = [t for (_, _, _, t) in g.ops]
         self.kinds = [k for (k, _, _, _) in g.ops]
         self.inputs, self.outputs = g.inputs, g.outputs
@@ -621,6 +633,9 @@ class Plan:
             self.ops[i].kind = kind
             setattr(self.ops[i].u, A.OP_FIELD[kind], st)
         self.structs = [st for (_, st, _, _) in g.ops]      # host copies (introspection / tests)
+        # (field, arena offset, bytes) of every activation buffer an op touches (debug tools: tools/replay_check.py)
+        self.op_bufs = [[(f, b.offset, b.nbytes) for f, b in refs] for (_, _, refs, _) in g.ops]
+        self.arena_base = base
         for st in g.stages:                                  # host tensors are not needed any more
             st.t = None
         self._lock = threading.Lock()

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 6
+#define EDE_ABI_VERSION 7
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
@@ -127,6 +127,10 @@ typedef struct EdeDwConv {
     const void* x; void* y; const float* w; const float* scale; const float* shift; float* pool_sum;
     int32_t n, h, w_, c_p, x_cs, x_co, oh, ow, y_cs, y_co;
     int32_t k, s, pt, pl, act, dtype;
+    int32_t pool_parts;     /* 0/1: pool_sum is fp32 [n][c_p], accumulated with atomics (order-dependent rounding).
+                               P > 1: pool_sum is fp32 [P][n][c_p]; when the kernel runs with <= P column strips each
+                               strip WRITES its own slab (no atomics: bit-reproducible forward), else it falls back
+                               to atomics on slab 0.  ede_se_fc sums the slabs in order. */
 } EdeDwConv;
 int ede_dwconv2d(const EdeDwConv* a, void* stream);
 
@@ -140,6 +144,7 @@ typedef struct EdeSeFc {
     int32_t clear_pool;     /* 1: write zeros back to pool_sum after reading it, so that the next forward's
                                ede_dwconv2d accumulates from zero without a separate ede_fill_zero launch */
     int32_t w2_transposed;  /* 1: w2 is fp32 [csq][c_p] (coalesced reads), 0: [c_p][csq]            */
+    int32_t pool_parts;     /* slabs of pool_sum (see EdeDwConv.pool_parts), summed in slab order; 0 = 1   */
 } EdeSeFc;
 int ede_se_fc(const EdeSeFc* a, void* stream);
 
