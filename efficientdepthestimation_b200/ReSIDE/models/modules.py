@@ -8,6 +8,7 @@ forward of every class is an operator emission into the B200 plan:
     applies the final ReLU (modules.py:36,39).
   * MFF / model: `torch.cat` (modules.py:265, net.py:30) is producers writing channel slices.
 """
+import contextlib
 import os
 
 from torch import nn
@@ -20,6 +21,10 @@ from ...engine import EdeModule, cat_views, emit
 _LOWRES_UPCONV = os.environ.get("EDE_LOWRES_UPCONV", "1") != "0"
 _LOWRES_MIN_CIN = int(os.environ.get("EDE_LOWRES_MIN_CIN", "192"))        # for moderate upsampling (4x in area)
 _ADD_AS_TAP_MAX_LANES = 64     # [x1 | bran2] lanes up to which conv1_2 + add run as one GEMM (fits one 64-channel chunk)
+# D.conv + that many up-projections at split-bf16 precision; -1 = by decoder width (measured, DESIGN.md section 5:
+# ENB4-HU, 224 channels, needs 3 to hold 1e-2 on every image of a batch of 32; ENB0-HU, 160 channels, holds it with 0)
+_ACCURATE_D = int(os.environ.get("EDE_ACCURATE_D", "-1"))
+_ACCURATE_D_MAX_C = 256
 _LOWRES_MIN_CIN_BIG = int(os.environ.get("EDE_LOWRES_MIN_CIN_BIG", "32"))  # for >= 8x in area: z is tiny
 
 
@@ -151,11 +156,20 @@ class D(EdeModule, nn.Module):
         self.out_channels = c
 
     def _emit(self, g, b1, b2, b3, b4, out=None):
-        x = g.conv_bn_act(b4, self.conv, self.bn, A.ACT_RELU, tag="D.conv")
-        x = self.up1._emit(g, x, [b3.h, b3.w], tag="D.up1")
-        x = self.up2._emit(g, x, [b2.h, b2.w], tag="D.up2")
-        x = self.up3._emit(g, x, [b1.h, b1.w], tag="D.up3")
-        return self.up4._emit(g, x, [b1.h * 2, b1.w * 2], out=out, tag="D.up4")
+        # Narrow decoders (EfficientNet: 160 / 224 channels after D.conv) run D.conv and the first `level`
+        # up-projections at the encoder's split-bf16 precision: those low-resolution stages are a few per cent of the
+        # FLOPs but the largest single source of bf16 error, which a random-init net amplifies.
+        # ResNet-50's D (1024 channels, 30 % of the FLOPs) stays plain bf16.
+        c = self.conv.out_channels
+        level = 0 if c > _ACCURATE_D_MAX_C else (_ACCURATE_D if _ACCURATE_D >= 0 else (3 if c > 192 else 1))
+        sizes = ([b3.h, b3.w], [b2.h, b2.w], [b1.h, b1.w], [b1.h * 2, b1.w * 2])
+        ups = (self.up1, self.up2, self.up3, self.up4)
+        with (g.encoder_scope() if level > 0 else contextlib.nullcontext()):
+            x = g.conv_bn_act(b4, self.conv, self.bn, A.ACT_RELU, tag="D.conv")
+        for i, (up, size) in enumerate(zip(ups, sizes)):
+            with (g.encoder_scope() if i < min(level, 3) else contextlib.nullcontext()):
+                x = up._emit(g, x, size, out=out if i == 3 else None, tag=f"D.up{i + 1}")
+        return x
 
 
 class MFF(EdeModule, nn.Module):

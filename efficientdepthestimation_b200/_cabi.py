@@ -130,7 +130,7 @@ EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_stem_
            "ede_resize_bilinear_ac", "ede_resize_planes_f32", "ede_maxpool3x3s2", "ede_eltwise", "ede_nchw_to_nhwc", "ede_nhwc_to_nchw",
            "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_depth_epilogue", "ede_resample_coeffs", "ede_preprocess_frames", "ede_plan_run",
            "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof",
-           "ede_prepack_conv_sizes", "ede_prepack_conv_to", "ede_prepack_conv", "ede_free"]
+           "ede_prepack_conv_sizes", "ede_prepack_conv_to", "ede_prepack_conv", "ede_free", "ede_dwconv2d_pool_parts"]
 
 _lib = None
 
@@ -154,6 +154,8 @@ def lib():
         f = getattr(L, name)
         f.argtypes = [POINTER(st), c_void_p]
         f.restype = c_int32
+    L.ede_dwconv2d_pool_parts.argtypes = [POINTER(EdeDwConv)]
+    L.ede_dwconv2d_pool_parts.restype = c_int32
     L.ede_stem_supported.argtypes = [c_int32, c_int32, c_int32, c_int32]
     L.ede_stem_supported.restype = c_int32
     L.ede_conv2d_umma_config.argtypes = [POINTER(EdeConv), POINTER(EdeUmmaCfg)]

@@ -239,15 +239,20 @@ static int pick_cols(int ow_units, int max_cols) {
 }
 
 template <typename T, int K, int S, int CH, int NC>
-static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
-    EncodeTiledFn enc = get_encode_fn();
-    if (!enc) return 1;
+static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st, int* strips_out) {
     constexpr int DEPTH = DwDepth<K>::value;
     constexpr int SUB = 64 / CH;
     DwParams p;
     memset(&p, 0, sizeof(p));
     p.a = a;
     p.cols = pick_cols(ceil_div(a.ow, SUB * NC), DwCols<K>::value);
+    if (strips_out) {                                     // host query: column strips (grid.x) of this shape
+        if (p.cols * SUB * NC * S + K - S > 256) return 1;
+        *strips_out = ceil_div(a.ow, p.cols * SUB * NC);
+        return 0;
+    }
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) return 1;
     const int esz = a.dtype == EDE_BF16 ? 2 : 4;
     const int box_w = p.cols * SUB * NC * S + K - S;
     if (box_w > 256) return 1;
@@ -304,7 +309,7 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st) {
 }
 
 template <typename T, int K, int S>
-static int dwconv_tma_launch_ks(const EdeDwConv& a, cudaStream_t st) {
+static int dwconv_tma_launch_ks(const EdeDwConv& a, cudaStream_t st, int* so) {
     // 32-lane chunks when they cut the idle lanes of the last chunk by a quarter or more (c_p = 32, 96, ...)
     // two output columns per thread except where the window would not fit the registers (5x5 stride 2) or the map
     // is so narrow that half of the column pairs would be padding
@@ -312,24 +317,25 @@ static int dwconv_tma_launch_ks(const EdeDwConv& a, cudaStream_t st) {
     static const char* nc_env = getenv("EDE_DW_NC");          // debug / tests: force one column per thread
     const bool one = NC == 1 || (nc_env && atoi(nc_env) == 1);
     const bool ch32 = 4 * round_up(a.c_p, 32) <= 3 * round_up(a.c_p, 64);
-    if (one) return ch32 ? dwconv_tma_launch_ch<T, K, S, 32, 1>(a, st) : dwconv_tma_launch_ch<T, K, S, 64, 1>(a, st);
+    if (one) return ch32 ? dwconv_tma_launch_ch<T, K, S, 32, 1>(a, st, so) : dwconv_tma_launch_ch<T, K, S, 64, 1>(a, st, so);
     // 3x3 stride 1: four columns per thread on the widest maps (the window is small enough for the registers)
     constexpr int NC4 = K == 3 ? 4 : NC;
     const bool four = K == 3 && S == 1 && a.ow >= 128 && !(nc_env && atoi(nc_env) == 2);   // measured: pays on 114x152 only
-    if (four) return ch32 ? dwconv_tma_launch_ch<T, K, S, 32, NC4>(a, st) : dwconv_tma_launch_ch<T, K, S, 64, NC4>(a, st);
-    return ch32 ? dwconv_tma_launch_ch<T, K, S, 32, NC>(a, st) : dwconv_tma_launch_ch<T, K, S, 64, NC>(a, st);
+    if (four) return ch32 ? dwconv_tma_launch_ch<T, K, S, 32, NC4>(a, st, so) : dwconv_tma_launch_ch<T, K, S, 64, NC4>(a, st, so);
+    return ch32 ? dwconv_tma_launch_ch<T, K, S, 32, NC>(a, st, so) : dwconv_tma_launch_ch<T, K, S, 64, NC>(a, st, so);
 }
 
-// returns 0 when the TMA kernel was launched, 1 when this (k, s) / device has no TMA path (caller falls back)
-int dwconv_tma_launch(const EdeDwConv& a, cudaStream_t st) {
-    if ((reinterpret_cast<uintptr_t>(a.x) & 15) != 0) return 1;
+// returns 0 when the TMA kernel was launched, 1 when this (k, s) / device has no TMA path (caller falls back);
+// with `strips_out` nothing is launched: it receives the number of column strips (grid.x) the kernel would use
+int dwconv_tma_launch(const EdeDwConv& a, cudaStream_t st, int* strips_out) {
+    if (!strips_out && (reinterpret_cast<uintptr_t>(a.x) & 15) != 0) return 1;
     const int ks = a.k * 10 + a.s;
     int rc = 1;
     EDE_DISPATCH_DTYPE(a.dtype, T, {
-        if (ks == 31) rc = dwconv_tma_launch_ks<T, 3, 1>(a, st);
-        else if (ks == 32) rc = dwconv_tma_launch_ks<T, 3, 2>(a, st);
-        else if (ks == 51) rc = dwconv_tma_launch_ks<T, 5, 1>(a, st);
-        else if (ks == 52) rc = dwconv_tma_launch_ks<T, 5, 2>(a, st);
+        if (ks == 31) rc = dwconv_tma_launch_ks<T, 3, 1>(a, st, strips_out);
+        else if (ks == 32) rc = dwconv_tma_launch_ks<T, 3, 2>(a, st, strips_out);
+        else if (ks == 51) rc = dwconv_tma_launch_ks<T, 5, 1>(a, st, strips_out);
+        else if (ks == 52) rc = dwconv_tma_launch_ks<T, 5, 2>(a, st, strips_out);
     });
     return rc;
 }

@@ -27,7 +27,6 @@ _PRECISION = os.environ.get("EDE_PRECISION", "bf16")
 _ENCODER_PRECISION = os.environ.get("EDE_ENCODER_PRECISION", "bf16x2")
 _ELT = {A.F32: 4, A.BF16: 2, A.BF16X2: 4}
 _ALIGN = 1024
-_POOL_PARTS = 16           # slabs of the squeeze-excite sums: one per column strip of the depthwise kernel (include/ede.h)
 
 
 def set_precision(mode: str, encoder: Optional[str] = None) -> None:
@@ -102,7 +101,7 @@ class View:
 class Stage:
     """A region of the plan's weight blob.  `t` = CPU tensor uploaded into it (None: a region that a prepack kernel
     or the forward itself writes); `temp` regions live in the staging blob that is freed after prepacking."""
-    __slots__ = ("t", "nbytes", "offset", "temp", "zero")
+    __slots__ = ("t", "nbytes", "offset", "temp", "zero", "parts")
 
     def __init__(self, t, nbytes, temp=False, zero=False):
         self.t, self.nbytes, self.offset, self.temp, self.zero = t, int(nbytes), -1, temp, zero
@@ -410,15 +409,17 @@ class Graph:
         w[:, idx] = wt[:, src]
         sc, sf = P.fold_bn(c, _bn_dict(bn), _cpu(conv.bias), "cpu")
         w, sc, sf = self._dev(w), self._dev(P.place_lanes(sc, x.lanes)), self._dev(P.place_lanes(sf, x.lanes))
-        pool_t = None
-        if pool:
-            # zeroed once at plan build; se_gate's FC kernel clears it again after reading (EdeSeFc.clear_pool), so a
-            # forward needs no fill launch (Plan.run re-zeroes the pools if a forward fails half way)
-            pool_t = self._reserve(_POOL_PARTS * x.n * x.c_p * 4, zero=True)
         st = A.EdeDwConv(x=None, y=None, w=None, scale=None, shift=None, pool_sum=None, n=x.n, h=x.h, w_=x.w,
                          c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
-                         oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype,
-                         pool_parts=_POOL_PARTS if pool else 0)
+                         oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype)
+        pool_t = None
+        if pool:
+            # one slab of squeeze sums per column strip of the depthwise kernel: plain stores, added in slab order by
+            # the SE FC kernel -> a bit-reproducible forward.  Zeroed once at plan build (Plan.run re-zeroes the state
+            # if a forward fails half way; EdeSeFc.clear_pool keeps the atomic fallback correct).
+            st.pool_parts = 1 if self.dry_no_lib else int(A.lib().ede_dwconv2d_pool_parts(C.byref(st)))
+            pool_t = self._reserve(st.pool_parts * x.n * x.c_p * 4, zero=True)
+            pool_t.parts = st.pool_parts
         self._add(A.OP_DWCONV, st, [("x", x.buf), ("y", out.buf)], tag,
                   [("w", w), ("scale", sc), ("shift", sf), ("pool_sum", pool_t)])
         self.flops += 2.0 * x.n * oh * ow * c * k * k
@@ -442,7 +443,7 @@ class Graph:
         b1 = self._dev(_cpu(reduce_conv.bias).float())
         gate = self._reserve(x.n * x.c_p * 4, zero=True)
         st = A.EdeSeFc(pool_sum=None, w1=None, b1=None, w2=None, b2=None, gate=None, n=x.n, c=c, c_p=x.c_p, csq=csq,
-                       inv_hw=1.0 / (x.h * x.w), clear_pool=1, w2_transposed=1, pool_parts=_POOL_PARTS)
+                       inv_hw=1.0 / (x.h * x.w), clear_pool=1, w2_transposed=1, pool_parts=pool_t.parts)
         self._add(A.OP_SE_FC, st, [], tag + ".fc",
                   [("pool_sum", pool_t), ("w1", w1), ("b1", b1), ("w2", w2), ("b2", b2), ("gate", gate)])
         out = View(self.new_buf(x.n, x.h, x.w, x.c_p, x.dtype), 0, x.lanes)

@@ -133,6 +133,9 @@ typedef struct EdeDwConv {
                                to atomics on slab 0.  ede_se_fc sums the slabs in order. */
 } EdeDwConv;
 int ede_dwconv2d(const EdeDwConv* a, void* stream);
+/* HOST function, no GPU: the pool_parts value with which ede_dwconv2d writes (instead of atomically adds) the squeeze
+ * sums of this shape -- its number of column strips; 1 when the shape takes the atomic path anyway. */
+int ede_dwconv2d_pool_parts(const EdeDwConv* a);
 
 /* Squeeze-excite gate: gate[n,c] = sigmoid(W2 . swish(W1 . (pool_sum[n,:]/hw) + b1) + b2).
  * replaces: _se_reduce -> swish -> _se_expand -> sigmoid (App. A.3).  w1: fp32 [csq][c_p],
