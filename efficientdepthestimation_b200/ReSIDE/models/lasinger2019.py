@@ -92,6 +92,37 @@ class ResidualBlock(EdeModule, nn.Module):
         return g.conv_bn_act(out, self.conv2, self.bn2, A.ACT_NONE, res=skip, tag=tag + ".conv2")
 
 
+class BottleneckBlock(EdeModule, nn.Module):
+    """The bottleneck version of the residual block (lasinger2019.py:166-211 of the reference): pre-activation ReLU ->
+    1x1 (to out/4) + BN + ReLU -> 3x3 + BN + ReLU -> 1x1 + BN, plus the RAW input (through a 1x1 + BN projection when
+    the channel counts differ); no ReLU on the sum."""
+
+    def __init__(self, in_channels, out_channels=None):
+        super().__init__()
+        out_channels = in_channels if out_channels is None else out_channels
+        mid = max(1, out_channels // 4)           # the ratio of torchvision's Bottleneck (lasinger2019.py:180-182)
+        self.conv1 = nn.Conv2d(in_channels, mid, kernel_size=1, bias=False)
+        self.bn1 = nn.BatchNorm2d(mid)
+        self.conv2 = nn.Conv2d(mid, mid, kernel_size=3, padding=1, bias=False)
+        self.bn2 = nn.BatchNorm2d(mid)
+        self.conv3 = nn.Conv2d(mid, out_channels, kernel_size=1, bias=False)
+        self.bn3 = nn.BatchNorm2d(out_channels)
+        if in_channels != out_channels:
+            self.down_sample = nn.Sequential(nn.Conv2d(in_channels, out_channels, kernel_size=1, bias=False),
+                                             nn.BatchNorm2d(out_channels))
+        else:
+            self.down_sample = None
+
+    def _emit(self, g, x, tag="bottleneck_block"):
+        out = g.conv_bn_act(x, self.conv1, self.bn1, A.ACT_RELU, relu_in=True, tag=tag + ".conv1")
+        out = g.conv_bn_act(out, self.conv2, self.bn2, A.ACT_RELU, tag=tag + ".conv2")
+        skip = x
+        if self.down_sample is not None:
+            ds = list(self.down_sample.children())
+            skip = g.conv_bn_act(x, ds[0], ds[1], A.ACT_NONE, tag=tag + ".down_sample")
+        return g.conv_bn_act(out, self.conv3, self.bn3, A.ACT_NONE, res=skip, tag=tag + ".conv3")
+
+
 class DecoderBlock(EdeModule, nn.Module):
     """Transforms the previous decoder block's output and the corresponding encoder block's output."""
 

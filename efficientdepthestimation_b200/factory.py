@@ -3,7 +3,7 @@ reference's own constructor calls (ReSIDE/train.py:20-38,86-91) minus the downlo
 from typing import Tuple
 
 from .ReSIDE.models import modules, net, resnet
-from .ReSIDE.models.lasinger2019 import Decoder, Encoder, MidasNet
+from .ReSIDE.models.lasinger2019 import BottleneckBlock, Decoder, Encoder, MidasNet, ResidualBlock
 
 ARCHS = ("rn50-hu", "enb0-hu", "enb4-hu", "rn50-lr", "enb0-lr", "enb4-lr")
 _ENC = {"rn50": "resnet50", "enb0": "efficientnet-b0", "enb4": "efficientnet-b4"}
@@ -13,7 +13,7 @@ def input_hw(arch: str) -> Tuple[int, int]:
     return (228, 304) if arch.endswith("-hu") else (384, 384)
 
 
-def build_model(arch: str, lr_output_wh=None):
+def build_model(arch: str, lr_output_wh=None, lr_block: str = "residual"):
     """arch = '<rn50|enb0|enb4>-<hu|lr>'; random-init weights (load a state_dict afterwards)."""
     if arch not in ARCHS:
         raise RuntimeError(f"Unsupported model '{arch}' (expected one of {', '.join(ARCHS)})")
@@ -25,5 +25,6 @@ def build_model(arch: str, lr_output_wh=None):
         return net.model(e, e.num_features, e.block_out_channels)
     e = Encoder(_ENC[enc], pretrained=False)
     h, w = input_hw(arch)
-    return MidasNet(e, Decoder(e.block_out_channels, num_features="auto"),
+    block = {"residual": ResidualBlock, "bottleneck": BottleneckBlock}[lr_block]      # Decoder(block_type=...), :252-262
+    return MidasNet(e, Decoder(e.block_out_channels, num_features="auto", block_type=block),
                     output_size=lr_output_wh or (w // 2, h // 2), input_size=(w, h))

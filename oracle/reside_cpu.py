@@ -208,16 +208,28 @@ def lr_residual_block(c: Ctx, x, p: str, has_ds: bool):
     return out + skip
 
 
+def lr_bottleneck_block(c: Ctx, x, p: str, has_ds: bool):
+    """BottleneckBlock.forward, ReSIDE/models/lasinger2019.py:197-211."""
+    out = F.relu(x)
+    out = F.relu(_bn(c, _conv(c, out, p + "conv1"), p + "bn1"))
+    out = F.relu(_bn(c, _conv(c, out, p + "conv2", 1, 1), p + "bn2"))
+    out = _bn(c, _conv(c, out, p + "conv3"), p + "bn3")
+    skip = _bn(c, _conv(c, x, p + "down_sample.0"), p + "down_sample.1") if has_ds else x
+    return out + skip
+
+
 def lr_decoder(c: Ctx, enc: Sequence[torch.Tensor], output_size, num_features: int,
                non_negative=False, p="decoder."):
     """Decoder.forward, ReSIDE/models/lasinger2019.py:279-295 + DecoderBlock :238-246."""
     sizes = [tuple(e.shape[-2:]) for e in reversed(enc[:-1])]
     sizes.append((sizes[-1][0] * 2, sizes[-1][1] * 2))
     out = None
+    # Decoder(block_type=...) (lasinger2019.py:252-262): the checkpoint tells which block type was trained
+    block = lr_bottleneck_block if f"{p}blocks.0.res_block1.conv3.weight" in c.sd else lr_residual_block
     for i, (e, size) in enumerate(zip(reversed(enc), sizes)):
         bp = f"{p}blocks.{i}."
-        r = lr_residual_block(c, e, bp + "res_block1.", e.shape[1] != num_features)
-        out = r if out is None else lr_residual_block(c, out + r, bp + "res_block2.", False)
+        r = block(c, e, bp + "res_block1.", e.shape[1] != num_features)
+        out = r if out is None else block(c, out + r, bp + "res_block2.", False)
         out = _interp(out, size)
     out = F.relu(_bn(c, _conv(c, out, p + "conv1", 1, 1), p + "bn1"))
     out = _interp(out, output_size)

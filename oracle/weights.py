@@ -74,7 +74,7 @@ def _up(L: _Layout, p: str, cin: int, cout: int):
     L.conv(p + "conv2", cout, cin, 5); L.bn(p + "bn2", cout)
 
 
-def layout(arch: str) -> List[Tuple[str, tuple, str]]:
+def layout(arch: str, lr_block: str = "residual") -> List[Tuple[str, tuple, str]]:
     enc, dec = arch.split("-")
     L = _Layout()
     if dec == "hu":
@@ -108,8 +108,14 @@ def layout(arch: str) -> List[Tuple[str, tuple, str]]:
         for i, cin in enumerate(reversed(ch)):
             for rb, c_in in (("res_block1", cin), ("res_block2", f)):
                 p = f"decoder.blocks.{i}.{rb}."
-                L.conv(p + "conv1", f, c_in, 3); L.bn(p + "bn1", f)
-                L.conv(p + "conv2", f, f, 3); L.bn(p + "bn2", f)
+                if lr_block == "bottleneck":                    # BottleneckBlock, lasinger2019.py:169-195
+                    mid = max(1, f // 4)
+                    L.conv(p + "conv1", mid, c_in, 1); L.bn(p + "bn1", mid)
+                    L.conv(p + "conv2", mid, mid, 3); L.bn(p + "bn2", mid)
+                    L.conv(p + "conv3", f, mid, 1); L.bn(p + "bn3", f)
+                else:
+                    L.conv(p + "conv1", f, c_in, 3); L.bn(p + "bn1", f)
+                    L.conv(p + "conv2", f, f, 3); L.bn(p + "bn2", f)
                 if c_in != f:
                     L.conv(p + "down_sample.0", f, c_in, 1); L.bn(p + "down_sample.1", f)
         L.conv("decoder.conv1", 128, f, 3); L.bn("decoder.bn1", 128)
@@ -136,13 +142,13 @@ def forward(sd, x, arch: str, lr_output_hw=None, calibrate=False, taps=None):
 
 
 def make_state_dict(arch: str, seed: int = 1234, condition: bool = True,
-                    calib_hw=None, calib_batch: int = 2) -> Dict[str, torch.Tensor]:
+                    calib_hw=None, calib_batch: int = 2, lr_block: str = "residual") -> Dict[str, torch.Tensor]:
     """Random weights for `arch`; deterministic for (arch, seed) on CPU.
 
     condition=False gives the degenerate default-like init (identity BN statistics)."""
     g = torch.Generator().manual_seed(seed)
     sd: Dict[str, torch.Tensor] = {}
-    for key, shape, kind in layout(arch):
+    for key, shape, kind in layout(arch, lr_block):
         if kind == "conv":
             fan_in = shape[1] * shape[2] * shape[3]
             sd[key] = torch.randn(shape, generator=g) * math.sqrt(2.0 / fan_in)

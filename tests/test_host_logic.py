@@ -206,3 +206,45 @@ def test_plan_build_packs_on_the_host_and_reserves_device_regions(lib):
     assert sum(1 for st in g.stages if st.zero) == 2 * 16            # pool sums + gates of the 16 MBConv blocks
     plan = g.finalize()
     assert plan.weight_bytes > 0 and plan.weights is None and all(st.t is None for st in g.stages)
+
+
+@pytest.mark.parametrize("name", ["efficientnet-b1", "efficientnet-b3", "efficientnet-b5", "efficientnet-b6",
+                                  "efficientnet-b7"])
+def test_every_efficientnet_split_compiles_to_a_plan(lib, name):
+    """The B1..B7 block splits of ReSIDE/models/modules.py:168-181 (B0 / B4 are covered by the parity tests): the
+    encoder builds with the reference's channel counts and the whole Hu model compiles onto the tcgen05 path."""
+    from oracle import effnet_spec as spec
+    from efficientdepthestimation_b200.ReSIDE.models import modules, net
+    enc = modules.E_efficientnet(name, pretrained=False)
+    _, blocks, _ = spec.block_specs(name)
+    idx = spec.split_indices(name)
+    assert enc.block_out_channels == [blocks[i - 1].cout for i in idx[1:]]
+    assert [len(b) for b in enc.blocks] == [idx[1] + 2] + [b - a for a, b in zip(idx[1:-1], idx[2:])]
+    m = net.model(enc, enc.num_features, enc.block_out_channels).eval()
+    plan, _, _ = compile_module(m, (torch.empty(1, 3, 228, 304, device="meta"),), torch.device("cpu"), "bf16")
+    assert plan.outputs[0][1] == (1, 1, 114, 152)
+    cfgs = plan.conv_configs()
+    assert all(cfg.eligible for _, _, cfg in cfgs), [t for t, _, c in cfgs if not c.eligible]
+    assert all(cfg.smem_bytes <= 227 * 1024 and cfg.tmem_cols <= 512 for _, _, cfg in cfgs)
+
+
+def test_unknown_efficientnet_name_raises_like_the_reference():
+    from efficientdepthestimation_b200.ReSIDE.models import modules
+    with pytest.raises(RuntimeError, match="Unsupported encoder network"):
+        modules.E_efficientnet("efficientnet-b9", pretrained=False)
+    with pytest.raises(RuntimeError, match="Unsupported encoder network"):
+        modules.E_efficientnet("resnet50", pretrained=False)
+
+
+def test_bottleneck_decoder_layout_and_plan(lib):
+    """Decoder(block_type=BottleneckBlock): state_dict keys equal the layout pinned against the reference
+    (tests/golden/make_golden_bottleneck.py), strict load works, the plan compiles."""
+    from oracle import weights as W
+    m = factory.build_model("enb0-lr", lr_block="bottleneck")
+    sd = W.make_state_dict("enb0-lr", seed=4321, lr_block="bottleneck", condition=False)
+    assert list(m.state_dict().keys()) == list(sd.keys())
+    assert all(tuple(v.shape) == tuple(sd[k].shape) for k, v in m.state_dict().items())
+    m.load_state_dict(sd, strict=True)
+    plan, _, _ = compile_module(m.eval(), (torch.empty(1, 3, 384, 384, device="meta"),), torch.device("cpu"), "bf16")
+    assert plan.outputs[0][1] == (1, 1, 192, 192)
+    assert sum(1 for t in plan.tags if t.endswith(".conv3")) >= 7        # 4 res_block1 + 3 res_block2 bottlenecks

@@ -86,3 +86,24 @@ def test_forward_errors(cuda, lib):
         m.train()(torch.zeros(1, 3, 64, 64, device="cuda"))          # training mode: no fallback
     with pytest.raises(RuntimeError):
         m.eval()(torch.zeros(1, 3, 64, 64))                          # CPU tensor: no fallback
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("arch", ["enb0-lr", "rn50-lr"])
+def test_bottleneck_decoder_matches_oracle_and_golden(cuda, lib, arch, precision):
+    """Decoder(block_type=BottleneckBlock), lasinger2019.py:166-211,252-262; golden from the real reference modules."""
+    gold = torch.load(os.path.join(GOLDEN, f"{arch}-bottleneck.pt"))
+    sd = W.make_state_dict(arch, seed=gold["seed"], lr_block="bottleneck")
+    x = W.make_input(arch, 1, seed=gold["input_seed"])
+    m = factory.build_model(arch, lr_block="bottleneck")
+    m.load_state_dict(sd, strict=True)
+    m = m.cuda().eval()
+    engine.set_precision(precision)
+    try:
+        with torch.no_grad():
+            y = m(x.cuda()).cpu()
+    finally:
+        engine.set_precision("bf16")
+    err = rc.relative_l1(y, gold["output"])
+    print(f"\n{arch} bottleneck decoder {precision}: rel_l1 vs reference golden {err:.3e}")
+    assert err <= TOL[precision], (arch, precision, err)

@@ -77,3 +77,15 @@ def test_effnet_spec_tables():
     assert spec.static_same_pad(3, 1, 224) == (1, 1) and spec.static_same_pad(5, 1, 224) == (2, 2)
     with pytest.raises(RuntimeError):
         spec.split_indices("efficientnet-b9")
+
+
+def test_oracle_bottleneck_decoder_matches_reference_output():
+    """Decoder(block_type=BottleneckBlock) (lasinger2019.py:166-211): fixture from the real reference modules
+    (tests/golden/make_golden_bottleneck.py)."""
+    arch = "enb0-lr"
+    gold = torch.load(os.path.join(GOLDEN, f"{arch}-bottleneck.pt"))
+    sd = W.make_state_dict(arch, seed=gold["seed"], lr_block="bottleneck")
+    assert len(sd) == gold["n_entries"] and "decoder.blocks.0.res_block1.conv3.weight" in sd
+    with torch.no_grad():
+        y = W.forward(sd, W.make_input(arch, 1, seed=gold["input_seed"]), arch)
+    assert torch.allclose(y, gold["output"], rtol=1e-5, atol=1e-5)
