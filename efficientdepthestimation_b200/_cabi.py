@@ -107,6 +107,17 @@ class EdePackedConv(Structure):
         "w_umma_cout_p", "w_umma_cin_p", "w_pack_g", "w_passes") + [("device_bytes", c_int64)]
 
 
+class EdeMeshFromDepth(Structure):
+    _fields_ = [("depth", c_void_p), ("vertices", c_void_p), ("uv", c_void_p), ("indices", c_void_p)] + _ints(
+        "h", "w", "depth_stride", "density") + [("displacement", c_float)]
+
+
+class EdeRender(Structure):
+    _fields_ = [("vertices", c_void_p), ("uv", c_void_p), ("indices", c_void_p), ("mvp", c_void_p),
+                ("texture", c_void_p), ("frames", c_void_p), ("workspace", c_void_p)] + _ints(
+        "n_vertices", "n_triangles", "n_frames", "tex_h", "tex_w", "height", "width", "flip_y")
+
+
 class _Zero(Structure):
     _fields_ = [("p", c_void_p), ("bytes", c_int64)]
 
@@ -130,7 +141,8 @@ EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_stem_
            "ede_resize_bilinear_ac", "ede_resize_planes_f32", "ede_maxpool3x3s2", "ede_eltwise", "ede_nchw_to_nhwc", "ede_nhwc_to_nchw",
            "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_depth_epilogue", "ede_resample_coeffs", "ede_preprocess_frames", "ede_plan_run",
            "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof",
-           "ede_prepack_conv_sizes", "ede_prepack_conv_to", "ede_prepack_conv", "ede_free", "ede_dwconv2d_pool_parts"]
+           "ede_prepack_conv_sizes", "ede_prepack_conv_to", "ede_prepack_conv", "ede_free", "ede_dwconv2d_pool_parts",
+           "ede_mesh_from_depth", "ede_render_workspace_bytes", "ede_render_mesh"]
 
 _lib = None
 
@@ -154,6 +166,12 @@ def lib():
         f = getattr(L, name)
         f.argtypes = [POINTER(st), c_void_p]
         f.restype = c_int32
+    L.ede_mesh_from_depth.argtypes = [POINTER(EdeMeshFromDepth), c_void_p]
+    L.ede_mesh_from_depth.restype = c_int32
+    L.ede_render_workspace_bytes.argtypes = [POINTER(EdeRender)]
+    L.ede_render_workspace_bytes.restype = c_int64
+    L.ede_render_mesh.argtypes = [POINTER(EdeRender), c_void_p]
+    L.ede_render_mesh.restype = c_int32
     L.ede_dwconv2d_pool_parts.argtypes = [POINTER(EdeDwConv)]
     L.ede_dwconv2d_pool_parts.restype = c_int32
     L.ede_stem_supported.argtypes = [c_int32, c_int32, c_int32, c_int32]

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 7
+#define EDE_ABI_VERSION 8
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
@@ -280,6 +280,33 @@ typedef struct EdePreprocess {
 } EdePreprocess;
 int ede_resample_coeffs(int32_t in_size, int32_t out_size, int32_t first, int32_t count, int32_t* bounds, int32_t* kk);
 int ede_preprocess_frames(const EdePreprocess* a, void* stream);
+
+/* Depth-mesh rendering as a CUDA rasteriser (no graphics API).
+ * replaces: Mesh.from_texture (DepthRenderer/DepthRenderer/render.py:465-546, + the displacement of
+ *   Benchmark/benchmark.py:949), the vertex / fragment shaders (DepthRenderer/DepthRenderer/shaders/shader.vert:1-14,
+ *   shader.frag:1-8) and the fixed-function pipeline they run in (render.py:357-360 GL_LINEAR + GL_CLAMP, :631-634 cull
+ *   back faces + depth test + clear to opaque black, :787 glReadPixels RGBA8), driven per frame by
+ *   MeshRenderer.draw (render.py:800-823) from Benchmark/benchmark.py:845-1039 (create_rendered_images).
+ * ede_mesh_from_depth: depth uint8 [h][w] (element stride depth_stride: 1, or the channel count when the map is HxWxC
+ *   and channel 0 is used) -> vertices fp32 [(2^d+1)^2][3], uv fp32 [..][2], indices uint32 [2 * 4^d][3].
+ * ede_render_mesh: n_frames camera poses (mvp fp32 [n_frames][16], ROW-major as render.py:812 uploads them with
+ *   transpose = GL_TRUE) of ONE mesh -> frames uint8 [n_frames][height][width][4]; row 0 = bottom of the window as
+ *   glReadPixels returns it, or the top when flip_y = 1.  texture: uint8 [tex_h][tex_w][4], row 0 = v 0.
+ *   workspace: DEVICE scratch of ede_render_workspace_bytes() bytes (HOST function).  Rasterisation rules (sub-pixel
+ *   snapping, fill rule, depth format, texel rounding): oracle/render_cpu.py, matched bit for bit. */
+typedef struct EdeMeshFromDepth {
+    const uint8_t* depth; float* vertices; float* uv; uint32_t* indices;
+    int32_t h, w, depth_stride, density;
+    float displacement;
+} EdeMeshFromDepth;
+int ede_mesh_from_depth(const EdeMeshFromDepth* a, void* stream);
+typedef struct EdeRender {
+    const float* vertices; const float* uv; const uint32_t* indices; const float* mvp; const uint8_t* texture;
+    uint8_t* frames; void* workspace;
+    int32_t n_vertices, n_triangles, n_frames, tex_h, tex_w, height, width, flip_y;
+} EdeRender;
+int64_t ede_render_workspace_bytes(const EdeRender* a);
+int ede_render_mesh(const EdeRender* a, void* stream);
 
 /* Run a pre-built operator list ("forward plan") back to back on one stream. */
 enum { EDE_OP_CONV = 1, EDE_OP_DWCONV = 2, EDE_OP_SE_FC = 3, EDE_OP_SE_SCALE = 4, EDE_OP_RESIZE = 5,

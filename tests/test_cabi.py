@@ -24,7 +24,7 @@ def test_header_symbols_are_exported(lib):
 
 
 def test_version_and_error_plumbing(lib):
-    assert lib.ede_version() == 7
+    assert lib.ede_version() == 8
     assert lib.ede_fill_zero(None, -1, None) == -1            # EDE_E_ARG, no GPU touched
     assert b"ede_fill_zero" in lib.ede_last_error()
     assert lib.ede_plan_run(None, 0, None) == 0
@@ -36,10 +36,10 @@ def test_struct_sizes_match_header():
     src = r'''
     #include <stdio.h>
     #include "ede.h"
-    int main(){ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(EdeConv), sizeof(EdeUmmaCfg),
+    int main(){ printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\n", sizeof(EdeConv), sizeof(EdeUmmaCfg),
       sizeof(EdeDwConv), sizeof(EdeSeFc), sizeof(EdeSeScale), sizeof(EdeResize), sizeof(EdeMaxPool),
       sizeof(EdeEltwise), sizeof(EdeLayout), sizeof(EdeOp), sizeof(EdeUpConv), sizeof(EdePrepackConv),
-      sizeof(EdePackedConv)); return 0; }'''
+      sizeof(EdePackedConv), sizeof(EdeMeshFromDepth), sizeof(EdeRender)); return 0; }'''
     import tempfile
     with tempfile.TemporaryDirectory() as d:
         c = os.path.join(d, "s.c")
@@ -49,7 +49,7 @@ def test_struct_sizes_match_header():
         sizes = [int(v) for v in subprocess.check_output([exe]).split()]
     mine = [ctypes.sizeof(t) for t in (A.EdeConv, A.EdeUmmaCfg, A.EdeDwConv, A.EdeSeFc, A.EdeSeScale, A.EdeResize,
                                        A.EdeMaxPool, A.EdeEltwise, A.EdeLayout, A.EdeOp, A.EdeUpConv, A.EdePrepackConv,
-                                       A.EdePackedConv)]
+                                       A.EdePackedConv, A.EdeMeshFromDepth, A.EdeRender)]
     assert mine == sizes
 
 

@@ -145,3 +145,24 @@ def test_epilogue_edge_cases_and_errors(cuda, lib):
         L.depth_epilogue(pred, size=(4, 4), want_edges=True)                        # edges need a label
     with pytest.raises(RuntimeError):
         L.depth_epilogue(pred, size=(4, 4), label=torch.zeros(1, 1, 3, 3, device=cuda))
+
+
+@pytest.mark.parametrize("n,size", [(4, (480, 640)), (32, (228, 304)), (3, (231, 299))])
+def test_depth_mm_bit_exact_against_the_reference_lines_on_the_gpu(cuda, lib, n, size):
+    """ReSIDE/test_nyu.py:84-88 runs `F.interpolate(outputs, size, 'bilinear', align_corners=True)` ON THE GPU, then caps
+    and converts on the host.  Integer outputs are held to bit-exactness: the fused epilogue's resized map must equal
+    ATen's CUDA upsample_bilinear2d bit for bit (same expression order: src = scale * dst in fp32, lambdas in fp32,
+    `h0 * (w0 * a + w1 * b) + h1 * (w0 * c + w1 * d)` with nvcc's FMA contraction), so the uint16 millimetre maps are
+    equal.  torch on the GPU is the TEST ORACLE here; the product path never calls it."""
+    import torch.nn.functional as F
+    pred = (0.3 + 10.5 * torch.rand(n, 1, 114, 152, generator=torch.Generator().manual_seed(n))).to(cuda)
+    r = L.depth_epilogue(pred, size=size, want_resized=True, want_depth_mm=True)
+    outputs = F.interpolate(pred, size=size, mode="bilinear", align_corners=True)          # test_nyu.py:85
+    torch.cuda.synchronize()
+    assert torch.equal(r["resized"], outputs), float((r["resized"] - outputs).abs().max())
+    out = outputs.squeeze().cpu().numpy()                                                    # :86
+    out[out > 10.0] = 0.0                                                                    # :87  cap at 10 m
+    out = (out * 1000.0).astype(np.uint16)                                                   # :88
+    assert np.array_equal(r["depth_mm"].cpu().numpy(), out)
+    only = L.depth_epilogue(pred, size=size, want_depth_mm=True)["depth_mm"]                 # the label-free kernel
+    assert np.array_equal(only.cpu().numpy(), out)
