@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libede_sm100.so")
-SOURCES = ["api.cu", "conv_direct.cu", "conv_umma.cu", "bandwidth.cu", "dwconv.cu", "upconv.cu", "stem.cu", "sobel.cu", "preprocess.cu", "prepack.cu", "render.cu"]
+SOURCES = ["api.cu", "conv_direct.cu", "conv_umma.cu", "bandwidth.cu", "dwconv.cu", "dwconv_tile.cu", "upconv.cu", "stem.cu", "sobel.cu", "preprocess.cu", "prepack.cu", "render.cu"]
 
 
 def _stale() -> bool:

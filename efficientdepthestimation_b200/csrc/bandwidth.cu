@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(256) dwconv_kernel(const EdeDwConv a) {
 
 
 int dwconv_tma_launch(const EdeDwConv& a, cudaStream_t st, int* strips_out);      // dwconv.cu
+int dwconv_tile_launch(const EdeDwConv& a, cudaStream_t st, int* bands_out);      // dwconv_tile.cu
 
 // ------------------------------------------------------------------ squeeze-excite FCs
 __global__ void __launch_bounds__(1024) se_fc_kernel(const EdeSeFc a) {
@@ -301,6 +302,10 @@ int ede_dwconv2d(const EdeDwConv* a, void* stream) {
     EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_dwconv2d: channel counts must be multiples of 8");
     EDE_REQUIRE(a->n > 0 && a->oh > 0 && a->ow > 0 && a->k > 0 && a->s > 0, "ede_dwconv2d: bad shape");
     static const bool generic_only = getenv("EDE_DW_GENERIC") != nullptr;   // debug: force the per-output kernel
+    if (!generic_only && dwconv_tile_launch(*a, (cudaStream_t)stream, nullptr) == 0) {   // small / medium maps: one tile per block
+        EDE_LAUNCH_CHECK("dwconv_tile_kernel");
+        return EDE_OK;
+    }
     if (!generic_only && dwconv_tma_launch(*a, (cudaStream_t)stream, nullptr) == 0) {   // k in {3,5}, s in {1,2}: TMA-staged
         EDE_LAUNCH_CHECK("dwconv_tma_kernel");
         return EDE_OK;
@@ -319,7 +324,9 @@ int ede_dwconv2d(const EdeDwConv* a, void* stream) {
 int ede_dwconv2d_pool_parts(const EdeDwConv* a) {
     if (a == nullptr || a->ow <= 0 || a->c_p <= 0) return 1;
     int strips = 1;
-    if (getenv("EDE_DW_GENERIC") != nullptr || dwconv_tma_launch(*a, nullptr, &strips) != 0) return 1;
+    if (getenv("EDE_DW_GENERIC") != nullptr) return 1;
+    if (dwconv_tile_launch(*a, nullptr, &strips) == 0) return strips < 1 ? 1 : strips;
+    if (dwconv_tma_launch(*a, nullptr, &strips) != 0) return 1;
     return strips < 1 ? 1 : strips;
 }
 
