@@ -262,7 +262,7 @@ def roofline_of(plan, arch, n, dev, clocks, step_ms):
     times = per_op_times(plan, dev)
     capped = bool(clocks and "sw_power_cap" in (clocks.get("reasons") or []))
     peak = peaks["tensor"] if capped else peaks["tensor_burst"]
-    conv_kinds = (A.OP_CONV, A.OP_UPCONV, A.OP_STEM)
+    conv_kinds = (A.OP_CONV, A.OP_UPCONV, A.OP_STEM, A.OP_TAPSUM)
     conv_ms = sum(t for t, k in zip(times, plan.kinds) if k in conv_kinds)
     umma_ms = sum(t for t, k in zip(times, plan.kinds) if k == A.OP_CONV)
     achieved = plan.conv_flops / conv_ms / 1e9 if conv_ms > 0 else 0.0

@@ -15,7 +15,7 @@ F32, BF16, BF16X2 = 0, 1, 2
 ACT_NONE, ACT_RELU, ACT_SWISH, ACT_SIGMOID = 0, 1, 2, 3
 NHWC, NCHW = 0, 1
 (OP_CONV, OP_DWCONV, OP_SE_FC, OP_SE_SCALE, OP_RESIZE, OP_MAXPOOL, OP_ELTWISE, OP_TO_NHWC, OP_TO_NCHW,
- OP_ZERO, OP_UPCONV, OP_STEM) = range(1, 13)
+ OP_ZERO, OP_UPCONV, OP_STEM, OP_TAPSUM) = range(1, 14)
 
 
 def _ints(*names):
@@ -27,7 +27,7 @@ class EdeConv(Structure):
                 ("w_umma", c_void_p), ("w_direct", c_void_p)] + _ints(
         "n", "h", "w", "cin_p", "x_cs", "x_co", "oh", "ow", "cout_p", "y_cs", "y_co", "res_cs", "res_co",
         "kh", "kw", "sh", "sw", "pt", "pl", "act", "act_c_end", "x_dtype", "y_dtype", "x_layout", "relu_in",
-        "w_umma_cout_p", "w_umma_cin_p", "force_direct", "w_passes", "w_pack_g")
+        "w_umma_cout_p", "w_umma_cin_p", "force_direct", "w_passes", "w_pack_g", "w_per_image")
 
 
 class EdeUmmaCfg(Structure):
@@ -45,7 +45,8 @@ class EdeDwConv(Structure):
 
 class EdeSeFc(Structure):
     _fields_ = [("pool_sum", c_void_p), ("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p),
-                ("gate", c_void_p)] + _ints("n", "c", "c_p", "csq") + [("inv_hw", c_float)] + _ints("clear_pool", "w2_transposed", "pool_parts")
+                ("gate", c_void_p)] + _ints("n", "c", "c_p", "csq") + [("inv_hw", c_float)] + _ints("clear_pool", "w2_transposed", "pool_parts") + [
+        ("w_src", c_void_p), ("w_dst", c_void_p)] + _ints("w_rows", "w_cols", "w_passes", "w_split")
 
 
 class EdeSeScale(Structure):
@@ -81,6 +82,11 @@ class EdeUpConv(Structure):
 class EdeStem(Structure):
     _fields_ = [("x", c_void_p), ("y", c_void_p), ("w", c_void_p), ("scale", c_void_p), ("shift", c_void_p)] + _ints(
         "n", "cin", "h", "w_", "oh", "ow", "cout_p", "y_cs", "y_co", "k", "s", "pt", "pl", "act", "y_dtype")
+
+
+class EdeTapSum(Structure):
+    _fields_ = [("z", c_void_p), ("y", c_void_p), ("scale", c_void_p), ("shift", c_void_p)] + _ints(
+        "n", "h", "w", "z_cs", "z_co", "y_cs", "y_co", "y_dtype", "kh", "kw", "pt", "pl", "act")
 
 
 class EdeDepthEpilogue(Structure):
@@ -125,7 +131,7 @@ class _Zero(Structure):
 class _OpU(Union):
     _fields_ = [("conv", EdeConv), ("dw", EdeDwConv), ("se_fc", EdeSeFc), ("se_scale", EdeSeScale),
                 ("resize", EdeResize), ("maxpool", EdeMaxPool), ("eltwise", EdeEltwise), ("layout", EdeLayout),
-                ("upconv", EdeUpConv), ("stem", EdeStem), ("zero", _Zero)]
+                ("upconv", EdeUpConv), ("stem", EdeStem), ("tapsum", EdeTapSum), ("zero", _Zero)]
 
 
 class EdeOp(Structure):
@@ -134,7 +140,7 @@ class EdeOp(Structure):
 
 OP_FIELD = {OP_CONV: "conv", OP_DWCONV: "dw", OP_SE_FC: "se_fc", OP_SE_SCALE: "se_scale", OP_RESIZE: "resize",
             OP_MAXPOOL: "maxpool", OP_ELTWISE: "eltwise", OP_TO_NHWC: "layout", OP_TO_NCHW: "layout",
-            OP_ZERO: "zero", OP_UPCONV: "upconv", OP_STEM: "stem"}
+            OP_ZERO: "zero", OP_UPCONV: "upconv", OP_STEM: "stem", OP_TAPSUM: "tapsum"}
 
 # every symbol include/ede.h declares (checked by tests/test_cabi.py without a GPU)
 EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_stem_conv", "ede_stem_supported", "ede_dwconv2d", "ede_se_fc", "ede_se_scale",
@@ -142,7 +148,7 @@ EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_stem_
            "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_depth_epilogue", "ede_resample_coeffs", "ede_preprocess_frames", "ede_plan_run",
            "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof",
            "ede_prepack_conv_sizes", "ede_prepack_conv_to", "ede_prepack_conv", "ede_free", "ede_dwconv2d_pool_parts",
-           "ede_mesh_from_depth", "ede_render_workspace_bytes", "ede_render_mesh"]
+           "ede_mesh_from_depth", "ede_render_workspace_bytes", "ede_render_mesh", "ede_tapsum"]
 
 _lib = None
 
@@ -161,7 +167,7 @@ def lib():
                      ("ede_se_scale", EdeSeScale), ("ede_resize_bilinear_ac", EdeResize),
                      ("ede_maxpool3x3s2", EdeMaxPool), ("ede_eltwise", EdeEltwise),
                      ("ede_nchw_to_nhwc", EdeLayout), ("ede_nhwc_to_nchw", EdeLayout),
-                     ("ede_upconv_taps", EdeUpConv), ("ede_stem_conv", EdeStem),
+                     ("ede_upconv_taps", EdeUpConv), ("ede_stem_conv", EdeStem), ("ede_tapsum", EdeTapSum),
                      ("ede_depth_epilogue", EdeDepthEpilogue), ("ede_preprocess_frames", EdePreprocess)):
         f = getattr(L, name)
         f.argtypes = [POINTER(st), c_void_p]

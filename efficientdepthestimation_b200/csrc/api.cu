@@ -61,6 +61,7 @@ int ede_plan_run(const EdeOp* ops, int32_t n_ops, void* stream) {
             case EDE_OP_TO_NCHW: rc = ede_nhwc_to_nchw(&op.u.layout, stream); break;
             case EDE_OP_UPCONV: rc = ede_upconv_taps(&op.u.upconv, stream); break;
             case EDE_OP_STEM: rc = ede_stem_conv(&op.u.stem, stream); break;
+            case EDE_OP_TAPSUM: rc = ede_tapsum(&op.u.tapsum, stream); break;
             case EDE_OP_ZERO: rc = ede_fill_zero(op.u.zero.p, op.u.zero.bytes, stream); break;
             default:
                 ede::set_error("ede_plan_run: op %d has unknown kind %d", i, op.kind);

@@ -113,7 +113,39 @@ __global__ void __launch_bounds__(1024) se_fc_kernel(const EdeSeFc a) {
                 for (int j = 0; j < a.csq; ++j) s = fmaf(a.w2[(long long)c * a.csq + j], hid[j], s);
             }
         }
-        a.gate[(long long)n * a.c_p + c] = c < a.c ? apply_act(s, EDE_ACT_SIGMOID) : 0.f;
+        const float g = c < a.c ? apply_act(s, EDE_ACT_SIGMOID) : 0.f;
+        a.gate[(long long)n * a.c_p + c] = g;
+        mean[c] = g;                                       // kept for the weight fold below (mean is dead by now)
+    }
+    if (a.w_src) {
+        // (x * g) . W == x . (g * W): scale column ci of the consumer's 1x1 weights by this image's gate and re-split
+        // into bf16 hi / lo, 8 columns (= 8 consecutive channels, also in the doubled-lane split layout) per step
+        __syncthreads();
+        const int rows = a.w_rows, cols8 = a.w_cols >> 3;
+        const uint4* src = reinterpret_cast<const uint4*>(a.w_src);
+        uint4* dst = reinterpret_cast<uint4*>(a.w_dst) + (long long)n * a.w_passes * rows * cols8;
+        const long long lo_off = (long long)rows * cols8;
+        for (int e = threadIdx.x; e < rows * cols8; e += blockDim.x) {
+            const int ci = (e % cols8) << 3;
+            const int lane = a.w_split ? ((ci >> 4) << 3) : ci;
+            const uint4 h = src[e];
+            uint4 l = make_uint4(0, 0, 0, 0);
+            if (a.w_passes == 2) l = src[lo_off + e];
+            const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+            uint32_t oh[4], ol[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float g0 = lane + 2 * q < a.c_p ? mean[lane + 2 * q] : 0.f;
+                const float g1 = lane + 2 * q + 1 < a.c_p ? mean[lane + 2 * q + 1] : 0.f;
+                const float v0 = (bf16lo_f(hw[q]) + bf16lo_f(lw[q])) * g0, v1 = (bf16hi_f(hw[q]) + bf16hi_f(lw[q])) * g1;
+                const __nv_bfloat162 hh = __floats2bfloat162_rn(v0, v1);
+                oh[q] = *reinterpret_cast<const uint32_t*>(&hh);
+                const __nv_bfloat162 ll = __floats2bfloat162_rn(v0 - bf16lo_f(oh[q]), v1 - bf16hi_f(oh[q]));
+                ol[q] = *reinterpret_cast<const uint32_t*>(&ll);
+            }
+            dst[e] = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+            if (a.w_passes == 2) dst[lo_off + e] = make_uint4(ol[0], ol[1], ol[2], ol[3]);
+        }
     }
 }
 
@@ -333,6 +365,9 @@ int ede_dwconv2d_pool_parts(const EdeDwConv* a) {
 int ede_se_fc(const EdeSeFc* a, void* stream) {
     EDE_REQUIRE(a && a->pool_sum && a->w1 && a->b1 && a->w2 && a->b2 && a->gate, "ede_se_fc: null argument");
     EDE_REQUIRE(a->n > 0 && a->c > 0 && a->c <= a->c_p && a->csq > 0, "ede_se_fc: bad shape");
+    EDE_REQUIRE(a->w_src == nullptr || (a->w_dst && a->w_rows > 0 && a->w_cols > 0 && (a->w_cols & 7) == 0 &&
+                                        (a->w_passes == 1 || a->w_passes == 2)),
+                "ede_se_fc: bad weight-fold description");
     const size_t smem = (size_t)(a->c_p + a->csq) * sizeof(float);
     EDE_REQUIRE(smem <= 48 * 1024, "ede_se_fc: too many channels (%d)", a->c_p);
     // latency bound (one block per image, three dependent phases): wide blocks for the wide late stages

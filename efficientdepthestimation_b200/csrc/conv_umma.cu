@@ -94,6 +94,7 @@ struct alignas(64) UmmaParams {
     int pack_g, kw_steps, n_cols;            // pack_g taps share one MMA (M rows = [tap j][128/pack_g channels]); kw_steps = ceil(kw/pack_g); n_cols = UMMA N of the swapped form
     int a_stages, b_stages, a_stage_bytes, b_stage_bytes, b_tx_bytes;
     int b_group;          // taps per weight stage (one TMA box, one wait, one commit); > 1 only swapped + resident
+    int w_img_taps;       // > 0: the weight tensor map holds one set of that many taps per image (SE gate folded in)
     int layout_type, sbo_bytes, tmem_cols, flat;
     uint32_t idesc;
     void* y;
@@ -439,7 +440,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                         if (prof) w_empty += clock64() - c0;
                         if (leader) {
                             mbar_expect_tx(b_full(b_st), b_tx);
-                            tma_load_3d(b_base + b_st * b_stage_bytes, &p.tm_b, b_full(b_st), cch, wrow, tap);
+                            tma_load_3d(b_base + b_st * b_stage_bytes, &p.tm_b, b_full(b_st), cch, wrow, tap + t.img * p.w_img_taps);
                         }
                         if (++b_st == b_stages) { b_st = 0; b_ph ^= 1; }
 #if EDE_UNIFORM_PRODUCER
@@ -791,7 +792,9 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     const int force_npad = env_int("EDE_UMMA_NPAD", 0);
     const int force_group = env_int("EDE_UMMA_GROUP", 0);
     const int n16 = round_up(a.cout_p, 16);
-    const bool is_1x1 = a.kh == 1 && a.kw == 1 && a.sh == 1 && a.pt == 0 && a.pl == 0 && a.oh == a.h && a.ow == a.w;
+    // 1x1 convs fold N*H*W into one pixel axis -- unless every image has its own weights (tiles must not span images)
+    const bool is_1x1 = a.kh == 1 && a.kw == 1 && a.sh == 1 && a.pt == 0 && a.pl == 0 && a.oh == a.h && a.ow == a.w &&
+                        a.w_per_image <= 0;
     const int OH = is_1x1 ? 1 : a.oh;
     const long long OWl = is_1x1 ? (long long)a.n * a.h * a.w : a.ow;
     if (OWl > 0x7fffffffLL) return;
@@ -1094,6 +1097,11 @@ static int conv_umma_build(const EdeConv& a, const EdeUmmaCfg& c, ConvLaunch& L)
         p.b_group = b_group;
         cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)w_rows_box, (cuuint32_t)b_group};
         dims[2] = (cuuint64_t)(a.kh * ceil_div(a.kw, c.pack_g) * a.w_passes);
+        if (a.w_per_image > 0) {
+            if (a.w_per_image != (int)dims[2]) { set_error("ede_conv2d: w_per_image must equal the taps of one weight set (%d)", (int)dims[2]); return EDE_E_ARG; }
+            p.w_img_taps = a.w_per_image;
+            dims[2] *= (cuuint64_t)a.n;
+        }
         cuuint32_t es[3] = {1, 1, 1};
         CUresult r = enc(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, (void*)a.w_umma, dims, strides, box, es,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -1183,7 +1191,7 @@ static int conv_umma_launch(const EdeConv& a, ConvLaunch& L, cudaStream_t st) {
 }
 
 // ---- launch cache: EdeConv bytes (pointers, shapes, flags) + device -> tile configuration + tensor maps
-constexpr size_t CONV_KEY_BYTES = offsetof(EdeConv, w_pack_g) + sizeof(int32_t);
+constexpr size_t CONV_KEY_BYTES = offsetof(EdeConv, w_per_image) + sizeof(int32_t);
 struct ConvCacheEntry {
     unsigned char key[CONV_KEY_BYTES];
     int dev;

@@ -70,6 +70,8 @@ template <> __device__ __forceinline__ float2 store_pair<bf16x2_t>(bf16x2_t* px,
     return make_float2(hx + bf16lo_f(ul), hy + bf16hi_f(ul));
 }
 
+template <int S> struct DwTileRows { static constexpr int value = S == 1 ? 3 : 2; };   // output rows per item
+
 template <typename T, int K, int S, int CH>
 __global__ void __launch_bounds__(DT_THREADS, 2) dwconv_tile_kernel(const __grid_constant__ DwTileParams p) {
     constexpr int SUB = 64 / CH;                           // pixel groups per warp (CH / 2 lanes each)
@@ -107,49 +109,65 @@ __global__ void __launch_bounds__(DT_THREADS, 2) dwconv_tile_kernel(const __grid
         tma_load_4d(smem_u32(tile), &p.tm_x, smem_u32(&bar), c0, -a.pl, oh0 * S - a.pt, n);
     }
     mbar_wait(smem_u32(&bar), 0);
-    // split bf16 -> fp32 in place, once per element (rows the band does not need are skipped)
-    const int rows_in = (rows - 1) * S + K;
+    // split bf16 -> fp32 in place, once per element
     if (sizeof(T) == 4 && !std::is_same<T, float>::value) {
-        const int groups = rows_in * p.box_w * (CH / 8);
+        const int groups = p.box_h * p.box_w * (CH / 8);
         for (int g = threadIdx.x; g < groups; g += DT_THREADS) expand_group<T>(tile + (size_t)g * 32);
         __syncthreads();
     }
+    // an item = NR output rows x 2 output columns of the thread's channel pair: its (NR-1)*S+K input rows are read once,
+    // (K+S) LDS.64 per row, and feed up to NR*2*K packed FMAs -- 2-3x less shared-memory traffic than one row per item
+    constexpr int NR = DwTileRows<S>::value;
+    constexpr int RIN = (NR - 1) * S + K;
     const bool swish = a.act == EDE_ACT_SWISH;
     const int cpairs = (a.ow + 1) >> 1;
-    const int items = rows * cpairs;
+    const int items = ((rows + NR - 1) / NR) * cpairs;
     float2 psum = make_float2(0.f, 0.f);
     for (int it = warp * SUB + sub; it < items; it += NWARP * SUB) {
-        const int oy = it / cpairs, ox = (it - oy * cpairs) * 2;
+        const int ib = it / cpairs;
+        const int oy = ib * NR, ox = (it - ib * cpairs) * 2;
         const uint8_t* base = tile + ((size_t)(oy * S) * p.box_w + ox * S) * PB + cl * 8;
-        float2 acc0 = make_float2(0.f, 0.f), acc1 = make_float2(0.f, 0.f);
+        float2 acc[NR][2];
 #pragma unroll
-        for (int ky = 0; ky < K; ++ky) {
+        for (int j = 0; j < NR; ++j) acc[j][0] = acc[j][1] = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < RIN; ++r) {
             float2 xr[K + S];
 #pragma unroll
             for (int kx = 0; kx < K + S; ++kx) xr[kx] = *reinterpret_cast<const float2*>(base + kx * PB);
 #pragma unroll
-            for (int kx = 0; kx < K; ++kx) {
-                acc0 = ffma2(xr[kx], w[ky * K + kx], acc0);
-                acc1 = ffma2(xr[kx + S], w[ky * K + kx], acc1);
+            for (int j = 0; j < NR; ++j) {
+                const int ky = r - j * S;                  // compile-time after unrolling
+                if (ky >= 0 && ky < K) {
+#pragma unroll
+                    for (int kx = 0; kx < K; ++kx) {
+                        acc[j][0] = ffma2(xr[kx], w[ky * K + kx], acc[j][0]);
+                        acc[j][1] = ffma2(xr[kx + S], w[ky * K + kx], acc[j][1]);
+                    }
+                }
             }
             base += (size_t)p.box_w * PB;
         }
         if (c_ok) {
-            T* yrow = reinterpret_cast<T*>(a.y) + (((long long)n * a.oh + oh0 + oy) * a.ow + ox) * a.y_cs + a.y_co;
-            float2 v0 = make_float2(fmaf(acc0.x, sc.x, sf.x), fmaf(acc0.y, sc.y, sf.y));
-            float2 v1 = make_float2(fmaf(acc1.x, sc.x, sf.x), fmaf(acc1.y, sc.y, sf.y));
-            if (swish) {
-                v0 = make_float2(swish_fast(v0.x), swish_fast(v0.y));
-                v1 = make_float2(swish_fast(v1.x), swish_fast(v1.y));
-            } else {
-                v0 = make_float2(apply_act(v0.x, a.act), apply_act(v0.y, a.act));
-                v1 = make_float2(apply_act(v1.x, a.act), apply_act(v1.y, a.act));
-            }
-            v0 = store_pair<T>(yrow, c, v0);
-            psum.x += v0.x; psum.y += v0.y;
-            if (ox + 1 < a.ow) {
-                v1 = store_pair<T>(yrow + a.y_cs, c, v1);
-                psum.x += v1.x; psum.y += v1.y;
+#pragma unroll
+            for (int j = 0; j < NR; ++j) {
+                if (oy + j >= rows) break;
+                T* yrow = reinterpret_cast<T*>(a.y) + (((long long)n * a.oh + oh0 + oy + j) * a.ow + ox) * a.y_cs + a.y_co;
+                float2 v0 = make_float2(fmaf(acc[j][0].x, sc.x, sf.x), fmaf(acc[j][0].y, sc.y, sf.y));
+                float2 v1 = make_float2(fmaf(acc[j][1].x, sc.x, sf.x), fmaf(acc[j][1].y, sc.y, sf.y));
+                if (swish) {
+                    v0 = make_float2(swish_fast(v0.x), swish_fast(v0.y));
+                    v1 = make_float2(swish_fast(v1.x), swish_fast(v1.y));
+                } else {
+                    v0 = make_float2(apply_act(v0.x, a.act), apply_act(v0.y, a.act));
+                    v1 = make_float2(apply_act(v1.x, a.act), apply_act(v1.y, a.act));
+                }
+                v0 = store_pair<T>(yrow, c, v0);
+                psum.x += v0.x; psum.y += v0.y;
+                if (ox + 1 < a.ow) {
+                    v1 = store_pair<T>(yrow + a.y_cs, c, v1);
+                    psum.x += v1.x; psum.y += v1.y;
+                }
             }
         }
     }
@@ -193,12 +211,14 @@ static bool dwconv_tile_config(const EdeDwConv& a, DwTileCfg& c) {
     for (int i = 0; i < 3; ++i) {
         const int ch = chs[i];
         const int row_bytes = box_w * ch * 4;
-        int box_h = std::min(256, (DT_SMEM_TARGET - 256) / row_bytes);
-        if (box_h < a.k) continue;
-        int band = std::min(a.oh, (box_h - a.k) / a.s + 1);
-        const int n_bands = ceil_div(a.oh, band);
-        band = ceil_div(a.oh, n_bands);                    // even bands
-        box_h = (band - 1) * a.s + a.k;
+        const int box_h_max = std::min(256, (DT_SMEM_TARGET - 256) / row_bytes);
+        const int nr = a.s == 1 ? 3 : 2;                   // DwTileRows: bands are whole items
+        if (box_h_max < a.k) continue;
+        const int max_rows = ((box_h_max - a.k) / a.s + 1) / nr * nr;
+        if (max_rows < nr) continue;
+        const int n_bands = ceil_div(a.oh, max_rows);
+        const int band = round_up(ceil_div(a.oh, n_bands), nr);
+        const int box_h = (band - 1) * a.s + a.k;
         // cost ~ bytes fetched (halo rows of neighbouring bands re-read, idle channel lanes of the last chunk included;
         // padding rows / columns are TMA zero fill and cost nothing) + a fixed cost per block
         const double chunks = ceil_div(a.c_p, ch);

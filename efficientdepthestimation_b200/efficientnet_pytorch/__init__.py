@@ -98,9 +98,13 @@ class MBConvBlock(EdeModule, nn.Module):
         if self._cfg["expand"] != 1:
             h = g.conv_bn_act(h, self._expand_conv, self._bn0, A.ACT_SWISH, tag=tag + ".expand")
         h, pool = g.dwconv_bn_act(h, self._depthwise_conv, self._bn1, A.ACT_SWISH, pool=True, tag=tag + ".dw")
+        res = x if self._id_skip else None
+        if g.se_fold_pays(h, self._cfg["cout"]):
+            # (h * gate) . W == h . (gate * W): no pass over the expanded tensor, the gate rides in per-image weights
+            h, fold = g.se_gate(h, pool, self._se_reduce, self._se_expand, tag=tag + ".se", fold=True)
+            return g.conv_bn_act(h, self._project_conv, self._bn2, A.ACT_NONE, res=res, tag=tag + ".project", se_fold=fold)
         h = g.se_gate(h, pool, self._se_reduce, self._se_expand, tag=tag + ".se")
-        return g.conv_bn_act(h, self._project_conv, self._bn2, A.ACT_NONE, res=x if self._id_skip else None,
-                             tag=tag + ".project")
+        return g.conv_bn_act(h, self._project_conv, self._bn2, A.ACT_NONE, res=res, tag=tag + ".project")
 
 
 class EfficientNet(EdeModule, nn.Module):

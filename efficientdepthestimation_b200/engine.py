@@ -27,6 +27,8 @@ _PRECISION = os.environ.get("EDE_PRECISION", "bf16")
 _ENCODER_PRECISION = os.environ.get("EDE_ENCODER_PRECISION", "bf16x2")
 _ELT = {A.F32: 4, A.BF16: 2, A.BF16X2: 4}
 _ALIGN = 1024
+_SE_FOLD = os.environ.get("EDE_SE_FOLD", "1") != "0"   # SE gate folded into the project conv's per-image weights
+_TAPSUM = os.environ.get("EDE_TAPSUM", "1") != "0"     # one-output-channel k x k convs as 1x1 GEMM + tap sum
 
 
 def set_precision(mode: str, encoder: Optional[str] = None) -> None:
@@ -249,7 +251,7 @@ class Graph:
         self.outputs.append((i, (v.n, v.c, v.h, v.w)))
 
     def conv(self, x: View, parts, stride=1, pad=(0, 0, 0, 0), act=A.ACT_NONE, res: Optional[View] = None,
-             out: Optional[View] = None, relu_in=False, out_dtype=None, tag="conv") -> View:
+             out: Optional[View] = None, relu_in=False, out_dtype=None, tag="conv", se_fold=None) -> View:
         """Dense conv + folded BN + activation (+ residual).  `parts` is a list of
         (weight OIHW, bn module|None, bias|None, activated: bool); the parts share the input and
         their outputs are laid side by side (each padded to 8 lanes) -- used to run the two 5x5
@@ -266,6 +268,10 @@ class Graph:
         oh = (x.h + pt + pb - kh) // stride + 1
         ow = (x.w + pl + pr - kw) // stride + 1
         cin = x.c
+        if (_TAPSUM and self.precision == "bf16" and len(parts) == 1 and int(parts[0][0].shape[0]) == 1 and kh * kw >= 9
+                and kh * kw <= 32 and stride == 1 and res is None and not relu_in and (oh, ow) == (x.h, x.w)
+                and x.dtype != A.F32 and not tag.endswith(".z_gemm")):
+            return self._conv_one_channel(x, parts[0], pad, act, out, out_dtype, tag)
         # a split-bf16 input is consumed as a plain bf16 tensor with twice the lanes (include/ede.h)
         split_in = x.dtype == A.BF16X2
         in_lanes = x.lanes
@@ -319,7 +325,8 @@ class Graph:
                        x_dtype=A.BF16 if split_in else x.dtype, y_dtype=out.dtype, x_layout=A.NHWC,
                        relu_in=1 if relu_in else 0, w_umma_cout_p=P.ceil_to(cout_p, 16),
                        w_umma_cin_p=P.ceil_to(x.c_p * mul, 64),
-                       force_direct=1 if self.precision == "fp32" else 0, w_passes=passes, w_pack_g=-1)
+                       force_direct=1 if self.precision == "fp32" else 0, w_passes=passes, w_pack_g=-1,
+                       w_per_image=kh * kw * passes if se_fold is not None else 0)
         # ask the tile picker whether the tcgen05 path takes this conv and how many kernel-row taps it wants on the
         # 128 M rows, then have ede_prepack_conv_to pack for exactly that (one kernel per conv, Plan.__init__)
         cfg = A.umma_config(st)
@@ -334,9 +341,43 @@ class Graph:
             job["w_direct"] = self._reserve(bytes4[1])
             st.w_umma, st.w_pack_g = None, 1
         self.prepacks.append(job)
+        w_used = job["w_umma"]
+        if se_fold is not None:
+            # the squeeze-excite gate of the input rides in the weights: ede_se_fc writes one gate-scaled copy of this
+            # conv's packed weights per image (EdeSeFc.w_src / w_dst), and the conv indexes them by image
+            if not cfg.eligible or kh * kw != 1 or pack_g != 1:
+                raise RuntimeError(f"{tag}: the SE gate can only be folded into a 1x1 conv on the tcgen05 path")
+            w_used = self._reserve(x.n * bytes4[0])
+            fc = se_fold["st"]
+            fc.w_rows, fc.w_cols, fc.w_passes, fc.w_split = dims2[0], dims2[1], passes, 1 if split_in else 0
+            fc._wrefs += [("w_src", job["w_umma"]), ("w_dst", w_used)]
         refs = [("x", x.buf), ("y", out.buf)] + ([("res", res.buf)] if res is not None else [])
-        self._add(A.OP_CONV, st, refs, tag, [("scale", scale), ("shift", shift), ("w_umma", job["w_umma"]),
+        self._add(A.OP_CONV, st, refs, tag, [("scale", scale), ("shift", shift), ("w_umma", w_used),
                                              ("w_direct", job["w_direct"])])
+        return out
+
+    def _conv_one_channel(self, x: View, part, pad, act, out, out_dtype, tag) -> View:
+        """k x k stride-1 conv to ONE channel (R.conv2, modules.py:296): a 128-row MMA would carry one useful row, so
+        the Cin contraction of all kh*kw taps runs as ONE 1x1 GEMM (kh*kw output lanes, fp32) and EDE_OP_TAPSUM adds
+        the taps at their pixel offsets (csrc/upconv.cu).  Exact in real arithmetic; z stays fp32."""
+        wt, bn, bias, _ = part
+        wt = _cpu(wt).float()
+        cin, kh, kw = int(wt.shape[1]), int(wt.shape[2]), int(wt.shape[3])
+        wz = wt[0].permute(1, 2, 0).reshape(kh * kw, cin, 1, 1)                     # lane ty*kw+tx
+        prev = self.count_ref_flops
+        self.count_ref_flops = False
+        z = self.conv(x, [(wz, None, None, False)], 1, (0, 0, 0, 0), A.ACT_NONE, out_dtype=A.F32, tag=tag + ".z_gemm")
+        self.count_ref_flops = prev
+        fl = 2.0 * x.n * x.h * x.w * cin * kh * kw
+        self.flops += fl
+        self.conv_flops += fl
+        if out is None:
+            out = self.new_view(x.n, x.h, x.w, 1, out_dtype)
+        sc, sf = P.fold_bn(1, bn if isinstance(bn, dict) or bn is None else _bn_dict(bn), _cpu(bias), "cpu")
+        scale, shift = self._dev(P.place_lanes(sc, out.lanes)), self._dev(P.place_lanes(sf, out.lanes))
+        st = A.EdeTapSum(z=None, y=None, scale=None, shift=None, n=x.n, h=x.h, w=x.w, z_cs=z.buf.cs, z_co=z.co,
+                         y_cs=out.buf.cs, y_co=out.co, y_dtype=out.dtype, kh=kh, kw=kw, pt=pad[0], pl=pad[1], act=act)
+        self._add(A.OP_TAPSUM, st, [("z", z.buf), ("y", out.buf)], tag + ".tapsum", [("scale", scale), ("shift", shift)])
         return out
 
     def _stem(self, x: View, part, stride, pad, act, out_dtype, tag) -> View:
@@ -386,12 +427,12 @@ class Graph:
         return y
 
     def conv_bn_act(self, x: View, conv, bn=None, act=A.ACT_NONE, res=None, out=None, relu_in=False,
-                    out_dtype=None, tag="conv") -> View:
+                    out_dtype=None, tag="conv", se_fold=None) -> View:
         """nn.Conv2d (+ nn.BatchNorm2d) (+ activation) as one fused operator."""
         if conv.groups != 1:
             raise RuntimeError(f"{tag}: grouped convolution is not a dense conv")
         return self.conv(x, [(conv.weight, bn, conv.bias, act != A.ACT_NONE)], conv.stride[0], _pad4(conv), act,
-                         res, out, relu_in, out_dtype, tag)
+                         res, out, relu_in, out_dtype, tag, se_fold=se_fold)
 
     def dwconv_bn_act(self, x: View, conv, bn, act, pool: bool, tag="dwconv"):
         """Depthwise conv + BN + activation; with pool=True also the per-(n,c) sums for SE."""
@@ -426,8 +467,20 @@ class Graph:
         self.exec_flops += 2.0 * x.n * oh * ow * c * k * k
         return out, pool_t
 
-    def se_gate(self, x: View, pool_t, reduce_conv, expand_conv, tag="se") -> View:
-        """Squeeze-excite: gate = sigmoid(W2 swish(W1 mean + b1) + b2); returns x * gate."""
+    def se_fold_pays(self, x: View, cout: int) -> bool:
+        """Fold the gate into the consumer's weights (one scaled weight set per image) instead of a full read + write
+        of the gated tensor?  Pays while the per-image weights are much smaller than the tensor: the early, high-
+        resolution MBConv blocks.  tcgen05 path only."""
+        if not _SE_FOLD or self.precision != "bf16" or self.dry_no_lib:
+            return False
+        mul = 2 if x.dtype == A.BF16X2 else 1
+        passes = 2 if self.act_dtype == A.BF16X2 else 1
+        w_bytes = passes * P.ceil_to(P.ceil8(cout), 16) * P.ceil_to(x.c_p * mul, 64) * 2
+        return 8 * w_bytes <= x.h * x.w * x.c_p * _ELT[x.dtype]
+
+    def se_gate(self, x: View, pool_t, reduce_conv, expand_conv, tag="se", fold=False):
+        """Squeeze-excite: gate = sigmoid(W2 swish(W1 mean + b1) + b2); returns x * gate -- or, with fold=True,
+        (x, handle) for conv(..., se_fold=handle), which applies the gate through its weights."""
         c, csq = x.c, int(reduce_conv.weight.shape[0])
         idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0])
         src = torch.tensor([v for v in x.lanes if v >= 0])
@@ -446,6 +499,8 @@ class Graph:
                        inv_hw=1.0 / (x.h * x.w), clear_pool=1, w2_transposed=1, pool_parts=pool_t.parts)
         self._add(A.OP_SE_FC, st, [], tag + ".fc",
                   [("pool_sum", pool_t), ("w1", w1), ("b1", b1), ("w2", w2), ("b2", b2), ("gate", gate)])
+        if fold:
+            return x, dict(st=st, gate=gate)
         out = View(self.new_buf(x.n, x.h, x.w, x.c_p, x.dtype), 0, x.lanes)
         st = A.EdeSeScale(x=None, y=None, gate=None, n=x.n, hw=x.h * x.w, c_p=x.c_p,
                           x_cs=x.buf.cs, x_co=x.co, y_cs=out.buf.cs, y_co=out.co, dtype=x.dtype)

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 8
+#define EDE_ABI_VERSION 10
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
@@ -69,6 +69,9 @@ typedef struct EdeConv {
                                j*(128/G)+c = w[c][.][ky][gx*G+j] (zero rows for taps >= kw), needs
                                cout_p <= 128/G; -1 only for ede_conv2d_umma_config: 'which G should I
                                prepack for?' (answer in EdeUmmaCfg.pack_g)                            */
+    int32_t w_per_image;    /* T > 0: w_umma holds n weight sets of T taps each (image i uses taps [i*T, (i+1)*T)): the
+                               squeeze-excite gate folded into the project conv's weights by ede_se_fc (w_dst); tiles
+                               then never span two images */
 } EdeConv;
 int ede_conv2d(const EdeConv* a, void* stream);
 
@@ -148,6 +151,12 @@ typedef struct EdeSeFc {
                                ede_dwconv2d accumulates from zero without a separate ede_fill_zero launch */
     int32_t w2_transposed;  /* 1: w2 is fp32 [csq][c_p] (coalesced reads), 0: [c_p][csq]            */
     int32_t pool_parts;     /* slabs of pool_sum (see EdeDwConv.pool_parts), summed in slab order; 0 = 1   */
+    /* optional: fold the gate into the weights of the 1x1 conv that consumes the gated tensor (x * g) . W == x . (g * W):
+     * w_src = that conv's w_umma (bf16 [w_passes][w_rows][w_cols], hi then lo halves), w_dst = bf16 [n][w_passes][w_rows]
+     * [w_cols] with column ci scaled by gate[n][lane(ci)] and re-split into hi / lo; w_split = 1 when the conv reads a
+     * split-bf16 input (columns = doubled lanes: groups of 16 = [8 hi][8 lo] of 8 channels).  NULL = off. */
+    const void* w_src; void* w_dst;
+    int32_t w_rows, w_cols, w_passes, w_split;
 } EdeSeFc;
 int ede_se_fc(const EdeSeFc* a, void* stream);
 
@@ -186,6 +195,17 @@ typedef struct EdeUpConv {
     int32_t kh, kw, pt, pl, act, act_c_end;
 } EdeUpConv;
 int ede_upconv_taps(const EdeUpConv* a, void* stream);
+
+/* k x k stride-1 convolution to ONE output channel, second half: sum of the per-tap products that ede_conv2d left in z.
+ * replaces: the 5x5 conv to a single channel + bias that ends the Hu decoder (R.conv2, ReSIDE/models/modules.py:285,296).
+ * z: fp32 NHWC [n,h,w], lane ty*kw+tx = (W[0,:,ty,tx] . x) at that pixel (a 1x1 GEMM with kh*kw output lanes);
+ *   y[n,oy,ox, lane 0] = act(scale[0] * sum_{ty,tx} inside(oy+ty-pt, ox+tx-pl) * z[n, oy+ty-pt, ox+tx-pl, ty*kw+tx] + shift[0]),
+ *   lanes 1..7 of the 8-lane output group are written as zeros. */
+typedef struct EdeTapSum {
+    const float* z; void* y; const float* scale; const float* shift;
+    int32_t n, h, w, z_cs, z_co, y_cs, y_co, y_dtype, kh, kw, pt, pl, act;
+} EdeTapSum;
+int ede_tapsum(const EdeTapSum* a, void* stream);
 
 /* 3x3 stride-2 pad-1 max pooling. replaces: nn.MaxPool2d(3,2,1), ReSIDE/models/resnet.py:107. */
 typedef struct EdeMaxPool {
@@ -311,12 +331,12 @@ int ede_render_mesh(const EdeRender* a, void* stream);
 /* Run a pre-built operator list ("forward plan") back to back on one stream. */
 enum { EDE_OP_CONV = 1, EDE_OP_DWCONV = 2, EDE_OP_SE_FC = 3, EDE_OP_SE_SCALE = 4, EDE_OP_RESIZE = 5,
        EDE_OP_MAXPOOL = 6, EDE_OP_ELTWISE = 7, EDE_OP_TO_NHWC = 8, EDE_OP_TO_NCHW = 9, EDE_OP_ZERO = 10,
-       EDE_OP_UPCONV = 11, EDE_OP_STEM = 12 };
+       EDE_OP_UPCONV = 11, EDE_OP_STEM = 12, EDE_OP_TAPSUM = 13 };
 typedef struct EdeOp {
     int32_t kind; int32_t _pad;
     union {
         EdeConv conv; EdeDwConv dw; EdeSeFc se_fc; EdeSeScale se_scale; EdeResize resize;
-        EdeMaxPool maxpool; EdeEltwise eltwise; EdeLayout layout; EdeUpConv upconv; EdeStem stem;
+        EdeMaxPool maxpool; EdeEltwise eltwise; EdeLayout layout; EdeUpConv upconv; EdeStem stem; EdeTapSum tapsum;
         struct { void* p; int64_t bytes; } zero;
     } u;
 } EdeOp;

@@ -36,6 +36,8 @@ def op_bytes(kind, st):
         return st.n * st.h * st.w * (st.c * 4 + st.c_p * es[st.dtype])
     if kind == A.OP_STEM:
         return st.n * (st.cin * st.h * st.w_ * 4 + st.oh * st.ow * st.cout_p * es[st.y_dtype])
+    if kind == A.OP_TAPSUM:
+        return st.n * st.h * st.w * (st.kh * st.kw * 4 + 4)
     if kind == A.OP_UPCONV:
         return st.n * st.cgrp * (st.h * st.w * st.kh * st.kw * 4 + st.oh * st.ow * es[st.y_dtype])
     return 0
