@@ -22,7 +22,8 @@ _LOWRES_UPCONV = os.environ.get("EDE_LOWRES_UPCONV", "1") != "0"
 _LOWRES_MIN_CIN = int(os.environ.get("EDE_LOWRES_MIN_CIN", "192"))        # for moderate upsampling (4x in area)
 _ADD_AS_TAP_MAX_LANES = 64     # [x1 | bran2] lanes up to which conv1_2 + add run as one GEMM (fits one 64-channel chunk)
 # D.conv + that many up-projections at split-bf16 precision; -1 = by decoder width (measured, DESIGN.md section 5:
-# ENB4-HU, 224 channels, needs 3 to hold 1e-2 on every image of a batch of 32; ENB0-HU, 160 channels, holds it with 0)
+# ENB4-HU, 224 channels, needs 3 to hold 1e-2 on every image of a batch of 32; ENB0-HU, 160 channels, holds it with 0:
+# max 4.6e-3 over a batch of 64, and each level costs it 0.03-0.4 ms per batch-64 step)
 _ACCURATE_D = int(os.environ.get("EDE_ACCURATE_D", "-1"))
 _ACCURATE_D_MAX_C = 256
 _LOWRES_MIN_CIN_BIG = int(os.environ.get("EDE_LOWRES_MIN_CIN_BIG", "32"))  # for >= 8x in area: z is tiny
@@ -161,7 +162,7 @@ class D(EdeModule, nn.Module):
         # FLOPs but the largest single source of bf16 error, which a random-init net amplifies.
         # ResNet-50's D (1024 channels, 30 % of the FLOPs) stays plain bf16.
         c = self.conv.out_channels
-        level = 0 if c > _ACCURATE_D_MAX_C else (_ACCURATE_D if _ACCURATE_D >= 0 else (3 if c > 192 else 1))
+        level = 0 if c > _ACCURATE_D_MAX_C else (_ACCURATE_D if _ACCURATE_D >= 0 else (3 if c > 192 else 0))
         sizes = ([b3.h, b3.w], [b2.h, b2.w], [b1.h, b1.w], [b1.h * 2, b1.w * 2])
         ups = (self.up1, self.up2, self.up3, self.up4)
         with (g.encoder_scope() if level > 0 else contextlib.nullcontext()):
