@@ -207,8 +207,10 @@ static bool dwconv_tile_config(const EdeDwConv& a, DwTileCfg& c) {
     const bool force = env && env[0] == '1';
     double best_cost = 1e30;
     bool found = false;
-    const int chs[3] = {64, 32, 16};
-    for (int i = 0; i < 3; ++i) {
+    // 64 / 32 lanes: a (half-)warp's LDS.64 covers whole 128-byte wavefronts; 16-lane chunks would put the four pixel
+    // groups of a warp on the same banks (measured: 4x the shared-memory wavefronts), so they are not offered
+    const int chs[2] = {64, 32};
+    for (int i = 0; i < 2; ++i) {
         const int ch = chs[i];
         const int row_bytes = box_w * ch * 4;
         const int box_h_max = std::min(256, (DT_SMEM_TARGET - 256) / row_bytes);

@@ -198,46 +198,52 @@ namespace ede {
 // y[n,oy,ox] = act(scale * sum_{ty,tx} z[n, oy+ty-pt, ox+tx-pl, ty*kw+tx] + shift)   (taps outside the map contribute 0)
 // z = (W_tap . x) for every tap, produced by ede_conv2d as a 1x1 GEMM with kh*kw output lanes: a 5x5 conv to one channel
 // (R.conv2 of the Hu decoder, ReSIDE/models/modules.py:296) would fill one of 128 tensor-core rows; as a GEMM it fills 25.
-// A block owns 16 x 32 output pixels: the (16+kh-1) x (32+kw-1) pixel vectors of z it needs are staged once in shared
-// memory (coalesced 16-byte loads; pitch 33 floats so that neighbouring pixels' reads of one lane hit different banks),
-// then every thread adds the kh*kw taps of two output pixels.  HBM-bound: z is read 1.4x (tile halo), y written once.
-constexpr int TS_TH = 16, TS_TW = 32, TS_PITCH = 33;
+// A block owns 8 x 32 output pixels: the (8+kh-1) x (32+kw-1) pixel vectors of z it needs are staged once in shared
+// memory (coalesced 16-byte loads; the kh*kw tap lanes of a pixel are packed at an ODD pitch so that neighbouring
+// pixels' reads of one lane hit different banks), then every thread adds the kh*kw taps of its output pixel.
+// 43 KB of shared memory per block -> 5 blocks per SM hide the load phase of one block behind the sums of the others.
+constexpr int TS_TH = 8, TS_TW = 32;
 template <typename TY>
 __global__ void __launch_bounds__(256) tapsum_kernel(const EdeTapSum a) {
-    extern __shared__ float zt[];                               // [(TS_TH+kh-1) * (TS_TW+kw-1)][TS_PITCH]
+    extern __shared__ float zt[];                               // [(TS_TH+kh-1) * (TS_TW+kw-1)][pitch]
     pdl_trigger();
     pdl_wait();
     const int n = blockIdx.z, oy0 = blockIdx.y * TS_TH, ox0 = blockIdx.x * TS_TW;
     const int th = TS_TH + a.kh - 1, tw = TS_TW + a.kw - 1;
-    const int quads = (a.kh * a.kw + 3) >> 2;                   // float4 groups of one pixel vector that hold taps
+    const int taps = a.kh * a.kw, pitch = taps | 1;
+    const int quads = (taps + 3) >> 2;                          // float4 groups of one pixel vector that hold taps
     const float* zn = a.z + (long long)n * a.h * a.w * a.z_cs + a.z_co;
-    for (int i = threadIdx.x; i < th * tw * quads; i += 256) {
-        const int q = i % quads, p = i / quads;
-        const int ty = p / tw, tx = p - ty * tw;
-        const int iy = oy0 + ty - a.pt, ix = ox0 + tx - a.pl;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);             // outside the map: the conv's zero padding
-        if (iy >= 0 && iy < a.h && ix >= 0 && ix < a.w)
-            v = __ldg(reinterpret_cast<const float4*>(zn + ((long long)iy * a.w + ix) * a.z_cs) + q);
-        float* d = zt + p * TS_PITCH + 4 * q;
-        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    // 8 lanes per pixel (one float4 each), 32 pixels per pass; (ty, tx) advance without divisions
+    const int q = threadIdx.x & 7;
+    int p = threadIdx.x >> 3, ty = p / tw, tx = p - ty * tw;
+    for (; p < th * tw; p += 32) {
+        if (q < quads) {
+            const int iy = oy0 + ty - a.pt, ix = ox0 + tx - a.pl;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);         // outside the map: the conv's zero padding
+            if (iy >= 0 && iy < a.h && ix >= 0 && ix < a.w)
+                v = __ldg(reinterpret_cast<const float4*>(zn + ((long long)iy * a.w + ix) * a.z_cs) + q);
+            float* d = zt + p * pitch + 4 * q;
+            const int left = taps - 4 * q;
+            d[0] = v.x;
+            if (left > 1) d[1] = v.y;
+            if (left > 2) d[2] = v.z;
+            if (left > 3) d[3] = v.w;
+        }
+        tx += 32;
+        while (tx >= tw) { tx -= tw; ++ty; }
     }
     __syncthreads();
-    const float sc = a.scale[0], sf = a.shift[0];
-    const int lx = threadIdx.x & 31;
-#pragma unroll
-    for (int r = 0; r < 2; ++r) {
-        const int ly = (threadIdx.x >> 5) + 8 * r;
-        const int oy = oy0 + ly, ox = ox0 + lx;
-        if (oy >= a.h || ox >= a.w) continue;
-        float acc = 0.f;
-        for (int ty = 0; ty < a.kh; ++ty) {
-            const float* row = zt + ((ly + ty) * tw + lx) * TS_PITCH + ty * a.kw;
-            for (int tx = 0; tx < a.kw; ++tx) acc += row[tx * TS_PITCH + tx];
-        }
-        float v[8] = {apply_act(fmaf(acc, sc, sf), a.act), 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        TY* y = reinterpret_cast<TY*>(a.y) + (((long long)n * a.h + oy) * a.w + ox) * a.y_cs + a.y_co;
-        store8<TY>(y, v);
+    const int lx = threadIdx.x & 31, ly = threadIdx.x >> 5;
+    const int oy = oy0 + ly, ox = ox0 + lx;
+    if (oy >= a.h || ox >= a.w) return;
+    float acc = 0.f;
+    for (int ky = 0; ky < a.kh; ++ky) {
+        const float* row = zt + ((ly + ky) * tw + lx) * pitch + ky * a.kw;
+        for (int kx = 0; kx < a.kw; ++kx) acc += row[kx * pitch + kx];
     }
+    float v[8] = {apply_act(fmaf(acc, a.scale[0], a.shift[0]), a.act), 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    TY* y = reinterpret_cast<TY*>(a.y) + (((long long)n * a.h + oy) * a.w + ox) * a.y_cs + a.y_co;
+    store8<TY>(y, v);
 }
 }  // namespace ede
 
@@ -293,7 +299,7 @@ extern "C" int ede_tapsum(const EdeTapSum* a, void* stream) {
                 "ede_tapsum: bad shape");
     EDE_REQUIRE(a->kh <= 8 && a->kw <= 8, "ede_tapsum: kernel larger than 8x8");
     const dim3 grid((unsigned)ceil_div(a->w, ede::TS_TW), (unsigned)ceil_div(a->h, ede::TS_TH), (unsigned)a->n);
-    const size_t smem = (size_t)(ede::TS_TH + a->kh - 1) * (ede::TS_TW + a->kw - 1) * ede::TS_PITCH * sizeof(float);
+    const size_t smem = (size_t)(ede::TS_TH + a->kh - 1) * (ede::TS_TW + a->kw - 1) * ((a->kh * a->kw) | 1) * sizeof(float);
     EDE_DISPATCH_DTYPE(a->y_dtype, TY, {
         static bool attr_set[64] = {};
         int dev = 0;
