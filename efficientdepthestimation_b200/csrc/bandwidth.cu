@@ -83,6 +83,22 @@ __global__ void __launch_bounds__(1024) se_fc_kernel(const EdeSeFc a) {
     float* hid = sm + a.c_p;
     const int n = blockIdx.x;
     pdl_trigger();
+    // The FC weights are constants of the plan but fall out of the L2 between forwards (a step streams ~7 GB through
+    // it): pull them in while the depthwise kernel that feeds this one is still running, before the dependency wait
+    {
+        const char* w1b = reinterpret_cast<const char*>(a.w1);
+        const char* w2b = reinterpret_cast<const char*>(a.w2);
+        const int bytes = a.csq * a.c_p * 4;
+        for (int o = threadIdx.x * 128; o < bytes; o += blockDim.x * 128) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(w1b + o));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(w2b + o));
+        }
+        if (a.w_src) {
+            const char* wb = reinterpret_cast<const char*>(a.w_src);
+            const int wbytes = a.w_passes * a.w_rows * a.w_cols * 2;
+            for (int o = threadIdx.x * 128; o < wbytes; o += blockDim.x * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(wb + o));
+        }
+    }
     pdl_wait();
     const int parts = a.pool_parts > 1 ? a.pool_parts : 1;
     for (int i = threadIdx.x; i < a.c_p; i += blockDim.x) {
@@ -371,7 +387,7 @@ int ede_se_fc(const EdeSeFc* a, void* stream) {
     const size_t smem = (size_t)(a->c_p + a->csq) * sizeof(float);
     EDE_REQUIRE(smem <= 48 * 1024, "ede_se_fc: too many channels (%d)", a->c_p);
     // latency bound (one block per image, three dependent phases): wide blocks for the wide late stages
-    (void)launch_pdl(se_fc_kernel, dim3(a->n), dim3(a->c_p >= 512 ? 1024 : (a->c_p >= 192 ? 512 : 256)), smem,
+    (void)launch_pdl(se_fc_kernel, dim3(a->n), dim3(a->c_p >= 384 || a->w_src ? 1024 : 512), smem,
                      (cudaStream_t)stream, *a);
     EDE_LAUNCH_CHECK("se_fc_kernel");
     return EDE_OK;

@@ -45,7 +45,7 @@ def main():
             f.write(f"{name} | {a[0]} | {a[1] * scale:.3f} | {100 * a[1] / total:.1f}%"
                     + (f" | {a[2] / 1e6:.1f}" if has_dram else "") + "\n")
     if key and has_dram:
-        path = os.path.join(os.path.dirname(dst), "r01_traffic.json")
+        path = os.path.join(os.path.dirname(dst), "r02_traffic.json")
         t = json.load(open(path)) if os.path.exists(path) else {}
         conv = agg.get("conv_umma_kernel", [0, 0.0, 0.0])
         t[key] = {"conv_umma_dram_bytes_per_step": conv[2] / steps, "conv_umma_launches_per_step": conv[0] / steps,
