@@ -14,6 +14,14 @@ static inline unsigned grid_for(long long work, int block) {
     if (g > 0x7fffffffLL) g = 0x7fffffffLL;
     return (unsigned)g;
 }
+// grid-stride kernels: a few resident blocks per SM that each walk many items (independent loads of consecutive
+// iterations overlap) instead of one short-lived block per 256 items
+static inline unsigned grid_persistent(long long work, int block, int blocks_per_sm = 8) {
+    static const int cap_env = [] { const char* e = getenv("EDE_GRID_CAP"); return e && *e ? atoi(e) : 0; }();
+    const long long cap = 148LL * (cap_env > 0 ? cap_env : blocks_per_sm);
+    const long long g = grid_for(work, block);
+    return (unsigned)(g < cap ? g : cap);
+}
 
 // ------------------------------------------------------------------ depthwise conv + BN + act + SE squeeze
 template <typename T>
@@ -397,7 +405,7 @@ int ede_se_scale(const EdeSeScale* a, void* stream) {
     EDE_REQUIRE(a && a->x && a->y && a->gate, "ede_se_scale: null argument");
     EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_se_scale: channel counts must be multiples of 8");
     const long long total = (long long)a->n * a->hw * (a->c_p >> 3);
-    EDE_DISPATCH_DTYPE(a->dtype, T, ((void)launch_pdl(se_scale_kernel<T>, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream, *a)));
+    EDE_DISPATCH_DTYPE(a->dtype, T, ((void)launch_pdl(se_scale_kernel<T>, dim3(grid_persistent(total, 256)), dim3(256), 0, (cudaStream_t)stream, *a)));
     EDE_LAUNCH_CHECK("se_scale_kernel");
     return EDE_OK;
 }
@@ -409,7 +417,7 @@ int ede_resize_bilinear_ac(const EdeResize* a, void* stream) {
     const float sh = a->oh > 1 ? (float)(a->h - 1) / (float)(a->oh - 1) : 0.f;
     const float sw = a->ow > 1 ? (float)(a->w - 1) / (float)(a->ow - 1) : 0.f;
     const long long total = (long long)a->n * a->oh * a->ow * (a->c_p >> 3);
-    const unsigned g = grid_for(total, 256);
+    const unsigned g = grid_persistent(total, 256);
     cudaStream_t st = (cudaStream_t)stream;
     EDE_DISPATCH_DTYPE(a->x_dtype, TX,
                        EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(resize_kernel<TX, TY>, dim3(g), dim3(256), 0, st, *a, sh, sw))));
