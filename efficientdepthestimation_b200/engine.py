@@ -795,7 +795,7 @@ class Plan:
                 self._enqueue(ins, outs)                       # warm-up outside capture (lazy attribute setting etc.)
                 side.synchronize()
                 graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph, stream=side):
+                with torch.cuda.graph(graph, stream=side, capture_error_mode="thread_local"):
                     self._enqueue(ins, outs)
             torch.cuda.current_stream(self.device).wait_stream(side)
             self._cg = (graph, ins, outs)
@@ -1004,8 +1004,11 @@ class EdeModule:
                 hit = None
         if hit is None:
             plan, out_spec, in_spec = compile_module(self, args, dev, precision)
-            if os.environ.get("EDE_CUDA_GRAPH", "auto") == "1" or (
-                    os.environ.get("EDE_CUDA_GRAPH", "auto") == "auto" and not plan.dry and _graph_pays(plan)):
+            # CUDA-graph replay for launch-bound plans -- not for DataParallel replicas: their forwards run in one host
+            # thread per device at the same time, and a stream capture in one thread must not meet the plan build
+            # (allocations, uploads) of another
+            mode = os.environ.get("EDE_CUDA_GRAPH", "auto")
+            if not plan.dry and not replica and (mode == "1" or (mode == "auto" and _graph_pays(plan))):
                 plan.enable_graph()
             hit = (plan, out_spec, in_spec, _WEIGHT_EPOCH[0], None if replica else _fingerprint(self))
             cache[key] = hit
