@@ -148,7 +148,8 @@ EXPORTS = ["ede_conv2d", "ede_conv2d_umma_config", "ede_upconv_taps", "ede_stem_
            "ede_fill_zero", "ede_sobel", "ede_sobel_loss_metrics", "ede_edge_counts", "ede_depth_epilogue", "ede_resample_coeffs", "ede_preprocess_frames", "ede_plan_run",
            "ede_launch_count", "ede_version", "ede_last_error", "ede_umma_available", "ede_debug_umma_prof",
            "ede_prepack_conv_sizes", "ede_prepack_conv_to", "ede_prepack_conv", "ede_free", "ede_dwconv2d_pool_parts",
-           "ede_mesh_from_depth", "ede_render_workspace_bytes", "ede_render_mesh", "ede_tapsum"]
+           "ede_mesh_from_depth", "ede_render_workspace_bytes", "ede_render_mesh", "ede_tapsum",
+           "ede_upconv_taps_static", "ede_upconv_taps_static_max_bytes"]
 
 _lib = None
 
@@ -167,11 +168,13 @@ def lib():
                      ("ede_se_scale", EdeSeScale), ("ede_resize_bilinear_ac", EdeResize),
                      ("ede_maxpool3x3s2", EdeMaxPool), ("ede_eltwise", EdeEltwise),
                      ("ede_nchw_to_nhwc", EdeLayout), ("ede_nhwc_to_nchw", EdeLayout),
-                     ("ede_upconv_taps", EdeUpConv), ("ede_stem_conv", EdeStem), ("ede_tapsum", EdeTapSum),
+                     ("ede_upconv_taps", EdeUpConv), ("ede_upconv_taps_static", EdeUpConv), ("ede_stem_conv", EdeStem), ("ede_tapsum", EdeTapSum),
                      ("ede_depth_epilogue", EdeDepthEpilogue), ("ede_preprocess_frames", EdePreprocess)):
         f = getattr(L, name)
         f.argtypes = [POINTER(st), c_void_p]
         f.restype = c_int32
+    L.ede_upconv_taps_static_max_bytes.argtypes = []
+    L.ede_upconv_taps_static_max_bytes.restype = c_int64
     L.ede_mesh_from_depth.argtypes = [POINTER(EdeMeshFromDepth), c_void_p]
     L.ede_mesh_from_depth.restype = c_int32
     L.ede_render_workspace_bytes.argtypes = [POINTER(EdeRender)]

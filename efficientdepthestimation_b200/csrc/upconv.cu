@@ -9,6 +9,7 @@
 // the tap-shifted position, sums, applies the folded BatchNorm / ReLU and stores NHWC.  Exact in real
 // arithmetic; fp32 z keeps it at least as accurate as convolving a bf16 upsampled map.
 #include <algorithm>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -290,6 +291,51 @@ extern "C" int ede_upconv_taps(const EdeUpConv* a, void* stream) {
     }
     EDE_LAUNCH_CHECK("upconv_taps_kernel");
     return EDE_OK;
+}
+
+// ---- allocation-free variant of the separable gather: the `rows` workspace lives in a file-scope device array.
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  Every GPU that loads the library holds the
+// array until exit.  The array's name is only a host-side stand-in in host code: the device address is looked up once
+// per device with cudaGetSymbolAddress (that device current) and handed to the existing kernels through EdeUpConv.rows.
+namespace ede {
+constexpr long long UPCONV_STATIC_ROWS_FLOATS = 4LL << 20;                 // 16 MiB
+static __device__ __align__(256) float g_upconv_static_rows[UPCONV_STATIC_ROWS_FLOATS];
+}  // namespace ede
+
+extern "C" int64_t ede_upconv_taps_static_max_bytes(void) { return ede::UPCONV_STATIC_ROWS_FLOATS * (int64_t)sizeof(float); }
+
+extern "C" int ede_upconv_taps_static(const EdeUpConv* a, void* stream) {
+    EDE_REQUIRE(a, "ede_upconv_taps_static: null argument");
+    EDE_REQUIRE(a->n > 0 && a->h > 0 && a->kh > 0 && a->ow > 0 && a->cgrp > 0, "ede_upconv_taps_static: bad shape");
+    const long long need = (long long)a->n * a->h * a->kh * a->ow * a->cgrp;   // floats of rows[n][h][kh][ow][cgrp]
+    EDE_REQUIRE(need <= ede::UPCONV_STATIC_ROWS_FLOATS,
+                "ede_upconv_taps_static: the rows workspace of this shape needs %lld bytes, the static scratch holds %lld "
+                "(use ede_upconv_taps with a caller-provided workspace)",
+                need * (long long)sizeof(float), ede::UPCONV_STATIC_ROWS_FLOATS * (long long)sizeof(float));
+    static float* dev_ptr[64] = {};                                        // per device, looked up once
+    static std::mutex mu;
+    int dev = 0;
+    int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+    if (rc) return rc;
+    EDE_REQUIRE(dev >= 0 && dev < 64, "ede_upconv_taps_static: device ordinal %d out of range", dev);
+    float* rows = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!dev_ptr[dev]) {
+            void* p = nullptr;
+            rc = check_cuda(cudaGetSymbolAddress(&p, ede::g_upconv_static_rows), "cudaGetSymbolAddress(g_upconv_static_rows)");
+            if (rc) return rc;
+            EDE_REQUIRE(p != nullptr, "ede_upconv_taps_static: cudaGetSymbolAddress returned a null address");
+            dev_ptr[dev] = static_cast<float*>(p);
+        }
+        rows = dev_ptr[dev];
+    }
+    // upconv_rows_kernel writes every element of rows[n][h][kh][ow][cgrp] before upconv_cols_kernel reads it (stream
+    // order), so nothing of the previous call's contents has to be cleared.
+    EdeUpConv b = *a;
+    b.rows = rows;
+    return ede_upconv_taps(&b, stream);
 }
 
 extern "C" int ede_tapsum(const EdeTapSum* a, void* stream) {

@@ -196,6 +196,19 @@ typedef struct EdeUpConv {
 } EdeUpConv;
 int ede_upconv_taps(const EdeUpConv* a, void* stream);
 
+/* Allocation-free variant of the separable form of ede_upconv_taps: the `rows` workspace is a file-scope device array
+ * inside the library (a->rows is ignored), so the call needs no cudaMalloc by anyone.
+ * No counterpart in the reference: added for callers that cannot allocate (code
+ *   under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Limit: n*h*kh*ow*cgrp*4 bytes <= ede_upconv_taps_static_max_bytes() (16 MiB, held by every GPU that loads the
+ *   library until the process exits); larger shapes return EDE_E_ARG with the byte counts in ede_last_error().  Needs an
+ *   upsampled map (h < oh) like the separable form.  The first call on a device looks the array's address up
+ *   (cudaGetSymbolAddress, that device current); no call allocates or frees device memory.
+ * All calls share the one array: it keeps the previous call's contents (pass 1 rewrites every element it later reads,
+ *   nothing needs clearing), and two calls that overlap on the GPU (different streams) race on it. */
+int ede_upconv_taps_static(const EdeUpConv* a, void* stream);
+int64_t ede_upconv_taps_static_max_bytes(void);
+
 /* k x k stride-1 convolution to ONE output channel, second half: sum of the per-tap products that ede_conv2d left in z.
  * replaces: the 5x5 conv to a single channel + bias that ends the Hu decoder (R.conv2, ReSIDE/models/modules.py:285,296).
  * z: fp32 NHWC [n,h,w], lane ty*kw+tx = (W[0,:,ty,tx] . x) at that pixel (a 1x1 GEMM with kh*kw output lanes);
