@@ -192,6 +192,131 @@ __global__ void __launch_bounds__(256) upconv_cols_kernel(const EdeUpConv a, flo
     }
 }
 
+
+// ---- one-pass streaming form (no workspace): the two lerps fused.  A thread owns one (output column, 8-lane group)
+// and walks DOWN a band of output rows.  For every tap row ty it keeps the two x-lerped low-resolution rows that
+// bracket the current sample position in registers,
+//   A[ty] = sum_tx inside_x * lerp_x(z[n][y0][.][(ty,tx),c]),   B[ty] = the same for row y0+1,
+// so an output row costs K y-lerps (2 FMAs per lane each).  The map is upsampled (scale_h < 1), so from one output row
+// to the next y0 either stays or moves down by ONE: then B becomes A and only one new row is x-lerped.  All conditions
+// depend on (output row, tap row) only -- uniform over the block.  z is read once from DRAM (neighbouring bands re-read
+// their 2*K boundary rows through L2); the `rows` workspace of the separable form (1.2x the bytes of z for 28x38 ->
+// 114x152) is neither written nor read.
+template <int V> __device__ __forceinline__ void ldz(const float* p, float (&v)[V]) {
+    if constexpr (V == 8) {
+        uint32_t u[8];
+        ldg256(p, u);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(u[j]);
+    } else {
+        const float4 f = *reinterpret_cast<const float4*>(p);
+        v[0] = f.x; v[1] = f.y; v[2] = f.z; v[3] = f.w;
+    }
+}
+template <int K, int V>
+__device__ __forceinline__ void upconv_xlerp(const float* __restrict__ zrow, const int (&off0)[K], const int (&off1)[K],
+                                             const float (&hx)[K], const float (&lx)[K], float (&out)[V]) {
+    float u0[K][V], u1[K][V];
+#pragma unroll
+    for (int tx = 0; tx < K; ++tx) {                          // 2K independent loads in flight
+        ldz<V>(zrow + off0[tx], u0[tx]);
+        ldz<V>(zrow + off1[tx], u1[tx]);
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) out[j] = 0.f;
+#pragma unroll
+    for (int tx = 0; tx < K; ++tx)
+#pragma unroll
+        for (int j = 0; j < V; ++j) out[j] = fmaf(hx[tx], u0[tx][j], fmaf(lx[tx], u1[tx][j], out[j]));
+}
+template <int K>
+__device__ __forceinline__ void upconv_prefetch(const float* zrow, const int (&off0)[K], const int (&off1)[K]) {
+#pragma unroll
+    for (int tx = 0; tx < K; ++tx) {
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(zrow + off0[tx]));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(zrow + off1[tx]));
+    }
+}
+
+template <int K, typename TY, int V, int THREADS, int MINB, bool PF>
+__global__ void __launch_bounds__(THREADS, MINB) upconv_stream_kernel(const EdeUpConv a, float scale_h, float scale_w, int band) {
+    const int ngrp = a.cgrp / V;
+    const int bands = (a.oh + band - 1) / band;
+    const int n = blockIdx.y / bands, oy0 = (blockIdx.y - n * bands) * band;
+    const int oy1 = min(oy0 + band, a.oh);
+    pdl_trigger();
+    const int t = blockIdx.x * THREADS + threadIdx.x;        // (output column, V-lane group)
+    if (t >= a.ow * ngrp) return;
+    const int px = t / ngrp, c = (t - px * ngrp) * V;
+    int off0[K], off1[K];
+    float hx[K], lx[K];
+#pragma unroll
+    for (int tx = 0; tx < K; ++tx) {
+        const int qx = px + tx - a.pl;
+        const bool vx = qx >= 0 && qx < a.ow;                // else: tap column in the zero padding
+        const float sx = scale_w * (vx ? qx : 0);
+        const int x0 = (int)sx, x1 = x0 + (x0 < a.w - 1 ? 1 : 0);
+        const float l = sx - x0;
+        hx[tx] = vx ? 1.f - l : 0.f;
+        lx[tx] = vx ? l : 0.f;
+        off0[tx] = x0 * a.z_cs + tx * a.cgrp;
+        off1[tx] = x1 * a.z_cs + tx * a.cgrp;
+    }
+    float sc[V], sf[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) { sc[j] = a.scale[c + j]; sf[j] = a.shift[c + j]; }
+    const bool activated = c < a.act_c_end;
+    const float* zimg = a.z + (long long)n * a.h * a.w * a.z_cs + a.z_co + c;
+    const int zrow_stride = a.w * a.z_cs;
+    // row base of the output pixel (lane 0 of the view) -- store4 wants the row and the lane separately
+    TY* yout = reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oy0) * a.ow + px) * a.y_cs + a.y_co;
+    float A[K][V], B[K][V];
+    int ya[K];
+#pragma unroll
+    for (int ty = 0; ty < K; ++ty) ya[ty] = -2;
+    pdl_wait();
+    for (int oy = oy0; oy < oy1; ++oy) {
+        float acc[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int ty = 0; ty < K; ++ty) {
+            const int q = oy + ty - a.pt;
+            if (q < 0 || q >= a.oh) continue;                // tap row in the zero padding
+            const float sy = scale_h * q;
+            const int y0 = (int)sy;
+            const float ly = sy - y0, hy = 1.f - ly;
+            if (ya[ty] != y0) {
+                const float* zr = zimg + (long long)y0 * zrow_stride + ty * K * a.cgrp;
+                if (ya[ty] == y0 - 1) {
+#pragma unroll
+                    for (int j = 0; j < V; ++j) A[ty][j] = B[ty][j];
+                } else {
+                    upconv_xlerp<K, V>(zr, off0, off1, hx, lx, A[ty]);
+                }
+                ya[ty] = y0;
+                if (y0 < a.h - 1) {
+                    upconv_xlerp<K, V>(zr + zrow_stride, off0, off1, hx, lx, B[ty]);
+                    if (PF && y0 < a.h - 2) upconv_prefetch<K>(zr + 2 * zrow_stride, off0, off1);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < V; ++j) B[ty][j] = A[ty][j];
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < V; ++j) acc[j] = fmaf(hy, A[ty][j], fmaf(ly, B[ty][j], acc[j]));
+        }
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+            acc[j] = fmaf(acc[j], sc[j], sf[j]);
+            if (activated) acc[j] = apply_act(acc[j], a.act);
+        }
+        if constexpr (V == 8) store8<TY>(yout + c, acc);
+        else store4<TY>(yout, c, acc);
+        yout += (long long)a.ow * a.y_cs;
+    }
+}
+
 }  // namespace ede
 
 namespace ede {
@@ -282,6 +407,28 @@ extern "C" int ede_upconv_taps(const EdeUpConv* a, void* stream) {
             else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(upconv_cols_kernel<3, TY, 2>, g2, dim3(256), 0, st, *a, sh))); }
         }
         EDE_LAUNCH_CHECK("upconv_cols_kernel");
+        return EDE_OK;
+    }
+    static const char* stream_knob = getenv("EDE_UPCONV_STREAM");         // 0: keep the 4-corner gather for rows == NULL
+    if (sh < 1.f && !(stream_knob && stream_knob[0] == '0')) {              // upsampled map: one-pass streaming form
+        static const char* band_knob = getenv("EDE_UPCONV_BAND");
+        const unsigned col_blocks = (unsigned)((a->ow * (a->cgrp >> 3) + 255) / 256);
+        // rows per band: long bands amortise the 2*K rows x-lerped at a band's start, short ones fill the machine;
+        // aim at >= 6 waves of 148 SMs (one 256-thread block each: 240 registers per thread), never below 16 rows
+        int band = band_knob ? atoi(band_knob) : 0;
+        if (band <= 0) {
+            const long long want_blocks = 148LL * 6;
+            long long bands = (want_blocks + (long long)a->n * col_blocks - 1) / ((long long)a->n * col_blocks);
+            bands = std::max(1LL, std::min(bands, (long long)(a->oh + 15) / 16));
+            band = (int)((a->oh + bands - 1) / bands);
+        }
+        band = std::max(1, std::min(band, (int)a->oh));
+        const long long gy = (long long)a->n * ((a->oh + band - 1) / band);
+        EDE_REQUIRE(gy <= 65535 && col_blocks < 0x7fffffffu, "ede_upconv_taps: map too large");
+        const dim3 gs(col_blocks, (unsigned)gy);
+        if (a->kh == 5) { EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(upconv_stream_kernel<5, TY, 8, 256, 1, true>, gs, dim3(256), 0, st, *a, sh, sw, band))); }
+        else { EDE_DISPATCH_DTYPE(a->y_dtype, TY, ((void)launch_pdl(upconv_stream_kernel<3, TY, 8, 256, 2, false>, gs, dim3(256), 0, st, *a, sh, sw, band))); }
+        EDE_LAUNCH_CHECK("upconv_stream_kernel");
         return EDE_OK;
     }
     if (a->kh == 5) {

@@ -541,12 +541,16 @@ class Graph:
         self.count_ref_flops = prev
         out = View(self.new_buf(x.n, oh, ow, cgrp, self.decoder_dtype if self.act_dtype != A.F32 else A.F32), 0, out_lanes)
         scale, shift = self._dev(torch.cat(scales)), self._dev(torch.cat(shifts))
-        # fp32 workspace of the separable gather: [n][h][k][ow][cgrp] (x-lerp of every tap on the low-res rows)
-        rows = self.new_buf(x.n, x.h, k * ow, cgrp, A.F32)
+        # fp32 workspace of the separable two-pass gather: [n][h][k][ow][cgrp] (x-lerp of every tap on the low-res rows).
+        # EDE_UPCONV_ROWS=0: the workspace-free one-pass streaming kernel instead (measured 20 % slower on B200: 240
+        # registers per thread leave 8 warps per SM to hide the load latency; profiles/r02_upconv_stream.md)
+        bufs = [("z", z.buf), ("y", out.buf)]
+        if os.environ.get("EDE_UPCONV_ROWS", "1") != "0" and x.h < oh:
+            bufs.append(("rows", self.new_buf(x.n, x.h, k * ow, cgrp, A.F32)))
         st = A.EdeUpConv(z=None, y=None, scale=None, shift=None, rows=None, n=x.n, h=x.h, w=x.w,
                          z_cs=z.buf.cs, z_co=z.co, oh=oh, ow=ow, cgrp=cgrp, y_cs=out.buf.cs, y_co=out.co,
                          y_dtype=out.dtype, kh=k, kw=k, pt=pad[0], pl=pad[1], act=act, act_c_end=act_end)
-        self._add(A.OP_UPCONV, st, [("z", z.buf), ("y", out.buf), ("rows", rows)], tag + ".taps",
+        self._add(A.OP_UPCONV, st, bufs, tag + ".taps",
                   [("scale", scale), ("shift", shift)])
         self.exec_flops += 2.0 * x.n * oh * ow * cgrp * k * k * 4
         self.conv_exec_flops += 2.0 * x.n * oh * ow * cgrp * k * k * 4

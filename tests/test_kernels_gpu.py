@@ -487,3 +487,28 @@ def test_prepack_conv_behind_the_c_abi(cuda, lib, cout, cin, k, passes, pack_g, 
     assert rt.cudaMemcpy(C.c_void_p(back.data_ptr()), C.c_void_p(hc.w_umma), C.c_size_t(b4[0]), 3) == 0   # D2D
     assert torch.equal(back.cpu().view(torch.int16), exp_umma.reshape(-1).view(torch.int16))
     assert lib.ede_free(h) == 0
+
+
+@pytest.mark.parametrize("shape", [(2, 14, 19, 57, 76, 32, 5), (1, 7, 9, 114, 152, 32, 5), (2, 8, 10, 33, 41, 16, 3),
+                                   (1, 57, 76, 114, 152, 32, 5)])
+def test_upconv_streaming_form_matches_the_separable_form(cuda, lib, shape):
+    """ede_upconv_taps without a workspace (one-pass streaming kernel: x-lerped rows kept in registers while a thread
+    walks down a band of output rows) == the two-pass form through the `rows` workspace; fp32 outputs, same
+    arithmetic up to the order of the tap-row sum."""
+    n, h, w, oh, ow, cgrp, k = shape
+    g = torch.Generator().manual_seed(h * 131 + ow)
+    z_cs = k * k * cgrp
+    z = torch.randn(n, h, w, z_cs, generator=g).to(cuda)
+    scale = (0.5 + torch.rand(cgrp, generator=g)).to(cuda)
+    shift = (0.2 * torch.randn(cgrp, generator=g)).to(cuda)
+    ys = [torch.full((n, oh, ow, cgrp), float("nan"), device=cuda) for _ in range(2)]
+    rows = torch.empty(n * h * k * ow * cgrp, device=cuda)
+    st = torch.cuda.current_stream().cuda_stream
+    for y, r in ((ys[0], rows.data_ptr()), (ys[1], None)):
+        a = A.EdeUpConv(z=z.data_ptr(), y=y.data_ptr(), scale=scale.data_ptr(), shift=shift.data_ptr(), rows=r,
+                        n=n, h=h, w=w, z_cs=z_cs, z_co=0, oh=oh, ow=ow, cgrp=cgrp, y_cs=cgrp, y_co=0, y_dtype=A.F32,
+                        kh=k, kw=k, pt=k // 2, pl=k // 2, act=A.ACT_RELU, act_c_end=cgrp // 2)
+        assert lib.ede_upconv_taps(C.byref(a), st) == 0, lib.ede_last_error()
+    torch.cuda.synchronize()
+    assert not torch.isnan(ys[1]).any()
+    assert torch.allclose(ys[0], ys[1], rtol=1e-5, atol=2e-5), float((ys[0] - ys[1]).abs().max())
