@@ -80,6 +80,7 @@ __device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sy
 
 // ------------------------------------------------------------------ kernel parameters
 constexpr int MAX_STAGES = 12;
+constexpr int MAX_ACC_STAGES = 4;           // TMEM accumulator stages of conv_npack_kernel (2 everywhere else)
 constexpr int EPI_WARPS = 8;                 // two warps per TMEM lane quarter, interleaved over 16-column chunks
 constexpr int EPI_THREADS = 32 * EPI_WARPS;
 constexpr int NUM_THREADS = 64 + EPI_THREADS;   // warp 0 TMA, warp 1 MMA, warps 2.. epilogue
@@ -94,6 +95,12 @@ struct alignas(64) UmmaParams {
     int pack_g, kw_steps, n_cols;            // pack_g taps share one MMA (M rows = [tap j][128/pack_g channels]); kw_steps = ceil(kw/pack_g); n_cols = UMMA N of the swapped form
     int a_stages, b_stages, a_stage_bytes, b_stage_bytes, b_tx_bytes;
     int b_group;          // taps per weight stage (one TMA box, one wait, one commit); > 1 only swapped + resident
+    // ---- N-packed pixels-on-M form (conv_npack_kernel)
+    int npack, slot;      // npack = G > 0: the G taps of a kernel row sit on the N axis (column j*slot + c), smem pixel
+                          // pitch 32 = one epilogue warp per window row; the epilogue adds the slots lane-shifted
+    int b_resident;       // 1: the whole weight set sits in the b_stages (loaded once, never released)
+    int acc_stages;       // accumulator stages in TMEM (acc_stages * acc_cols <= 512)
+    int tiles_per_cta;    // a CTA walks that many CONSECUTIVE tiles (coordinates advance without divisions)
     int w_img_taps;       // > 0: the weight tensor map holds one set of that many taps per image (SE gate folded in)
     int layout_type, sbo_bytes, tmem_cols, flat;
     uint32_t idesc;
@@ -141,6 +148,16 @@ __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) 
     t.ow0 = tw * tile_w_pix;
     t.oh0 = th * p.bh;
     return t;
+}
+
+// the tile after `t` in raster order (conv_npack_kernel: consecutive tiles per CTA, one n-tile, resident pixel tile)
+__device__ __forceinline__ void next_tile_contig(const UmmaParams& p, TileCoord& t) {
+    t.ow0 += p.bw;
+    if (t.ow0 >= p.tiles_w * p.bw) {
+        t.ow0 = 0;
+        t.oh0 += p.bh;
+        if (t.oh0 >= p.tiles_h * p.bh) { t.oh0 = 0; ++t.img; }
+    }
 }
 
 // one 8-channel group of the epilogue: folded BN, residual, activation, typed store.  ACT and RES are compile
@@ -716,6 +733,238 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
     }
 }
 
+
+// =====================================================================================================================
+// conv_npack_kernel -- narrow stride-1 k x k convolutions (Cout <= 80, 2 <= kw <= 5) in the "N-packed pixels-on-M" form.
+//
+// GEMM orientation: M = 128 window positions of the resident halo tile, N = G * slot columns where column j*slot + c
+// holds kernel-row tap slot j of output channel c (slot = cout_p16, G = min(kw, 256 / slot) taps of a kernel row per
+// MMA), K = input channels.  One tcgen05.mma costs max(97, N/2) cycles whatever N <= 192 is, so a kernel row costs
+// ceil(kw / G) MMAs per 128 positions instead of kw (3x3 32->16: 6 instead of 18 per m-tile).  The partial sum of tap
+// slot j for output position q sits in accumulator row q + j: the smem pixel pitch is fixed at 32 so that one epilogue
+// warp holds exactly one window row (lanes >= bw = 33 - kw are halo columns) and the slot sum is a warp shuffle -- no
+// shared-memory staging, no barrier.  The whole weight set is loaded ONCE per CTA and stays resident (the picker only
+// offers the form when it fits); a CTA walks CONSECUTIVE tiles, so coordinates advance without divisions and halo
+// rows of neighbouring tiles meet in L2.  Roles as in conv_umma_kernel: warp 0 = TMA producer (pixel tiles only after
+// the first tile), warp 1 = MMA issuer, warps 2-9 = epilogue, two per TMEM lane quarter, which alternate over the
+// (m-tile, 16-channel chunk) units of a tile.  Up to four TMEM accumulator stages.
+// Measured (ENB0-HU batch 64, tools/cta_timeline.py): these warps run alone on their schedulers, so every dependent
+// instruction costs its full latency -- the epilogue keeps G compile-time (a run-time G put every SHFL -> FADD pair
+// behind its own uniform branch: one 2200-cycle dependent chain per unit) and carries no divisions.
+template <typename TY, int ACT, bool RES, int G>
+__device__ __forceinline__ void npack_tile_epilogue(const UmmaParams& p, uint32_t t_base, int half, int quarter, int lane,
+                                                    const TileCoord& t, const float* s_scale, const float* s_shift) {
+    const int nch = p.slot >> 4;
+    const bool col_ok = lane < p.bw && t.ow0 + lane < p.ow;
+    int oh = t.oh0 + quarter;
+    long long pix = ((long long)t.img * p.oh + oh) * p.ow + t.ow0 + lane;
+    const long long pix_step = 4ll * p.ow;
+    uint32_t t_row = t_base;
+    int par = 0;                                             // (m * nch + ci) % 2: which warp of the pair owns the unit
+    for (int m = 0; m < p.m_tiles; ++m, t_row += (uint32_t)p.n_pad, pix += pix_step, oh += 4) {
+        const bool valid = col_ok && oh < p.oh;
+        TY* const yrow = reinterpret_cast<TY*>(p.y) + pix * p.y_cs + p.y_co;
+        const TY* const rrow = RES ? reinterpret_cast<const TY*>(p.res) + pix * p.res_cs + p.res_co : nullptr;
+        for (int ci = 0; ci < nch; ++ci, par ^= 1) {
+            if (par != half) continue;
+            uint32_t acc[G][16];
+            const uint32_t col = t_row + (uint32_t)(ci << 4);
+#pragma unroll
+            for (int j = 0; j < G; ++j) tc_ld16(col + (uint32_t)(j * p.slot), acc[j]);      // all slots in flight, ONE wait
+            tc_ld_wait();
+            float v[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                float x = __uint_as_float(acc[0][k]);
+#pragma unroll
+                for (int j = 1; j < G; ++j) x += __shfl_down_sync(0xffffffffu, __uint_as_float(acc[j][k]), j);
+                v[k] = x;
+            }
+            if (!valid) continue;
+            const int c = ci << 4;
+            uint32_t u[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) u[k] = __float_as_uint(v[k]);
+            if (c < p.cout_p) epilogue_store8<TY, ACT, RES>(p, yrow, rrow, c, c, u, s_scale, s_shift);
+            if (c + 8 < p.cout_p) epilogue_store8<TY, ACT, RES>(p, yrow, rrow, c + 8, c + 8, u + 8, s_scale, s_shift);
+        }
+    }
+}
+
+template <typename TY, int ACT, bool RES>
+__global__ void __launch_bounds__(NUM_THREADS, 1) conv_npack_kernel(const __grid_constant__ UmmaParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t a_base = smem_base;
+    const uint32_t b_base = a_base + (uint32_t)p.a_stages * p.a_stage_bytes;
+    const uint32_t bar_base = b_base + (uint32_t)p.b_stages * p.b_stage_bytes;
+    // barriers: a_full[12] a_empty[12] b_full[12] acc_full[4] acc_empty[4], TMEM base slot; scale/shift at +512
+    auto a_full = [&](int s) { return bar_base + 8u * s; };
+    auto a_empty = [&](int s) { return bar_base + 8u * (MAX_STAGES + s); };
+    auto b_full = [&](int s) { return bar_base + 8u * (2 * MAX_STAGES + s); };
+    auto acc_full = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + s); };
+    auto acc_empty = [&](int s) { return bar_base + 8u * (3 * MAX_STAGES + MAX_ACC_STAGES + s); };
+    const uint32_t tmem_slot = bar_base + 8u * (3 * MAX_STAGES + 2 * MAX_ACC_STAGES);
+    float* const s_scale = reinterpret_cast<float*>(smem_raw + (bar_base - smem_u32(smem_raw)) + 512);
+    float* const s_shift = s_scale + 256;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int sp_taps = p.kh * p.kw_steps;        // (kernel row, tap group) steps of one weight pass
+    const int taps = sp_taps * p.w_passes;
+    pdl_trigger();
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < MAX_STAGES; ++s) { mbar_init(a_full(s), 1); mbar_init(a_empty(s), 1); mbar_init(b_full(s), 1); }
+        for (int s = 0; s < MAX_ACC_STAGES; ++s) { mbar_init(acc_full(s), 1); mbar_init(acc_empty(s), EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                     "r"((uint32_t)p.tmem_cols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {
+        // the shifted UMMA windows read past the TMA box into the tail of the stage (never written by TMA): those rows
+        // only meet halo positions or zero weight rows, but 0 * stale NaN is NaN -- zeroed once
+        const int tail0 = p.box_bytes & ~15, tail_n = (p.a_stage_bytes - tail0) >> 4;
+        for (int st = 0; st < p.a_stages; ++st) {
+            uint8_t* base = smem_raw + (a_base - smem_u32(smem_raw)) + (size_t)st * p.a_stage_bytes + tail0;
+            for (int i = threadIdx.x; i < tail_n; i += NUM_THREADS) reinterpret_cast<uint4*>(base)[i] = make_uint4(0, 0, 0, 0);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    for (int e = threadIdx.x; e < 256; e += NUM_THREADS) {   // folded-BN vectors: one n-tile, loaded once (weights, not
+        const bool in = e < p.cout_p;                        // activations: no dependency on the previous kernel)
+        s_scale[e] = in ? __ldg(p.scale + e) : 0.f;
+        s_shift[e] = in ? __ldg(p.shift + e) : 0.f;
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_addr;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_addr) : "r"(tmem_slot) : "memory");
+    const int tile_first = (int)blockIdx.x * p.tiles_per_cta;
+    const int tile_end = min(p.total_tiles, tile_first + p.tiles_per_cta);
+    const int n_chunks = p.n_chunks;
+
+    if (warp == 0) {
+        // ===================== TMA producer (one thread): the weight set once, then one halo tile per (tile, chunk)
+        if (lane == 0 && tile_first < tile_end) {
+            const int ck = p.ck_bytes >> 1;
+            const uint32_t b_tx = (uint32_t)(p.b_tx_bytes * p.b_group);
+            for (int chunk = 0; chunk < n_chunks; ++chunk) {                  // weights do not depend on the previous kernel
+                mbar_expect_tx(b_full(chunk), b_tx);
+                tma_load_3d(b_base + chunk * (uint32_t)p.b_stage_bytes, &p.tm_b, b_full(chunk), chunk * ck, 0, 0);
+            }
+            pdl_wait();                                                       // activations of the previous kernel
+            int a_st = 0, a_ph = 0;
+            TileCoord t = decode_tile(p, tile_first);
+            for (int tile = tile_first; tile < tile_end; ++tile) {
+                for (int chunk = 0; chunk < n_chunks; ++chunk) {
+                    mbar_wait(a_empty(a_st), a_ph ^ 1);
+                    mbar_expect_tx(a_full(a_st), (uint32_t)p.box_bytes);
+                    tma_load_4d(a_base + a_st * (uint32_t)p.a_stage_bytes, &p.tm_a, a_full(a_st), chunk * ck, t.ow0 - p.pl,
+                                t.oh0 - p.pt, t.img);
+                    if (++a_st == p.a_stages) { a_st = 0; a_ph ^= 1; }
+                }
+                next_tile_contig(p, t);
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer: the whole warp walks the loop, one elected lane issues
+        const bool leader = elect_one();
+        const int m_tiles = p.m_tiles, n_pad = p.n_pad, kws = p.kw_steps, a_stages = p.a_stages, acc_stages = p.acc_stages;
+        const uint32_t ck16 = (uint32_t)p.ck_bytes >> 4;
+        const uint32_t a_stage16 = (uint32_t)p.a_stage_bytes >> 4, b_stage16 = (uint32_t)p.b_stage_bytes >> 4;
+        const uint32_t m_step16 = 128u * ck16;                       // 128 window positions = 4 rows of pitch 32
+        const int ksteps = p.ck_bytes >> 5;
+        const uint32_t idesc = p.idesc;
+        const uint64_t dconst = smem_desc_const(p);
+        const uint32_t desc_hi = (uint32_t)(dconst >> 32);
+        const uint32_t a_base16 = (uint32_t)dconst + (a_base >> 4), b_base16 = (uint32_t)dconst + (b_base >> 4);
+        const uint32_t kx_step16 = (uint32_t)p.pack_g * ck16;                          // next tap group of a kernel row
+        const uint32_t ky_step16 = (uint32_t)(p.pitch - kws * p.pack_g) * ck16;        // wrap to the next kernel row
+        const uint32_t tap16 = (uint32_t)p.b_tx_bytes >> 4;
+        int a_st = 0, a_ph = 0, acc_st = 0, acc_ph = 0;
+        uint32_t a_cur = a_base16;
+        if (tile_first < tile_end)
+            for (int chunk = 0; chunk < n_chunks; ++chunk) mbar_wait(b_full(chunk), 0);   // resident from here on
+        tc_fence_after();
+        for (int tile = tile_first; tile < tile_end; ++tile) {
+            mbar_wait(acc_empty(acc_st), acc_ph ^ 1);
+            tc_fence_after();
+            const uint32_t d_base = tmem_addr + (uint32_t)(acc_st * p.acc_cols);
+            uint32_t accum = 0;
+            for (int chunk = 0; chunk < n_chunks; ++chunk) {
+                const int ks = min(ksteps, (p.k_bytes - chunk * p.ck_bytes + 31) >> 5);   // K steps that hold real channels
+                mbar_wait(a_full(a_st), a_ph);
+                tc_fence_after();
+                uint32_t bt = b_base16 + (uint32_t)chunk * b_stage16, shift16 = 0;
+                int kx = 0, tap_in_pass = 0;
+                for (int tap = 0; tap < taps; ++tap) {
+                    if (leader) {
+                        uint32_t am = a_cur + shift16, dm = d_base;
+                        for (int m = 0; m < m_tiles; ++m) {
+                            tc_mma_bf16_w(dm, am, bt, desc_hi, idesc, accum);
+                            if (ks > 1) tc_mma_bf16_w(dm, am + 2u, bt + 2u, desc_hi, idesc, 1u);
+                            if (ks > 2) tc_mma_bf16_w(dm, am + 4u, bt + 4u, desc_hi, idesc, 1u);
+                            if (ks > 3) tc_mma_bf16_w(dm, am + 6u, bt + 6u, desc_hi, idesc, 1u);
+                            am += m_step16;
+                            dm += (uint32_t)n_pad;
+                        }
+                    }
+                    accum = 1;
+                    bt += tap16;
+                    shift16 += kx_step16;
+                    if (++kx == kws) { kx = 0; shift16 += ky_step16; }
+                    if (++tap_in_pass == sp_taps) { tap_in_pass = 0; shift16 = 0; kx = 0; }   // the w_lo pass restarts
+                }
+                if (leader) tc_commit(a_empty(a_st));
+                __syncwarp();
+                a_cur += a_stage16;
+                if (++a_st == a_stages) { a_st = 0; a_ph ^= 1; a_cur = a_base16; }
+            }
+            if (leader) tc_commit(acc_full(acc_st));
+            __syncwarp();
+            if (++acc_st == acc_stages) { acc_st = 0; acc_ph ^= 1; }
+        }
+    } else {
+        // ===================== epilogue (warps 2..9): TMEM -> slot sums -> BN / residual / activation -> NHWC stores
+        const int quarter = warp & 3;                 // TMEM lanes [32q, 32q+32) are visible to warp%4 == q
+        const int half = (warp - 2) >> 2;
+        const int acc_stages = p.acc_stages;
+        int acc_st = 0, acc_ph = 0;
+        pdl_wait();                                   // residual reads and the stores below touch the arena
+        if (tile_first < tile_end) {
+            TileCoord t = decode_tile(p, tile_first);
+            for (int tile = tile_first; tile < tile_end; ++tile) {
+                mbar_wait(acc_full(acc_st), acc_ph);
+                tc_fence_after();
+                const uint32_t t_base = tmem_addr + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc_st * p.acc_cols);
+                if (p.npack == 5) npack_tile_epilogue<TY, ACT, RES, 5>(p, t_base, half, quarter, lane, t, s_scale, s_shift);
+                else if (p.npack == 3) npack_tile_epilogue<TY, ACT, RES, 3>(p, t_base, half, quarter, lane, t, s_scale, s_shift);
+                else if (p.npack == 4) npack_tile_epilogue<TY, ACT, RES, 4>(p, t_base, half, quarter, lane, t, s_scale, s_shift);
+                else npack_tile_epilogue<TY, ACT, RES, 2>(p, t_base, half, quarter, lane, t, s_scale, s_shift);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(acc_empty(acc_st));
+                if (++acc_st == acc_stages) { acc_st = 0; acc_ph ^= 1; }
+                next_tile_contig(p, t);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_addr),
+                     "r"((uint32_t)p.tmem_cols)
+                     : "memory");
+    }
+}
+
 // ------------------------------------------------------------------ host side
 static int env_int(const char* name, int dflt) {
     const char* s = getenv(name);
@@ -734,7 +983,10 @@ static bool umma_eligible(const EdeConv& a) {
     if ((a.x_cs | a.x_co | a.y_cs | a.y_co | a.cin_p | a.cout_p) & 7) return false;
     if (a.res && ((a.res_cs | a.res_co) & 7)) return false;
     if (a.w_umma_cin_p & 7) return false;
-    if (a.w_pack_g > 1 && (a.w_umma_cout_p != 128 || (a.w_pack_g != 2 && a.w_pack_g != 4))) return false;
+    if (a.w_pack_g > 1 && (a.w_pack_g & EDE_PACK_N)) {      // taps on the N axis: G slots of cout_p16 rows
+        const int G = a.w_pack_g & 15;
+        if (G < 2 || G > 5 || a.w_umma_cout_p != G * round_up(a.cout_p, 16) || a.w_umma_cout_p > 256) return false;
+    } else if (a.w_pack_g > 1 && (a.w_umma_cout_p != 128 || (a.w_pack_g != 2 && a.w_pack_g != 4))) return false;
     return true;
 }
 
@@ -782,6 +1034,16 @@ static int group_want(double mma_clk_per_kstep, int cin_p, int ck, int force_gro
     const double stage_clk = std::max(1.0, tail * mma_clk_per_kstep);
     const int t = std::max(1, std::min(6, (int)std::ceil(target_clk / stage_clk - 0.2)));
     return t == 1 && stage_clk < pair_below_clk ? 2 : t;
+}
+
+// TMEM accumulator stages: two, so that the epilogue of tile i overlaps the MMAs of tile i+1.  The N-packed form has
+// tiles of 1..3 m-tiles whose issue -> MMA -> wake-up -> epilogue -> release round trip (5-8k cycles, tools/cta_timeline.py)
+// is several times the MMA time of a tile: it takes as many stages as fit (up to 4).
+static int umma_acc_stages(const EdeUmmaCfg& c) {
+    if (c.swap || !(c.pack_g & EDE_PACK_N)) return 2;
+    static const int forced = env_int("EDE_UMMA_ACC_STAGES", 0);
+    const int fit = std::min(MAX_ACC_STAGES, 512 / std::max(1, c.m_tiles * c.n_pad));
+    return std::max(2, forced > 0 ? std::min(forced, fit) : fit);
 }
 
 static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
@@ -923,7 +1185,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
         for (int gi = 0; gi < 3; ++gi) {
             const int G = gs[gi];
             if (G > 1 && (a.cout_p > 128 / G || a.kw < 2 || a.sh != 1 || is_1x1)) continue;
-            if (a.w_pack_g >= 0 && std::max(1, a.w_pack_g) != G) continue;      // weights are already packed for one G
+            if (a.w_pack_g >= 0 && std::max(1, a.w_pack_g) != G) continue;      // weights are already packed for one G (or on N)
             if (force_pack >= 0 && a.w_pack_g < 0 && std::max(1, force_pack) != G) continue;
             const int kws = ceil_div(a.kw, G);
             const int steps = a.kh * kws * a.w_passes;
@@ -1010,11 +1272,69 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
           }
         }
     }
+    // ---- N-packed pixels-on-M candidates (narrow stride-1 k x k convs): the G taps of a kernel row sit side by side on
+    // the UMMA N axis (column j*slot + c, slot = cout_p16), so a kernel row costs ceil(kw/G) MMAs of max(97, N/2) cycles
+    // per 128 window positions instead of kw.  The smem pixel pitch is 32 -- one warp of the epilogue per window row -- so
+    // the slot sums are warp shuffles (epilogue_npack).  Offered when the whole weight set stays resident in shared
+    // memory: with 112..120 useful pixels per m-tile, re-streaming the weights per tile would bind on TMA ingest.
+    const int force_npack = env_int("EDE_UMMA_NPACK", -1);
+    if (a.sh == 1 && a.kh * a.kw >= 9 && a.kw >= 2 && a.kw <= 5 && !is_1x1 && force_npack != 0 && force_mode != 1 &&
+        (a.w_pack_g < 0 || (a.w_pack_g > 1 && (a.w_pack_g & EDE_PACK_N))) && a.w_per_image <= 0) {
+        if (force_npack == 1) best_time = 1e300;
+        const int slot = n16;
+        int G = std::min(a.kw, 256 / std::max(16, slot));
+        if (a.w_pack_g > 1) G = a.w_pack_g & 15;
+        const int n_pad = G * slot;
+        const int kws = ceil_div(a.kw, std::max(1, G));
+        const int steps = a.kh * kws * a.w_passes;
+        const int bw = 32 - (a.kw - 1);
+        for (int cki = 0; cki < 2 && G >= 2 && n_pad <= 256; ++cki) {
+            const int ck = cks[cki];
+            if (force_ck && force_ck != ck) continue;
+            if (!force_ck && ck == 32 && round_up(a.cin_p, 32) >= round_up(a.cin_p, 64)) continue;
+            const int ck_bytes = ck * 2, n_chunks = ceil_div(a.cin_p, ck);
+            const int w_chunk_bytes = steps * n_pad * ck_bytes;              // one stage = all taps of a channel chunk
+            if (n_chunks > MAX_STAGES || steps > 256 || n_chunks * w_chunk_bytes > 128 * 1024) continue;
+            const double t_mma = mma_cycles(ck_bytes, n_pad) * 1.15;
+            const int force_T = env_int("EDE_UMMA_NPACK_T", 0);
+            for (int T = 1; T <= 256 / n_pad && T <= 8; ++T) {
+                if (force_T && T != force_T && force_T <= 256 / n_pad) continue;
+                const int bh = 4 * T, box_rows = bh + a.kh - 1;
+                const int rows_alloc = std::max(box_rows * 32, T * 128 + (a.kh - 1) * 32 + kws * G);
+                const int a_bytes = round_up(rows_alloc * ck_bytes, 1024);
+                const int a_stages = std::min(6, (SMEM_BUDGET - n_chunks * w_chunk_bytes) / a_bytes);
+                if (a_stages < 2) continue;
+                EdeUmmaCfg cand{};
+                cand.a_mode = 0; cand.bh = bh; cand.bw = bw; cand.pitch = 32; cand.box_rows = box_rows;
+                cand.m_tiles = T; cand.a_stages = a_stages; cand.b_stages = n_chunks; cand.a_stage_bytes = a_bytes;
+                cand.b_stage_bytes = w_chunk_bytes;
+                cand.tiles_w = ceil_div(OW, bw); cand.tiles_h = ceil_div(OH, bh);
+                cand.useful_frac = (double)OH * OW / ((double)cand.tiles_w * cand.tiles_h * T * 128);
+                const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img;
+                const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
+                const double mma = (double)steps * T * ks_total * t_mma;
+                const double mem = (double)n_chunks * box_rows * 32 * ck_bytes / L2_BYTES_PER_CLK_PER_SM;
+                // per (m-tile, 16-channel chunk) unit: G tcgen05.ld + 16 (G-1) shuffles + BN / activation / stores; two
+                // warps per lane quarter share the units
+                const double epi = std::ceil(T * (slot / 16) / 2.0) * (260.0 + 90.0 * G) + 300.0;
+                const double t = rounds * (std::max(std::max(mma, mem), epi) + 400.0) + 4000.0;
+                if (t < best_time) {
+                    best_time = t;
+                    best = cand;
+                    best.swap = 0;
+                    best.pack_g = EDE_PACK_N | G;
+                    best.ck = ck; best.swizzle = ck_bytes; best.n_pad = n_pad; best.n_tiles = 1;
+                    best.useful_frac = cand.useful_frac * ((double)a.cin_p / (ks_total * 16)) *
+                                       ((double)a.cout_p * a.kw / ((double)n_pad * kws));
+                }
+            }
+        }
+    }
     if (best.m_tiles == 0) return;
     c = best;
     c.eligible = 1;
     if (c.pack_g < 1) c.pack_g = 1;
-    c.tmem_cols = c.swap ? 512 : pow2_cols(2 * c.m_tiles * c.n_pad);
+    c.tmem_cols = c.swap ? 512 : pow2_cols(umma_acc_stages(c) * c.m_tiles * c.n_pad);
     c.smem_bytes = c.a_stages * c.a_stage_bytes + c.b_stages * c.b_stage_bytes + SMEM_EXTRA;
     c.flat = is_1x1;
 }
@@ -1036,6 +1356,20 @@ static int launch_variant(const UmmaParams& p, int n_cta, int smem, int dev, cud
     }
     return check_cuda(launch_pdl(conv_umma_kernel<TY, ACT, RES>, dim3(n_cta), dim3(NUM_THREADS), (size_t)smem, st, p),
                       "launch(conv_umma_kernel)");
+}
+
+template <typename TY, int ACT, bool RES>
+static int launch_variant_npack(const UmmaParams& p, int n_cta, int smem, int dev, cudaStream_t st) {
+    static bool attr_set[64] = {};
+    if (!attr_set[dev]) {
+        int rc = check_cuda(cudaFuncSetAttribute(conv_npack_kernel<TY, ACT, RES>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024),
+                            "cudaFuncSetAttribute(conv_npack_kernel)");
+        if (rc) return rc;
+        attr_set[dev] = true;
+    }
+    return check_cuda(launch_pdl(conv_npack_kernel<TY, ACT, RES>, dim3(n_cta), dim3(NUM_THREADS), (size_t)smem, st, p),
+                      "launch(conv_npack_kernel)");
 }
 
 // Everything a launch needs, derived once per distinct EdeConv (ede_conv2d keeps these in a small cache keyed by
@@ -1091,12 +1425,13 @@ static int conv_umma_build(const EdeConv& a, const EdeUmmaCfg& c, ConvLaunch& L)
                               (cuuint64_t)(a.kh * a.kw * a.w_passes)};
         cuuint64_t strides[2] = {(cuuint64_t)a.w_umma_cin_p * 2, (cuuint64_t)a.w_umma_cin_p * 2 * a.w_umma_cout_p};
         const int w_rows_box = c.swap ? (c.pack_g > 1 ? 128 : std::min(128, round_up(a.cout_p, 8))) : c.n_pad;
+        const int taps_per_mma = (c.pack_g & EDE_PACK_N) ? (c.pack_g & 15) : std::max(1, c.pack_g);
         // taps per weight stage: the stage size the tile picker chose, in units of one tap's box
         const int b_group = (c.a_mode == 0 && (w_rows_box * c.ck * 2) % 1024 == 0)
                                 ? std::max(1, c.b_stage_bytes / (w_rows_box * c.ck * 2)) : 1;
         p.b_group = b_group;
         cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)w_rows_box, (cuuint32_t)b_group};
-        dims[2] = (cuuint64_t)(a.kh * ceil_div(a.kw, c.pack_g) * a.w_passes);
+        dims[2] = (cuuint64_t)(a.kh * ceil_div(a.kw, taps_per_mma) * a.w_passes);
         if (a.w_per_image > 0) {
             if (a.w_per_image != (int)dims[2]) { set_error("ede_conv2d: w_per_image must equal the taps of one weight set (%d)", (int)dims[2]); return EDE_E_ARG; }
             p.w_img_taps = a.w_per_image;
@@ -1118,6 +1453,7 @@ static int conv_umma_build(const EdeConv& a, const EdeUmmaCfg& c, ConvLaunch& L)
     p.n_tiles = c.n_tiles;
     p.total_tiles = c.tiles_w * c.tiles_h * p.n_img * c.n_tiles;
     p.acc_cols = c.swap ? 256 : c.m_tiles * c.n_pad;
+    p.acc_stages = umma_acc_stages(c);
     p.a_mode = c.a_mode; p.ck_bytes = c.ck * 2; p.k_bytes = a.cin_p * 2; p.n_chunks = ceil_div(a.cin_p, c.ck);
     p.w_passes = a.w_passes;
     p.kh = a.kh; p.kw = a.kw; p.sh = a.sh; p.sw = a.sw; p.pt = a.pt; p.pl = a.pl;
@@ -1129,7 +1465,12 @@ static int conv_umma_build(const EdeConv& a, const EdeUmmaCfg& c, ConvLaunch& L)
     p.sbo_bytes = 8 * c.ck * 2;
     p.tmem_cols = c.tmem_cols;
     p.flat = c.flat;
-    p.pack_g = c.pack_g; p.kw_steps = ceil_div(a.kw, c.pack_g); p.n_cols = c.swap ? (c.pack_g > 1 ? 240 : 256) : c.n_pad;
+    const bool on_n = (c.pack_g & EDE_PACK_N) != 0;
+    p.pack_g = on_n ? (c.pack_g & 15) : c.pack_g;
+    p.npack = on_n ? p.pack_g : 0;
+    p.slot = on_n ? c.n_pad / p.pack_g : 0;
+    p.b_resident = on_n ? 1 : 0;
+    p.kw_steps = ceil_div(a.kw, p.pack_g); p.n_cols = c.swap ? (c.pack_g > 1 ? 240 : 256) : c.n_pad;
     p.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.n_cols >> 3) << 17) | ((128u >> 4) << 24);
     p.swap = c.swap;
     p.y = a.y; p.res = a.res; p.scale = a.scale; p.shift = a.shift;
@@ -1148,6 +1489,7 @@ static int conv_umma_build(const EdeConv& a, const EdeUmmaCfg& c, ConvLaunch& L)
     // persistent grid: one CTA per SM (the dynamic smem request is kept above half an SM so that two CTAs
     // can never share one SM and fight over the 512 TMEM columns)
     L.n_cta = std::min(p.total_tiles, std::max(1, sm_count[dev]));
+    p.tiles_per_cta = p.npack ? ceil_div(p.total_tiles, L.n_cta) : 0;
     L.smem = std::max(c.smem_bytes, 120 * 1024);
     return EDE_OK;
 }
@@ -1170,7 +1512,8 @@ static int conv_umma_launch(const EdeConv& a, ConvLaunch& L, cudaStream_t st) {
     }
     // one kernel instantiation per (output dtype, activation, residual): the epilogue has no per-element branches
     int rc = EDE_OK;
-#define EDE_UMMA_LAUNCH(TY, ACT, RES) rc = launch_variant<TY, ACT, RES>(p, n_cta, smem, dev, st)
+#define EDE_UMMA_LAUNCH(TY, ACT, RES) \
+    rc = p.npack ? launch_variant_npack<TY, ACT, RES>(p, n_cta, smem, dev, st) : launch_variant<TY, ACT, RES>(p, n_cta, smem, dev, st)
 #define EDE_UMMA_ACT(TY, ACT) do { if (a.res) EDE_UMMA_LAUNCH(TY, ACT, true); else EDE_UMMA_LAUNCH(TY, ACT, false); } while (0)
 #define EDE_UMMA_TY(TY)                                                      \
     do {                                                                     \
@@ -1186,7 +1529,7 @@ static int conv_umma_launch(const EdeConv& a, ConvLaunch& L, cudaStream_t st) {
 #undef EDE_UMMA_ACT
 #undef EDE_UMMA_LAUNCH
     if (rc) return rc;
-    EDE_LAUNCH_CHECK("conv_umma_kernel");
+    EDE_LAUNCH_CHECK(p.npack ? "conv_npack_kernel" : "conv_umma_kernel");
     return EDE_OK;
 }
 

@@ -9,8 +9,9 @@
 namespace ede {
 
 struct PrepackDims {
-    int cout, cin, kh, kw, cin_p, cout_p, passes, g;   // g >= 1
+    int cout, cin, kh, kw, cin_p, cout_p, passes, g;   // g >= 1 taps of a kernel row per tile
     int co_rows, ci_cols, kws;                         // rows / columns of one w_umma tile, kernel-row steps
+    int slot;                                          // rows per tap slot: 128 / g (taps on the M rows) or cout_p16 (on N)
 };
 
 __device__ __forceinline__ float src_weight(const EdePrepackConv& a, int lane_o, int lane_i, int ky, int kx) {
@@ -33,8 +34,8 @@ __global__ void prepack_umma_kernel(const EdePrepackConv a, const PrepackDims d)
         const int ky = tile / d.kws, gx = tile - ky * d.kws;
         float v = 0.f;
         if (d.g > 1) {
-            const int cg = 128 / d.g, j = row / cg, co = row - j * cg, kx = gx * d.g + j;
-            if (kx < d.kw && co < d.cout_p) v = src_weight(a, co, c, ky, kx);
+            const int j = row / d.slot, co = row - j * d.slot, kx = gx * d.g + j;
+            if (j < d.g && kx < d.kw && co < d.cout_p) v = src_weight(a, co, c, ky, kx);
         } else {
             v = src_weight(a, row, c, ky, gx);
         }
@@ -84,17 +85,21 @@ static int prepack_dims(const EdePrepackConv& a, PrepackDims& d) {
     EDE_REQUIRE(a.in_map || a.cin <= a.cin_p, "ede_prepack_conv: cin exceeds the lane count (no in_map given)");
     EDE_REQUIRE(a.out_map || a.cout <= a.cout_p, "ede_prepack_conv: cout exceeds the lane count (no out_map given)");
     EDE_REQUIRE(a.passes == 1 || a.passes == 2, "ede_prepack_conv: passes must be 1 or 2");
-    EDE_REQUIRE(a.pack_g == 0 || a.pack_g == 1 || a.pack_g == 2 || a.pack_g == 4, "ede_prepack_conv: pack_g must be 0/1, 2 or 4");
+    const bool on_n = a.pack_g >= (EDE_PACK_N | 2) && a.pack_g <= (EDE_PACK_N | 5);
+    EDE_REQUIRE(a.pack_g == 0 || a.pack_g == 1 || a.pack_g == 2 || a.pack_g == 4 || on_n,
+                "ede_prepack_conv: pack_g must be 0/1, 2, 4 or EDE_PACK_N | 2..5");
     EDE_REQUIRE((a.bn_weight != nullptr) == (a.bn_bias != nullptr) && (a.bn_weight != nullptr) == (a.bn_mean != nullptr) &&
                     (a.bn_weight != nullptr) == (a.bn_var != nullptr),
                 "ede_prepack_conv: give all four BatchNorm vectors or none");
     d.cout = a.cout; d.cin = a.cin; d.kh = a.kh; d.kw = a.kw; d.cin_p = a.cin_p; d.cout_p = a.cout_p;
     d.passes = a.passes;
-    d.g = a.pack_g > 1 ? a.pack_g : 1;
-    EDE_REQUIRE(d.g == 1 || a.cout_p <= 128 / d.g, "ede_prepack_conv: %d output lanes do not fit %d taps in 128 rows",
+    d.g = on_n ? (a.pack_g & 15) : a.pack_g > 1 ? a.pack_g : 1;
+    d.slot = on_n ? round_up(a.cout_p, 16) : 128 / d.g;
+    EDE_REQUIRE(d.g == 1 || on_n || a.cout_p <= 128 / d.g, "ede_prepack_conv: %d output lanes do not fit %d taps in 128 rows",
                 a.cout_p, d.g);
+    EDE_REQUIRE(!on_n || d.g * d.slot <= 256, "ede_prepack_conv: %d taps of %d output lanes exceed 256 UMMA columns", d.g, d.slot);
     d.kws = ceil_div(a.kw, d.g);
-    d.co_rows = d.g > 1 ? 128 : round_up(a.cout_p, 16);
+    d.co_rows = on_n ? d.g * d.slot : d.g > 1 ? 128 : round_up(a.cout_p, 16);
     d.ci_cols = round_up(a.cin_p, 64);
     return EDE_OK;
 }

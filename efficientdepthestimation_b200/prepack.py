@@ -87,6 +87,32 @@ def pack_umma_taps(full: torch.Tensor, passes: int, g: int) -> Tuple[torch.Tenso
     return out.contiguous(), 128, ci_p
 
 
+PACK_N = 16      # include/ede.h EDE_PACK_N: kernel-row taps on the UMMA N axis
+
+
+def pack_umma_ntaps(full: torch.Tensor, passes: int, g: int) -> Tuple[torch.Tensor, int, int]:
+    """Tap-packed weights for the pixels-on-M tcgen05 form with `g` (2..5) taps of a kernel row on the N axis
+    (EdeConv.w_pack_g = EDE_PACK_N | g): [cout_p][cin_p][kh][kw] -> bf16 [passes*kh*ceil(kw/g)][g*cout_p16][cin_p64]
+    with row j*cout_p16+c of tile (ky, gx) = w[c][.][ky][gx*g + j]; rows of taps beyond kw and of channels beyond
+    cout_p stay zero.  passes=2 appends the bf16 low halves as in pack_umma."""
+    co, ci, kh, kw = full.shape
+    slot = ceil_to(co, 16)
+    if g * slot > 256:
+        raise ValueError(f"pack_umma_ntaps: {g} taps of {slot} output lanes exceed 256 UMMA columns")
+    kws, ci_p = (kw + g - 1) // g, ceil_to(ci, 64)
+    tiles = torch.zeros(kh * kws, g * slot, ci, dtype=torch.float32, device=full.device)
+    for ky in range(kh):
+        for kx in range(kw):
+            gx, j = divmod(kx, g)
+            tiles[ky * kws + gx, j * slot:j * slot + co] = full[:, :, ky, kx]
+    out = torch.zeros(passes * kh * kws, g * slot, ci_p, dtype=torch.bfloat16, device=full.device)
+    hi = tiles.to(torch.bfloat16)
+    out[:kh * kws, :, :ci] = hi
+    if passes == 2:
+        out[kh * kws:, :, :ci] = (tiles - hi.float()).to(torch.bfloat16)
+    return out.contiguous(), g * slot, ci_p
+
+
 def fold_bn(cout: int, bn: Optional[dict], conv_bias: Optional[torch.Tensor], device) -> Tuple[torch.Tensor, torch.Tensor]:
     """-> (scale, shift) fp32 [cout] with  bn(conv(x)+b) == scale*conv(x) + shift.
     bn: dict(weight, bias, mean, var, eps) or None."""

@@ -31,12 +31,13 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 10
+#define EDE_ABI_VERSION 11
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
 enum { EDE_OK = 0, EDE_E_ARG = -1, EDE_E_CUDA = -2, EDE_E_UNSUPPORTED = -3, EDE_E_DRIVER = -4 };
 enum { EDE_NHWC = 0, EDE_NCHW = 1 };
+enum { EDE_PACK_N = 16 };   /* flag in w_pack_g / pack_g: kernel-row taps packed on the UMMA N axis (see EdeConv.w_pack_g) */
 
 /* One dense convolution + folded BatchNorm + activation (+ residual).
  * replaces: nn.Conv2d -> nn.BatchNorm2d(eval) -> ReLU/swish -> `out += residual`
@@ -67,8 +68,11 @@ typedef struct EdeConv {
     int32_t w_pack_g;       /* how w_umma packs kernel-row taps on its Cout axis: 0/1 = one tap per tile
                                (layout above); G = 2/4: tiles [kh*ceil(kw/G)][128][cin_p64] with row
                                j*(128/G)+c = w[c][.][ky][gx*G+j] (zero rows for taps >= kw), needs
-                               cout_p <= 128/G; -1 only for ede_conv2d_umma_config: 'which G should I
-                               prepack for?' (answer in EdeUmmaCfg.pack_g)                            */
+                               cout_p <= 128/G; EDE_PACK_N | G (G = 2..5): the G taps sit on the UMMA N axis of the
+                               pixels-on-M form instead -- tiles [kh*ceil(kw/G)][G*cout_p16][cin_p64] with row
+                               j*cout_p16+c (cout_p16 = cout_p rounded up to 16, G*cout_p16 <= 256); -1 only for
+                               ede_conv2d_umma_config: 'which packing should I prepack for?' (answer in
+                               EdeUmmaCfg.pack_g)                                                       */
     int32_t w_per_image;    /* T > 0: w_umma holds n weight sets of T taps each (image i uses taps [i*T, (i+1)*T)): the
                                squeeze-excite gate folded into the project conv's weights by ede_se_fc (w_dst); tiles
                                then never span two images */
@@ -117,7 +121,7 @@ typedef struct EdeUmmaCfg {
     int32_t tiles_w, tiles_h, flat;              /* flat: N*H*W folded into one pixel axis (1x1)  */
     double useful_frac;     /* real MACs / issued tensor MACs                                    */
     int32_t swap;           /* 1: weights are the M-side operand (Cout <= 128), 256 pixels on N  */
-    int32_t pack_g;         /* kernel-row taps per MMA in the swapped form (1, 2 or 4), see w_pack_g */
+    int32_t pack_g;         /* kernel-row taps per MMA: 1, 2 or 4 (swapped form) or EDE_PACK_N | G, see w_pack_g */
 } EdeUmmaCfg;
 int ede_conv2d_umma_config(const EdeConv* a, EdeUmmaCfg* out);
 

@@ -70,6 +70,34 @@ CONV_CASES = [
 @pytest.mark.parametrize("mode", ["bf16", "split", "fp32"])
 @pytest.mark.parametrize("case", CONV_CASES, ids=[c[0] for c in CONV_CASES])
 def test_conv2d(cuda, lib, case, mode):
+    _run_conv_case(cuda, lib, case, mode)
+
+
+# narrow stride-1 k x k convs in the N-packed pixels-on-M form (EDE_PACK_N | G: the taps of a kernel row on the UMMA N
+# axis, lane-shifted sums in the epilogue, weights resident in shared memory), forced through EDE_UMMA_NPACK=1 so that
+# the form is exercised whatever the tile picker's time model prefers
+NPACK_CASES = [
+    ("np_3x3_32_to_16", 2, 57, 76, 32, 16, 3, 1, (1, 1, 1, 1), False, A.ACT_RELU),          # conv1_2: G = 3, N = 48
+    ("np_5x5_24_to_32", 2, 57, 76, 24, 32, 5, 1, (2, 2, 2, 2), False, A.ACT_RELU),          # D.up4: G = 5, N = 160
+    ("np_5x5_24_to_48_res", 1, 41, 67, 24, 48, 5, 1, (2, 2, 2, 2), True, A.ACT_RELU),       # G = 5, N = 240, residual
+    ("np_3x3_40_to_40_swish", 2, 28, 38, 40, 40, 3, 1, (1, 1, 1, 1), True, A.ACT_SWISH),    # G = 3, N = 144
+    ("np_3x3_16_to_90_g2", 1, 30, 61, 16, 90, 3, 1, (1, 1, 1, 1), False, A.ACT_RELU),       # G = 2 < kw: 2 steps per kernel row
+    ("np_3x3_90_to_24_two_chunks", 2, 20, 33, 90, 24, 3, 1, (1, 1, 1, 1), False, A.ACT_NONE),   # K = 64 + 32: two stages
+    ("np_4x4_asym_16_to_8", 1, 37, 45, 16, 8, 4, 1, (1, 1, 2, 2), False, A.ACT_RELU),       # even kernel, asymmetric pad
+]
+
+
+@pytest.mark.parametrize("mode", ["bf16", "split"])
+@pytest.mark.parametrize("case", NPACK_CASES, ids=[c[0] for c in NPACK_CASES])
+def test_conv2d_taps_on_n(cuda, lib, case, mode, monkeypatch):
+    monkeypatch.setenv("EDE_UMMA_NPACK", "1")
+    cfg = _run_conv_case(cuda, lib, case, mode)
+    if mode == "split" and not cfg.pack_g & P.PACK_N:
+        pytest.skip("hi+lo weights over doubled lanes do not fit the resident-weight budget of this form")
+    assert cfg.pack_g & P.PACK_N and cfg.pitch == 32 and cfg.swap == 0, (cfg.pack_g, cfg.pitch, cfg.swap)
+
+
+def _run_conv_case(cuda, lib, case, mode):
     name, n, h, w, cin, cout, k, s, (pt, pl, pb, pr), use_res, act = case
     g = torch.Generator().manual_seed(len(name) * 131 + k)
     oh, ow = (h + pt + pb - k) // s + 1, (w + pl + pr - k) // s + 1
@@ -113,7 +141,8 @@ def test_conv2d(cuda, lib, case, mode):
     q = A.umma_config(a)
     pack_g = int(q.pack_g) if q.eligible and q.pack_g > 1 else 1
     if pack_g > 1:
-        w_umma, co16, ci64 = P.pack_umma_taps(full, passes, pack_g)
+        w_umma, co16, ci64 = (P.pack_umma_ntaps(full, passes, pack_g & 15) if pack_g & P.PACK_N else
+                              P.pack_umma_taps(full, passes, pack_g))
         a.w_umma, a.w_umma_cout_p, a.w_umma_cin_p = w_umma.data_ptr(), co16, ci64
     a.w_pack_g = pack_g
     cfg = A.umma_config(a)
@@ -136,6 +165,7 @@ def test_conv2d(cuda, lib, case, mode):
     rel = {"bf16": 4e-3, "split": 6e-5 + 2.0e-8 * cin * k * k, "fp32": 2e-5}[mode]
     tol = rel * ref.abs() + rel
     assert bool((err <= tol).all()), (name, mode, float(err.max()), float((err / (ref.abs() + 1)).max()))
+    return cfg
 
 
 @pytest.mark.parametrize("c", [44, 90, 150])      # 48 lanes (one 64-chunk), 96 (three 32-lane chunks), 152 (64+64+24)
@@ -424,6 +454,9 @@ def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, 
     (16, 48, 3, 1, 4, True, False, True),         # 4 kernel-row taps on the 128 M rows, conv bias, no BN
     (40, 40, 5, 2, 2, False, True, True),         # 2 taps, hi+lo passes, BN + bias
     (1, 74, 5, 1, 1, False, False, True),         # R.conv2: one output channel + bias
+    (16, 32, 3, 1, 16 | 3, False, True, False),   # conv1_2: the 3 taps of a kernel row on the UMMA N axis (EDE_PACK_N | 3)
+    (30, 24, 5, 2, 16 | 5, False, True, True),    # 5 taps x 32 columns, hi+lo passes
+    (74, 74, 5, 1, 16 | 3, False, False, False),  # R.conv0: 3 taps x 80 columns, 2 kernel-row steps
 ])
 def test_prepack_conv_behind_the_c_abi(cuda, lib, cout, cin, k, passes, pack_g, use_maps, use_bn, use_bias):
     """ede_prepack_conv_to / ede_prepack_conv / ede_free: OIHW weight + BatchNorm vectors -> w_umma / w_direct / scale /
@@ -446,7 +479,8 @@ def test_prepack_conv_behind_the_c_abi(cuda, lib, cout, cin, k, passes, pack_g, 
     bias = torch.randn(cout, generator=g) if use_bias else None
     # expected: the host functions
     full = P.scatter_weight(w, in_map.tolist(), out_map.tolist())
-    exp_umma, co16, ci64 = (P.pack_umma_taps(full, passes, pack_g) if pack_g > 1 else P.pack_umma(full, passes))
+    exp_umma, co16, ci64 = (P.pack_umma_ntaps(full, passes, pack_g & 15) if pack_g & P.PACK_N else
+                            P.pack_umma_taps(full, passes, pack_g) if pack_g > 1 else P.pack_umma(full, passes))
     exp_direct = P.pack_direct(full)
     sc, sf = P.fold_bn(cout, bn, bias, "cpu")
     exp_scale, exp_shift = P.place_lanes(sc, out_map.tolist()), P.place_lanes(sf, out_map.tolist())

@@ -46,10 +46,12 @@ def main():
               f"tmem={cfg.tmem_cols}")
         print(f"   MMA warp busy span       median {np.median(mma):9.1f} us")
         print(f"   issuer waiting for weight/pixel stages median {np.median(t[:, 4]) / clk:9.1f} us")
+        print(f"   issuer waiting for the resident pixel tile median {np.median(t[:, 13]) / clk:9.1f} us")
         print(f"   producer waiting for free weight stages median {np.median(t[:, 5]) / clk:9.1f} us")
         print(f"   issuer waiting for a drained accumulator median {np.median(t[:, 8]) / clk:9.1f} us")
         print(f"   swapped epilogue (warp 2): barrier {np.median(t[:, 9]) / clk:.1f} us, finish+store {np.median(t[:, 10]) / clk:.1f} us, "
               f"ld wait+stage {np.median(t[:, 11]) / clk:.1f} us")
+        print(f"   epilogue (warp 2): tile decode + scale/shift {np.median(t[:, 14]) / clk:.1f} us, accumulator -> stores -> release {np.median(t[:, 15]) / clk:.1f} us")
         print(f"   epilogue waiting for MMA median {np.median(t[:, 6]) / clk:9.1f} us")
         print(f"   epilogue end - MMA end   median {np.median(t[:, 3] - t[:, 2]) / 1e3:9.1f} us")
 
