@@ -291,7 +291,7 @@ def roofline_of(plan, arch, n, dev, clocks, step_ms):
     bw_ms = sum(e["ms"] for e in fam.values())
     bw_bytes = sum(e["bytes"] for e in fam.values())
     total = sum(times)
-    return {"bound": "tensor", "kernel": "conv_umma_kernel (+ tap gathers + stem: the reference's dense-conv FLOPs)",
+    return {"bound": "tensor", "kernel": "conv_umma_kernel / conv_npack_kernel (+ tap gathers + stem: the reference's dense-conv FLOPs)",
             "achieved": round(achieved, 1), "peak": peak, "unit": "TFLOP/s", "frac": round(achieved / peak, 4),
             "peak_kind": "bf16 sustained (sw_power_cap seen)" if capped else "bf16 burst (no power cap in the clocks record)",
             "peak_source": peaks["source"],

@@ -972,6 +972,8 @@ static int env_int(const char* name, int dflt) {
 }
 
 constexpr int SMEM_BUDGET = 189 * 1024;      // operand rings; barriers + alignment slack on top
+constexpr int SMEM_EXTRA_NPACK = 1024 + 512 + 2048;                 // conv_npack_kernel stages nothing in its epilogue
+constexpr int SMEM_BUDGET_NPACK = 227 * 1024 - SMEM_EXTRA_NPACK - 1024;
 constexpr int SMEM_EXTRA = 1024 + 512 + 2048 + 4 * 16 * 132 * 4;   // alignment slack + barriers + scale/shift slice + 2 half-sets x 2 staging tiles (swapped epilogue)
 
 static bool umma_eligible(const EdeConv& a) {
@@ -1294,7 +1296,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
             if (!force_ck && ck == 32 && round_up(a.cin_p, 32) >= round_up(a.cin_p, 64)) continue;
             const int ck_bytes = ck * 2, n_chunks = ceil_div(a.cin_p, ck);
             const int w_chunk_bytes = steps * n_pad * ck_bytes;              // one stage = all taps of a channel chunk
-            if (n_chunks > MAX_STAGES || steps > 256 || n_chunks * w_chunk_bytes > 128 * 1024) continue;
+            if (n_chunks > MAX_STAGES || steps > 256 || n_chunks * w_chunk_bytes > 160 * 1024) continue;
             const double t_mma = mma_cycles(ck_bytes, n_pad) * 1.15;
             const int force_T = env_int("EDE_UMMA_NPACK_T", 0);
             for (int T = 1; T <= 256 / n_pad && T <= 8; ++T) {
@@ -1302,7 +1304,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                 const int bh = 4 * T, box_rows = bh + a.kh - 1;
                 const int rows_alloc = std::max(box_rows * 32, T * 128 + (a.kh - 1) * 32 + kws * G);
                 const int a_bytes = round_up(rows_alloc * ck_bytes, 1024);
-                const int a_stages = std::min(6, (SMEM_BUDGET - n_chunks * w_chunk_bytes) / a_bytes);
+                const int a_stages = std::min(6, (SMEM_BUDGET_NPACK - n_chunks * w_chunk_bytes) / a_bytes);
                 if (a_stages < 2) continue;
                 EdeUmmaCfg cand{};
                 cand.a_mode = 0; cand.bh = bh; cand.bw = bw; cand.pitch = 32; cand.box_rows = box_rows;
@@ -1317,7 +1319,13 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                 // per (m-tile, 16-channel chunk) unit: G tcgen05.ld + 16 (G-1) shuffles + BN / activation / stores; two
                 // warps per lane quarter share the units
                 const double epi = std::ceil(T * (slot / 16) / 2.0) * (260.0 + 90.0 * G) + 300.0;
-                const double t = rounds * (std::max(std::max(mma, mem), epi) + 400.0) + 4000.0;
+                // every role pays ~1500 cycles of per-tile bookkeeping (waits, fences, commits run at full latency: one
+                // warp per scheduler), and a pixel tile lands ~3000 cycles after its stage was released: with few stages
+                // the difference is exposed (measured: 5x5 24->32 runs 20 % faster with 32-channel chunks = 6 stages of
+                // 16 KB than with 64-channel chunks = 2 stages of 33 KB although its MMAs are 1.6x slower)
+                double t_tile = std::max(std::max(std::max(mma, mem), epi), 1500.0);
+                if ((a_stages - 1) * t_tile < 3000.0) t_tile += (3000.0 - (a_stages - 1) * t_tile) / a_stages;
+                const double t = rounds * (t_tile + 400.0) + 4000.0;
                 if (t < best_time) {
                     best_time = t;
                     best = cand;
@@ -1335,7 +1343,8 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     c.eligible = 1;
     if (c.pack_g < 1) c.pack_g = 1;
     c.tmem_cols = c.swap ? 512 : pow2_cols(umma_acc_stages(c) * c.m_tiles * c.n_pad);
-    c.smem_bytes = c.a_stages * c.a_stage_bytes + c.b_stages * c.b_stage_bytes + SMEM_EXTRA;
+    c.smem_bytes = c.a_stages * c.a_stage_bytes + c.b_stages * c.b_stage_bytes +
+                   ((c.pack_g & EDE_PACK_N) ? SMEM_EXTRA_NPACK : SMEM_EXTRA);
     c.flat = is_1x1;
 }
 

@@ -27,7 +27,7 @@ def main():
     agg = collections.defaultdict(lambda: [0, 0.0, 0.0])
     for d in per.values():
         name = d["name"].split("(")[0].replace("void ", "").replace("ede::", "")
-        name = name.split("<")[0] if name.startswith("conv_umma_kernel") else name
+        name = name.split("<")[0] if name.startswith(("conv_umma_kernel", "conv_npack_kernel")) else name
         a = agg[name]
         a[0] += 1
         a[1] += d.get("gpu__time_duration.sum", 0.0)
@@ -47,7 +47,7 @@ def main():
     if key and has_dram:
         path = os.path.join(os.path.dirname(dst), "r02_traffic.json")
         t = json.load(open(path)) if os.path.exists(path) else {}
-        conv = agg.get("conv_umma_kernel", [0, 0.0, 0.0])
+        conv = [sum(agg.get(k, [0, 0.0, 0.0])[i] for k in ("conv_umma_kernel", "conv_npack_kernel")) for i in range(3)]   # both tcgen05 conv kernels
         t[key] = {"conv_umma_dram_bytes_per_step": conv[2] / steps, "conv_umma_launches_per_step": conv[0] / steps,
                   "all_kernels_dram_bytes_per_step": sum(a[2] for a in agg.values()) / steps, "capture": capture}
         json.dump(t, open(path, "w"), indent=1)
