@@ -957,8 +957,11 @@ class EdeModule:
         """Drop compiled plans (weights changed: load_state_dict, .to(), .train())."""
         from torch import nn
         _WEIGHT_EPOCH[0] += 1
+        # every EdeModule gets a (fresh) cache dict HERE, not lazily in its first forward: DataParallel replicas are
+        # shallow copies made per call, so the dict must exist on the source module for the replicas to share it
+        # (entries are keyed by device) -- otherwise each call would compile into a dict that dies with the replica
         for m in self.modules() if isinstance(self, nn.Module) else [self]:
-            if "_ede_plans" in m.__dict__:
+            if isinstance(m, EdeModule):
                 m.__dict__["_ede_plans"] = {}
 
     def freeze_plans(self, frozen: bool = True) -> None:
