@@ -419,7 +419,7 @@ int ede_dwconv2d(const EdeDwConv* a, void* stream) {
     if (gx > 2048) gx = 2048;
     dim3 grid((unsigned)gx, (unsigned)a->n);
     const size_t smem = a->pool_sum ? (size_t)a->c_p * sizeof(float) : 0;
-    EDE_DISPATCH_DTYPE(a->dtype, T, (dwconv_kernel<T><<<grid, 256, smem, (cudaStream_t)stream>>>(*a)));
+    EDE_DISPATCH_DTYPE_DW(a->dtype, T, (dwconv_kernel<T><<<grid, 256, smem, (cudaStream_t)stream>>>(*a)));
     EDE_LAUNCH_CHECK("dwconv_kernel");
     return EDE_OK;
 }

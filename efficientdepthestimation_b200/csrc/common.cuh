@@ -39,6 +39,11 @@ static inline size_t dtype_size(int dt) { return dt == EDE_BF16 ? 2 : 4; }
 // tensor with twice the lanes it feeds the tensor cores directly: weights laid out [w,w] make one
 // K=16 MMA compute (hi+lo).w, so the same TMA/UMMA path runs at near-fp32 operand accuracy.
 struct bf16x2_t { __nv_bfloat16 hi, lo; };
+// EDE_F32_TO_BF16X2 (depthwise convs only): the INPUT lanes are plain fp32 (the expand conv of an MBConv block writes
+// fp32 -- the same 4 bytes per lane -- so that neither its epilogue splits nor the depthwise kernel recombines), the
+// OUTPUT lanes are split bf16 (the project conv reads them as a tensor-core operand).  A tag type with the layout of
+// the output lane: loads go through the float overloads, stores through the split ones.
+struct f32in_t : bf16x2_t {};
 
 // ---------------------------------------------------------------- typed element access
 template <typename T> struct Elt;
@@ -109,6 +114,9 @@ template <> __device__ __forceinline__ void load8<bf16x2_t>(const bf16x2_t* p, f
         v[2 * i + 1] = bf16hi_f(u[i]) + bf16hi_f(u[4 + i]);
     }
 }
+template <> __device__ __forceinline__ void load8<f32in_t>(const f32in_t* p, float (&v)[8]) {
+    load8<float>(reinterpret_cast<const float*>(p), v);
+}
 template <typename T> __device__ __forceinline__ void store8(T* p, const float (&v)[8]);
 template <> __device__ __forceinline__ void store8<float>(float* p, const float (&v)[8]) {
     uint32_t u[8];
@@ -134,6 +142,10 @@ template <> __device__ __forceinline__ void store8<bf16x2_t>(bf16x2_t* p, const 
         u[4 + i] = *reinterpret_cast<const uint32_t*>(&l);
     }
     stg256(p, u);
+}
+
+template <> __device__ __forceinline__ void store8<f32in_t>(f32in_t* p, const float (&v)[8]) {
+    store8<bf16x2_t>(static_cast<bf16x2_t*>(p), v);
 }
 
 // 4 consecutive channels (c % 4 == 0) of one pixel row `p` (lane 0 of the row, 32-byte aligned)
@@ -181,6 +193,8 @@ template <> __device__ __forceinline__ float round_as<bf16x2_t>(float v) {
     const float h = __bfloat162float(__float2bfloat16_rn(v));
     return h + __bfloat162float(__float2bfloat16_rn(v - h));
 }
+
+template <> __device__ __forceinline__ float round_as<f32in_t>(float v) { return round_as<bf16x2_t>(v); }
 
 // ---- programmatic dependent launch.  Kernels of a forward plan are launched with
 // cudaLaunchAttributeProgrammaticStreamSerialization: the next kernel's CTAs may become resident (and run their
@@ -289,6 +303,15 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 // dispatch helper: call f.template operator()<T>() for the dtype
+// depthwise kernels: the three storage types plus fp32-in / split-out
+#define EDE_DISPATCH_DTYPE_DW(dt, T, ...)                    \
+    do {                                                     \
+        if ((dt) == EDE_BF16) { using T = __nv_bfloat16; __VA_ARGS__; } \
+        else if ((dt) == EDE_BF16X2) { using T = ::ede::bf16x2_t; __VA_ARGS__; } \
+        else if ((dt) == EDE_F32_TO_BF16X2) { using T = ::ede::f32in_t; __VA_ARGS__; } \
+        else { using T = float; __VA_ARGS__; }              \
+    } while (0)
+
 #define EDE_DISPATCH_DTYPE(dt, T, ...)                       \
     do {                                                     \
         if ((dt) == EDE_BF16) { using T = __nv_bfloat16; __VA_ARGS__; } \

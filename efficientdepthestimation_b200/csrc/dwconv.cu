@@ -75,6 +75,14 @@ template <> struct Pair<bf16x2_t> {
     }
 };
 
+template <> struct Pair<f32in_t> {       // fp32 lanes in, split-bf16 lanes out
+    static constexpr int kPixelBytes = 256;
+    static __device__ __forceinline__ float2 lds(const uint8_t* px, int lane) { return Pair<float>::lds(px, lane); }
+    static __device__ __forceinline__ float2 st(f32in_t* px, int c, float2 v) {
+        return Pair<bf16x2_t>::st(static_cast<bf16x2_t*>(px), c, v);
+    }
+};
+
 struct alignas(64) DwParams {
     CUtensorMap tm_x;      // (channel lanes, W, H, N), element = one lane of the dtype
     EdeDwConv a;
@@ -331,7 +339,7 @@ int dwconv_tma_launch(const EdeDwConv& a, cudaStream_t st, int* strips_out) {
     if (!strips_out && (reinterpret_cast<uintptr_t>(a.x) & 15) != 0) return 1;
     const int ks = a.k * 10 + a.s;
     int rc = 1;
-    EDE_DISPATCH_DTYPE(a.dtype, T, {
+    EDE_DISPATCH_DTYPE_DW(a.dtype, T, {
         if (ks == 31) rc = dwconv_tma_launch_ks<T, 3, 1>(a, st, strips_out);
         else if (ks == 32) rc = dwconv_tma_launch_ks<T, 3, 2>(a, st, strips_out);
         else if (ks == 51) rc = dwconv_tma_launch_ks<T, 5, 1>(a, st, strips_out);

@@ -41,6 +41,7 @@ struct alignas(64) DwTileParams {
 
 template <typename T> __device__ __forceinline__ void expand_group(uint8_t* g);
 template <> __device__ __forceinline__ void expand_group<float>(uint8_t*) {}
+template <> __device__ __forceinline__ void expand_group<f32in_t>(uint8_t*) {}     // fp32 lanes already
 template <> __device__ __forceinline__ void expand_group<bf16x2_t>(uint8_t* g) {
     const uint4 hi = *reinterpret_cast<const uint4*>(g), lo = *reinterpret_cast<const uint4*>(g + 16);
     float4 a, b;
@@ -57,6 +58,10 @@ template <typename T> __device__ __forceinline__ float2 store_pair(T* px, int c,
 template <> __device__ __forceinline__ float2 store_pair<float>(float* px, int c, float2 v) {
     *reinterpret_cast<float2*>(px + c) = v;
     return v;
+}
+template <> __device__ __forceinline__ float2 store_pair<bf16x2_t>(bf16x2_t* px, int c, float2 v);
+template <> __device__ __forceinline__ float2 store_pair<f32in_t>(f32in_t* px, int c, float2 v) {
+    return store_pair<bf16x2_t>(static_cast<bf16x2_t*>(px), c, v);
 }
 template <> __device__ __forceinline__ float2 store_pair<bf16x2_t>(bf16x2_t* px, int c, float2 v) {
     uint32_t* g = reinterpret_cast<uint32_t*>(px + (c & ~7)) + ((c & 7) >> 1);
@@ -110,7 +115,7 @@ __global__ void __launch_bounds__(DT_THREADS, 2) dwconv_tile_kernel(const __grid
     }
     mbar_wait(smem_u32(&bar), 0);
     // split bf16 -> fp32 in place, once per element
-    if (sizeof(T) == 4 && !std::is_same<T, float>::value) {
+    if (std::is_same<T, bf16x2_t>::value) {
         const int groups = p.box_h * p.box_w * (CH / 8);
         for (int g = threadIdx.x; g < groups; g += DT_THREADS) expand_group<T>(tile + (size_t)g * 32);
         __syncthreads();
@@ -299,6 +304,12 @@ int dwconv_tile_launch(const EdeDwConv& a, cudaStream_t st, int* bands_out) {
     int rc = 1;
     if (a.dtype == EDE_BF16X2) {
         using T = bf16x2_t;
+        if (ks == 31) rc = dwconv_tile_launch_ks<T, 3, 1>(a, c, st);
+        else if (ks == 32) rc = dwconv_tile_launch_ks<T, 3, 2>(a, c, st);
+        else if (ks == 51) rc = dwconv_tile_launch_ks<T, 5, 1>(a, c, st);
+        else if (ks == 52) rc = dwconv_tile_launch_ks<T, 5, 2>(a, c, st);
+    } else if (a.dtype == EDE_F32_TO_BF16X2) {
+        using T = f32in_t;
         if (ks == 31) rc = dwconv_tile_launch_ks<T, 3, 1>(a, c, st);
         else if (ks == 32) rc = dwconv_tile_launch_ks<T, 3, 2>(a, c, st);
         else if (ks == 51) rc = dwconv_tile_launch_ks<T, 5, 1>(a, c, st);

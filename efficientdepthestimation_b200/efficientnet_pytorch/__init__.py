@@ -96,7 +96,11 @@ class MBConvBlock(EdeModule, nn.Module):
     def _emit(self, g, x, tag="mbconv"):
         h = x
         if self._cfg["expand"] != 1:
-            h = g.conv_bn_act(h, self._expand_conv, self._bn0, A.ACT_SWISH, tag=tag + ".expand")
+            # the expanded tensor only feeds the depthwise kernel (CUDA cores): in the split-precision scope it is written
+            # as plain fp32 -- the same 4 bytes per lane -- so the conv epilogue does not split and the depthwise
+            # kernel does not recombine (EDE_F32_TO_BF16X2)
+            h = g.conv_bn_act(h, self._expand_conv, self._bn0, A.ACT_SWISH, tag=tag + ".expand",
+                              out_dtype=A.F32 if g.expand_f32() else None, hi_lo=g.expand_f32())
         h, pool = g.dwconv_bn_act(h, self._depthwise_conv, self._bn1, A.ACT_SWISH, pool=True, tag=tag + ".dw")
         res = x if self._id_skip else None
         if g.se_fold_pays(h, self._cfg["cout"]):

@@ -251,7 +251,7 @@ class Graph:
         self.outputs.append((i, (v.n, v.c, v.h, v.w)))
 
     def conv(self, x: View, parts, stride=1, pad=(0, 0, 0, 0), act=A.ACT_NONE, res: Optional[View] = None,
-             out: Optional[View] = None, relu_in=False, out_dtype=None, tag="conv", se_fold=None) -> View:
+             out: Optional[View] = None, relu_in=False, out_dtype=None, tag="conv", se_fold=None, hi_lo=False) -> View:
         """Dense conv + folded BN + activation (+ residual).  `parts` is a list of
         (weight OIHW, bn module|None, bias|None, activated: bool); the parts share the input and
         their outputs are laid side by side (each padded to 8 lanes) -- used to run the two 5x5
@@ -312,7 +312,8 @@ class Graph:
                 raise RuntimeError(f"{tag}: destination slice {out.n, out.h, out.w, out.c_p} does not match "
                                    f"conv output {x.n, oh, ow, cout_p}")
         # hi+lo weights whenever the OUTPUT is kept at split precision (the accurate encoder path)
-        passes = 2 if (out.dtype == A.BF16X2 and self.precision != "fp32") else 1
+        # ... or when the caller keeps an fp32 output at that precision (hi_lo: the expand conv of an MBConv block)
+        passes = 2 if ((out.dtype == A.BF16X2 or hi_lo) and self.precision != "fp32") else 1
         scale = self._dev(torch.cat(scales))
         shift = self._dev(torch.cat(shifts))
         if res is not None and res.dtype != out.dtype:
@@ -427,12 +428,12 @@ class Graph:
         return y
 
     def conv_bn_act(self, x: View, conv, bn=None, act=A.ACT_NONE, res=None, out=None, relu_in=False,
-                    out_dtype=None, tag="conv", se_fold=None) -> View:
+                    out_dtype=None, tag="conv", se_fold=None, hi_lo=False) -> View:
         """nn.Conv2d (+ nn.BatchNorm2d) (+ activation) as one fused operator."""
         if conv.groups != 1:
             raise RuntimeError(f"{tag}: grouped convolution is not a dense conv")
         return self.conv(x, [(conv.weight, bn, conv.bias, act != A.ACT_NONE)], conv.stride[0], _pad4(conv), act,
-                         res, out, relu_in, out_dtype, tag, se_fold=se_fold)
+                         res, out, relu_in, out_dtype, tag, se_fold=se_fold, hi_lo=hi_lo)
 
     def dwconv_bn_act(self, x: View, conv, bn, act, pool: bool, tag="dwconv"):
         """Depthwise conv + BN + activation; with pool=True also the per-(n,c) sums for SE."""
@@ -442,7 +443,9 @@ class Graph:
         c = x.c
         if conv.groups != c or int(conv.weight.shape[0]) != c:
             raise RuntimeError(f"{tag}: not a depthwise convolution over {c} channels")
-        out = View(self.new_buf(x.n, oh, ow, x.c_p, x.dtype), 0, x.lanes)
+        # fp32 lanes in / split-bf16 lanes out (EDE_F32_TO_BF16X2) when the producer wrote fp32 inside a split-precision scope
+        mixed = x.dtype == A.F32 and self.act_dtype == A.BF16X2
+        out = View(self.new_buf(x.n, oh, ow, x.c_p, A.BF16X2 if mixed else x.dtype), 0, x.lanes)
         wt = _cpu(conv.weight).float().reshape(c, k * k).t()               # [k*k][c]
         w = torch.zeros(k * k, x.c_p, dtype=torch.float32)
         idx = torch.tensor([j for j, v in enumerate(x.lanes) if v >= 0])
@@ -452,7 +455,8 @@ class Graph:
         w, sc, sf = self._dev(w), self._dev(P.place_lanes(sc, x.lanes)), self._dev(P.place_lanes(sf, x.lanes))
         st = A.EdeDwConv(x=None, y=None, w=None, scale=None, shift=None, pool_sum=None, n=x.n, h=x.h, w_=x.w,
                          c_p=x.c_p, x_cs=x.buf.cs, x_co=x.co,
-                         oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act, dtype=x.dtype)
+                         oh=oh, ow=ow, y_cs=out.buf.cs, y_co=out.co, k=k, s=s, pt=pt, pl=pl, act=act,
+                         dtype=A.F32_TO_BF16X2 if mixed else x.dtype)
         pool_t = None
         if pool:
             # one slab of squeeze sums per column strip of the depthwise kernel: plain stores, added in slab order by
@@ -466,6 +470,10 @@ class Graph:
         self.flops += 2.0 * x.n * oh * ow * c * k * k
         self.exec_flops += 2.0 * x.n * oh * ow * c * k * k
         return out, pool_t
+
+    def expand_f32(self) -> bool:
+        """Write the expanded tensor of an MBConv block as fp32 instead of split bf16? (EDE_EXPAND_F32=0 turns it off)"""
+        return self.act_dtype == A.BF16X2 and self.precision == "bf16" and os.environ.get("EDE_EXPAND_F32", "1") != "0"
 
     def se_fold_pays(self, x: View, cout: int) -> bool:
         """Fold the gate into the consumer's weights (one scaled weight set per image) instead of a full read + write

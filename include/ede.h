@@ -31,9 +31,10 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 11
+#define EDE_ABI_VERSION 12
 
-enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2 };
+enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2,
+       EDE_F32_TO_BF16X2 = 3 };   /* EdeDwConv.dtype only: x lanes are fp32, y lanes split bf16 (same 4 bytes per lane) */
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
 enum { EDE_OK = 0, EDE_E_ARG = -1, EDE_E_CUDA = -2, EDE_E_UNSUPPORTED = -3, EDE_E_DRIVER = -4 };
 enum { EDE_NHWC = 0, EDE_NCHW = 1 };
@@ -133,7 +134,8 @@ int ede_conv2d_umma_config(const EdeConv* a, EdeUmmaCfg* out);
 typedef struct EdeDwConv {
     const void* x; void* y; const float* w; const float* scale; const float* shift; float* pool_sum;
     int32_t n, h, w_, c_p, x_cs, x_co, oh, ow, y_cs, y_co;
-    int32_t k, s, pt, pl, act, dtype;
+    int32_t k, s, pt, pl, act, dtype;            /* dtype of x and y; EDE_F32_TO_BF16X2: fp32 in (as the expand conv of an
+                                                    MBConv block can write it), split bf16 out (tensor-core operand) */
     int32_t pool_parts;     /* 0/1: pool_sum is fp32 [n][c_p], accumulated with atomics (order-dependent rounding).
                                P > 1: pool_sum is fp32 [P][n][c_p]; when the kernel runs with <= P column strips each
                                strip WRITES its own slab (no atomics: bit-reproducible forward), else it falls back

@@ -169,7 +169,7 @@ def _run_conv_case(cuda, lib, case, mode):
 
 
 @pytest.mark.parametrize("c", [44, 90, 150])      # 48 lanes (one 64-chunk), 96 (three 32-lane chunks), 152 (64+64+24)
-@pytest.mark.parametrize("dt", [A.F32, A.BF16, A.BF16X2])
+@pytest.mark.parametrize("dt", [A.F32, A.BF16, A.BF16X2, A.F32_TO_BF16X2])
 @pytest.mark.parametrize("k,s,pad", [(3, 1, (1, 1, 1, 1)), (3, 2, (0, 0, 1, 1)), (5, 2, (1, 1, 2, 2)), (5, 1, (2, 2, 2, 2))])
 def test_dwconv_se(cuda, lib, dt, k, s, pad, c):
     """Depthwise + BN + swish + SE squeeze, SE FCs and the gate multiply (App. A.3 of SURVEY.md)."""
@@ -183,7 +183,14 @@ def test_dwconv_se(cuda, lib, dt, k, s, pad, c):
     scale, shift = (0.5 + torch.rand(c, generator=g)).to(cuda), (0.2 * torch.randn(c, generator=g)).to(cuda)
     w1, b1 = torch.randn(csq, c, generator=g).to(cuda) / c ** 0.5, 0.1 * torch.randn(csq, generator=g).to(cuda)
     w2, b2 = torch.randn(c, csq, generator=g).to(cuda) / csq ** 0.5, 0.1 * torch.randn(c, generator=g).to(cuda)
-    if dt == A.BF16X2:
+    dw_dt = dt
+    if dt == A.F32_TO_BF16X2:                        # fp32 lanes in (as an MBConv expand conv writes them), split bf16 out
+        xin = nhwc(x, c_p, A.F32)
+        x_eff = x
+        y = torch.zeros(n, oh, ow, 2 * c_p, device=cuda, dtype=torch.bfloat16)
+        z = torch.zeros_like(y)
+        dt = A.BF16X2                                # everything downstream of the depthwise conv is split bf16
+    elif dt == A.BF16X2:
         xin = split_store(nhwc(x, c_p, A.F32))
         x_eff = split_load(xin, c_p)[..., :c].permute(0, 3, 1, 2)
         y = torch.zeros(n, oh, ow, 2 * c_p, device=cuda, dtype=torch.bfloat16)
@@ -200,7 +207,7 @@ def test_dwconv_se(cuda, lib, dt, k, s, pad, c):
     pool = torch.zeros(n, c_p, device=cuda)
     a = A.EdeDwConv(x=xin.data_ptr(), y=y.data_ptr(), w=wk.data_ptr(), scale=sc.data_ptr(), shift=sf.data_ptr(),
                     pool_sum=pool.data_ptr(), n=n, h=h, w_=w, c_p=c_p, x_cs=c_p, x_co=0, oh=oh, ow=ow, y_cs=c_p,
-                    y_co=0, k=k, s=s, pt=pt, pl=pl, act=A.ACT_SWISH, dtype=dt)
+                    y_co=0, k=k, s=s, pt=pt, pl=pl, act=A.ACT_SWISH, dtype=dw_dt)
     A.check(lib.ede_dwconv2d(C.byref(a), stream()), "ede_dwconv2d")
     w1p = torch.zeros(csq, c_p, device=cuda); w1p[:, :c] = w1
     w2p = torch.zeros(c_p, csq, device=cuda); w2p[:c] = w2

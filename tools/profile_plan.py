@@ -17,7 +17,7 @@ from efficientdepthestimation_b200 import engine, factory      # noqa: E402
 
 
 def op_bytes(kind, st):
-    es = {A.F32: 4, A.BF16: 2, A.BF16X2: 4}
+    es = {A.F32: 4, A.BF16: 2, A.BF16X2: 4, A.F32_TO_BF16X2: 4}
     if kind == A.OP_CONV:
         # x_dtype is plain bf16 with doubled lanes for split inputs, so cin_p * 2 B is right either way
         return st.n * st.h * st.w * st.cin_p * es[st.x_dtype] + st.n * st.oh * st.ow * st.cout_p * es[st.y_dtype] * (
