@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libede_sm100.so")
 
 F32, BF16, BF16X2 = 0, 1, 2
-F32_TO_BF16X2 = 3      # EdeDwConv.dtype only: fp32 lanes in, split-bf16 lanes out
+F32_TO_BF16X2 = 3      # EdeDwConv.dtype / EdeSeScale.dtype only: fp32 lanes in, split-bf16 lanes out
 ACT_NONE, ACT_RELU, ACT_SWISH, ACT_SIGMOID = 0, 1, 2, 3
 NHWC, NCHW = 0, 1
 (OP_CONV, OP_DWCONV, OP_SE_FC, OP_SE_SCALE, OP_RESIZE, OP_MAXPOOL, OP_ELTWISE, OP_TO_NHWC, OP_TO_NCHW,

@@ -452,7 +452,7 @@ int ede_se_scale(const EdeSeScale* a, void* stream) {
     EDE_REQUIRE(a && a->x && a->y && a->gate, "ede_se_scale: null argument");
     EDE_REQUIRE(((a->c_p | a->x_cs | a->x_co | a->y_cs | a->y_co) & 7) == 0, "ede_se_scale: channel counts must be multiples of 8");
     const long long total = (long long)a->n * a->hw * (a->c_p >> 3);
-    EDE_DISPATCH_DTYPE(a->dtype, T, ((void)launch_pdl(se_scale_kernel<T>, dim3(grid_persistent(total, 256)), dim3(256), 0, (cudaStream_t)stream, *a)));
+    EDE_DISPATCH_DTYPE_DW(a->dtype, T, ((void)launch_pdl(se_scale_kernel<T>, dim3(grid_persistent(total, 256)), dim3(256), 0, (cudaStream_t)stream, *a)));
     EDE_LAUNCH_CHECK("se_scale_kernel");
     return EDE_OK;
 }

@@ -101,9 +101,16 @@ class MBConvBlock(EdeModule, nn.Module):
             # kernel does not recombine (EDE_F32_TO_BF16X2)
             h = g.conv_bn_act(h, self._expand_conv, self._bn0, A.ACT_SWISH, tag=tag + ".expand",
                               out_dtype=A.F32 if g.expand_f32() else None, hi_lo=g.expand_f32())
-        h, pool = g.dwconv_bn_act(h, self._depthwise_conv, self._bn1, A.ACT_SWISH, pool=True, tag=tag + ".dw")
+        # where the gate is a separate multiply (late blocks), the depthwise output stays fp32 up to it as well
+        dw = self._depthwise_conv
+        s, k = dw.stride[0], dw.kernel_size[0]
+        pl, pr, pt, pb = dw.static_pad
+        oh, ow = (h.h + pt + pb - k) // s + 1, (h.w + pl + pr - k) // s + 1
+        fold = g.se_fold_pays_dims(oh, ow, h.c_p, g.act_dtype, self._cfg["cout"])
+        h, pool = g.dwconv_bn_act(h, dw, self._bn1, A.ACT_SWISH, pool=True, tag=tag + ".dw",
+                                  out_f32=g.expand_f32() and not fold and h.dtype == A.F32)
         res = x if self._id_skip else None
-        if g.se_fold_pays(h, self._cfg["cout"]):
+        if fold:
             # (h * gate) . W == h . (gate * W): no pass over the expanded tensor, the gate rides in per-image weights
             h, fold = g.se_gate(h, pool, self._se_reduce, self._se_expand, tag=tag + ".se", fold=True)
             return g.conv_bn_act(h, self._project_conv, self._bn2, A.ACT_NONE, res=res, tag=tag + ".project", se_fold=fold)

@@ -435,8 +435,9 @@ class Graph:
         return self.conv(x, [(conv.weight, bn, conv.bias, act != A.ACT_NONE)], conv.stride[0], _pad4(conv), act,
                          res, out, relu_in, out_dtype, tag, se_fold=se_fold, hi_lo=hi_lo)
 
-    def dwconv_bn_act(self, x: View, conv, bn, act, pool: bool, tag="dwconv"):
-        """Depthwise conv + BN + activation; with pool=True also the per-(n,c) sums for SE."""
+    def dwconv_bn_act(self, x: View, conv, bn, act, pool: bool, tag="dwconv", out_f32=False):
+        """Depthwise conv + BN + activation; with pool=True also the per-(n,c) sums for SE.  out_f32: an fp32 input stays
+        fp32 on the way out (the consumer is the gate multiply, which writes the split lanes the project conv reads)."""
         k, s = conv.kernel_size[0], conv.stride[0]
         pt, pl, pb, pr = _pad4(conv)
         oh, ow = (x.h + pt + pb - k) // s + 1, (x.w + pl + pr - k) // s + 1
@@ -444,7 +445,7 @@ class Graph:
         if conv.groups != c or int(conv.weight.shape[0]) != c:
             raise RuntimeError(f"{tag}: not a depthwise convolution over {c} channels")
         # fp32 lanes in / split-bf16 lanes out (EDE_F32_TO_BF16X2) when the producer wrote fp32 inside a split-precision scope
-        mixed = x.dtype == A.F32 and self.act_dtype == A.BF16X2
+        mixed = x.dtype == A.F32 and self.act_dtype == A.BF16X2 and not out_f32
         out = View(self.new_buf(x.n, oh, ow, x.c_p, A.BF16X2 if mixed else x.dtype), 0, x.lanes)
         wt = _cpu(conv.weight).float().reshape(c, k * k).t()               # [k*k][c]
         w = torch.zeros(k * k, x.c_p, dtype=torch.float32)
@@ -479,12 +480,15 @@ class Graph:
         """Fold the gate into the consumer's weights (one scaled weight set per image) instead of a full read + write
         of the gated tensor?  Pays while the per-image weights are much smaller than the tensor: the early, high-
         resolution MBConv blocks.  tcgen05 path only."""
+        return self.se_fold_pays_dims(x.h, x.w, x.c_p, x.dtype, cout)
+
+    def se_fold_pays_dims(self, h: int, w: int, c_p: int, dtype: int, cout: int) -> bool:
         if not _SE_FOLD or self.precision != "bf16" or self.dry_no_lib:
             return False
-        mul = 2 if x.dtype == A.BF16X2 else 1
+        mul = 2 if dtype == A.BF16X2 else 1
         passes = 2 if self.act_dtype == A.BF16X2 else 1
-        w_bytes = passes * P.ceil_to(P.ceil8(cout), 16) * P.ceil_to(x.c_p * mul, 64) * 2
-        return 8 * w_bytes <= x.h * x.w * x.c_p * _ELT[x.dtype]
+        w_bytes = passes * P.ceil_to(P.ceil8(cout), 16) * P.ceil_to(c_p * mul, 64) * 2
+        return 8 * w_bytes <= h * w * c_p * _ELT[dtype]
 
     def se_gate(self, x: View, pool_t, reduce_conv, expand_conv, tag="se", fold=False):
         """Squeeze-excite: gate = sigmoid(W2 swish(W1 mean + b1) + b2); returns x * gate -- or, with fold=True,
@@ -509,9 +513,11 @@ class Graph:
                   [("pool_sum", pool_t), ("w1", w1), ("b1", b1), ("w2", w2), ("b2", b2), ("gate", gate)])
         if fold:
             return x, dict(st=st, gate=gate)
-        out = View(self.new_buf(x.n, x.h, x.w, x.c_p, x.dtype), 0, x.lanes)
+        mixed = x.dtype == A.F32 and self.act_dtype == A.BF16X2          # fp32 from the depthwise kernel -> split lanes
+        out = View(self.new_buf(x.n, x.h, x.w, x.c_p, A.BF16X2 if mixed else x.dtype), 0, x.lanes)
         st = A.EdeSeScale(x=None, y=None, gate=None, n=x.n, hw=x.h * x.w, c_p=x.c_p,
-                          x_cs=x.buf.cs, x_co=x.co, y_cs=out.buf.cs, y_co=out.co, dtype=x.dtype)
+                          x_cs=x.buf.cs, x_co=x.co, y_cs=out.buf.cs, y_co=out.co,
+                          dtype=A.F32_TO_BF16X2 if mixed else x.dtype)
         self._add(A.OP_SE_SCALE, st, [("x", x.buf), ("y", out.buf)], tag + ".scale", [("gate", gate)])
         return out
 

@@ -34,7 +34,8 @@ extern "C" {
 #define EDE_ABI_VERSION 12
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2,
-       EDE_F32_TO_BF16X2 = 3 };   /* EdeDwConv.dtype only: x lanes are fp32, y lanes split bf16 (same 4 bytes per lane) */
+       EDE_F32_TO_BF16X2 = 3 };   /* EdeDwConv.dtype / EdeSeScale.dtype only: x lanes are fp32, y lanes split bf16 (same
+                                     4 bytes per lane) */
 enum { EDE_ACT_NONE = 0, EDE_ACT_RELU = 1, EDE_ACT_SWISH = 2, EDE_ACT_SIGMOID = 3 };
 enum { EDE_OK = 0, EDE_E_ARG = -1, EDE_E_CUDA = -2, EDE_E_UNSUPPORTED = -3, EDE_E_DRIVER = -4 };
 enum { EDE_NHWC = 0, EDE_NCHW = 1 };

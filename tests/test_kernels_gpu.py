@@ -553,3 +553,23 @@ def test_upconv_streaming_form_matches_the_separable_form(cuda, lib, shape):
     torch.cuda.synchronize()
     assert not torch.isnan(ys[1]).any()
     assert torch.allclose(ys[0], ys[1], rtol=1e-5, atol=2e-5), float((ys[0] - ys[1]).abs().max())
+
+
+def test_se_scale_fp32_in_split_out(cuda, lib):
+    """ede_se_scale with EDE_F32_TO_BF16X2: the gate multiply reads the depthwise kernel's fp32 lanes and writes the split
+    lanes the project conv consumes (late MBConv blocks, where the gate is not folded into the weights)."""
+    g = torch.Generator().manual_seed(5)
+    n, hw, c, c_p = 3, 63, 44, 48
+    x = torch.zeros(n, hw, c_p)
+    x[..., :c] = torch.randn(n, hw, c, generator=g)
+    gate = torch.zeros(n, c_p)
+    gate[:, :c] = torch.rand(n, c, generator=g)
+    xd, gd = x.to(cuda), gate.to(cuda)
+    y = torch.full((n, hw, 2 * c_p), float("nan"), device=cuda, dtype=torch.bfloat16)
+    a = A.EdeSeScale(x=xd.data_ptr(), y=y.data_ptr(), gate=gd.data_ptr(), n=n, hw=hw, c_p=c_p, x_cs=c_p, x_co=0,
+                     y_cs=c_p, y_co=0, dtype=A.F32_TO_BF16X2)
+    A.check(lib.ede_se_scale(C.byref(a), stream()), "ede_se_scale")
+    torch.cuda.synchronize()
+    got = split_load(y.view(n, hw, 1, 2 * c_p), c_p).view(n, hw, c_p).cpu()
+    ref = x * gate.view(n, 1, c_p)
+    assert bool(((got - ref).abs() <= 2e-5 * ref.abs() + 1e-7).all()), float((got - ref).abs().max())

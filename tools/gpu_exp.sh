@@ -1,2 +1,5 @@
 #!/bin/bash
-timeout 2400 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+timeout 900 python -m pytest tests/test_kernels_gpu.py -m gpu -q -x -k "dwconv or se_scale" 2>&1 | tail -2
+timeout 900 python -m pytest tests/test_model_parity_gpu.py tests/test_config_parity_gpu.py -m gpu -q -x 2>&1 | tail -2
+timeout 300 python tools/profile_plan.py enb0-hu 64 --top 140 > gpurun_out/exp_plan.log 2>&1; head -2 gpurun_out/exp_plan.log | cut -c1-200
+timeout 300 python tools/profile_plan.py enb4-hu 32 --top 10 2>&1 | head -2 | cut -c1-200
