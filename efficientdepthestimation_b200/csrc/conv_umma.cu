@@ -577,7 +577,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                     if (leader) tc_commit(acc_full(acc_st));
                     if (++acc_st == 2) { acc_st = 0; acc_ph ^= 1; }
                 }
-            } else
+            } else {
+            const int pass_group = p.b_group;
+            const uint32_t pass_tap16 = (uint32_t)p.b_tx_bytes >> 4;
             for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
                 const long long ca = prof ? clock64() : 0;
                 mbar_wait(acc_empty(acc_st), acc_ph ^ 1);                // epilogue has drained this accumulator stage
@@ -591,29 +593,33 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                     if (a_mode == 0) mbar_wait(a_full(a_st), a_ph);
                     uint32_t shift16 = 0;
                     int kx = 0, tap_in_pass = 0;
-                    for (int tap = 0; tap < taps; ++tap) {
+                    // a weight stage holds pass_group tiles that share ONE pixel box: 1, or 2 = [w_hi ; w_lo] of a 1x1 conv
+                    for (int tap = 0; tap < taps; tap += pass_group) {
                         const long long c0 = prof ? clock64() : 0;
                         if (a_mode != 0) mbar_wait(a_full(a_st), a_ph);
                         mbar_wait(b_full(b_st), b_ph);
                         if (prof) w_ops += clock64() - c0;
                         tc_fence_after();
-                        const uint32_t a0 = a_cur + shift16, b0 = b_cur;
+                        const uint32_t a0 = a_cur + shift16;
                         if (leader) {
-                            if (swap) {
-                                // D[cout lanes][pixel columns] += W[128 x 16] . X[n_cols x 16]^T
-                                tc_mma_bf16_w(d_base, b0, a0, desc_hi, idesc, accum);
-                                if (ks > 1) tc_mma_bf16_w(d_base, b0 + 2u, a0 + 2u, desc_hi, idesc, 1u);
-                                if (ks > 2) tc_mma_bf16_w(d_base, b0 + 4u, a0 + 4u, desc_hi, idesc, 1u);
-                                if (ks > 3) tc_mma_bf16_w(d_base, b0 + 6u, a0 + 6u, desc_hi, idesc, 1u);
-                            } else {
-                                uint32_t am = a0, dm = d_base;
-                                for (int m = 0; m < m_tiles; ++m) {
-                                    tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, accum);
-                                    if (ks > 1) tc_mma_bf16_w(dm, am + 2u, b0 + 2u, desc_hi, idesc, 1u);
-                                    if (ks > 2) tc_mma_bf16_w(dm, am + 4u, b0 + 4u, desc_hi, idesc, 1u);
-                                    if (ks > 3) tc_mma_bf16_w(dm, am + 6u, b0 + 6u, desc_hi, idesc, 1u);
-                                    am += m_step16;
-                                    dm += (uint32_t)n_pad;
+                            uint32_t acc_flag = accum, b0 = b_cur;
+                            for (int t = 0; t < pass_group; ++t, b0 += pass_tap16, acc_flag = 1u) {
+                                if (swap) {
+                                    // D[cout lanes][pixel columns] += W[128 x 16] . X[n_cols x 16]^T
+                                    tc_mma_bf16_w(d_base, b0, a0, desc_hi, idesc, acc_flag);
+                                    if (ks > 1) tc_mma_bf16_w(d_base, b0 + 2u, a0 + 2u, desc_hi, idesc, 1u);
+                                    if (ks > 2) tc_mma_bf16_w(d_base, b0 + 4u, a0 + 4u, desc_hi, idesc, 1u);
+                                    if (ks > 3) tc_mma_bf16_w(d_base, b0 + 6u, a0 + 6u, desc_hi, idesc, 1u);
+                                } else {
+                                    uint32_t am = a0, dm = d_base;
+                                    for (int m = 0; m < m_tiles; ++m) {
+                                        tc_mma_bf16_w(dm, am, b0, desc_hi, idesc, acc_flag);
+                                        if (ks > 1) tc_mma_bf16_w(dm, am + 2u, b0 + 2u, desc_hi, idesc, 1u);
+                                        if (ks > 2) tc_mma_bf16_w(dm, am + 4u, b0 + 4u, desc_hi, idesc, 1u);
+                                        if (ks > 3) tc_mma_bf16_w(dm, am + 6u, b0 + 6u, desc_hi, idesc, 1u);
+                                        am += m_step16;
+                                        dm += (uint32_t)n_pad;
+                                    }
                                 }
                             }
                             tc_commit(b_empty(b_st));
@@ -642,6 +648,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) conv_umma_kernel(const __grid_
                 }
                 if (leader) tc_commit(acc_full(acc_st));
                 if (++acc_st == 2) { acc_st = 0; acc_ph ^= 1; }
+            }
             }
             if (p.prof && lane == 0) {
                 unsigned long long* q = p.prof + (size_t)blockIdx.x * 16;
@@ -1339,6 +1346,17 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
         }
     }
     if (best.m_tiles == 0) return;
+    // 1x1 convs with hi + lo weights (per-tap mode): both passes read the SAME pixel box, so a weight stage can hold both
+    // tiles and the box is loaded once per chunk instead of once per pass -- the deep-K convs are bound by TMA ingest
+    // (project 2304 -> 192 @7x9 moved 2 MB per 128-pixel tile: 0.039 -> 0.025 ms).  Applied to the tile the picker
+    // chose, and only where the doubled weight stage still leaves three ring stages (letting the picker re-tile
+    // for it made the shallow-K convs of ResNet-50 slower: more n-tiles).
+    if (best.a_mode == 1 && !best.swap && a.kh * a.kw == 1 && a.w_passes == 2 && best.ck >= 32 &&
+        env_int("EDE_UMMA_SHARE_PASSES", 1) != 0) {
+        const int b2 = 2 * best.n_pad * best.ck * 2;
+        const int st = fit_stages(0, best.a_stage_bytes + b2, 4);
+        if (st >= 3) { best.b_stage_bytes = b2; best.a_stages = best.b_stages = st; }
+    }
     c = best;
     c.eligible = 1;
     if (c.pack_g < 1) c.pack_g = 1;
@@ -1436,8 +1454,11 @@ static int conv_umma_build(const EdeConv& a, const EdeUmmaCfg& c, ConvLaunch& L)
         const int w_rows_box = c.swap ? (c.pack_g > 1 ? 128 : std::min(128, round_up(a.cout_p, 8))) : c.n_pad;
         const int taps_per_mma = (c.pack_g & EDE_PACK_N) ? (c.pack_g & 15) : std::max(1, c.pack_g);
         // taps per weight stage: the stage size the tile picker chose, in units of one tap's box
-        const int b_group = (c.a_mode == 0 && (w_rows_box * c.ck * 2) % 1024 == 0)
-                                ? std::max(1, c.b_stage_bytes / (w_rows_box * c.ck * 2)) : 1;
+        int b_group = (c.a_mode == 0 && (w_rows_box * c.ck * 2) % 1024 == 0)
+                          ? std::max(1, c.b_stage_bytes / (w_rows_box * c.ck * 2)) : 1;
+        // per-tap 1x1 conv with hi + lo weights sharing one pixel box per chunk (umma_config, share_passes)
+        if (c.a_mode == 1 && !c.swap && a.kh * a.kw == 1 && a.w_passes == 2 && c.b_stage_bytes == 2 * w_rows_box * c.ck * 2)
+            b_group = 2;
         p.b_group = b_group;
         cuuint32_t box[3] = {(cuuint32_t)c.ck, (cuuint32_t)w_rows_box, (cuuint32_t)b_group};
         dims[2] = (cuuint64_t)(a.kh * ceil_div(a.kw, taps_per_mma) * a.w_passes);
