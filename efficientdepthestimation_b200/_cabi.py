@@ -77,7 +77,7 @@ class EdeLayout(Structure):
 class EdeUpConv(Structure):
     _fields_ = [("z", c_void_p), ("y", c_void_p), ("scale", c_void_p), ("shift", c_void_p), ("rows", c_void_p)] + _ints(
         "n", "h", "w", "z_cs", "z_co", "oh", "ow", "cgrp", "y_cs", "y_co", "y_dtype", "kh", "kw", "pt", "pl", "act",
-        "act_c_end")
+        "act_c_end", "z_dtype")
 
 
 class EdeStem(Structure):

@@ -19,7 +19,7 @@ template <int K, typename TY>
 __global__ void __launch_bounds__(256) upconv_taps_kernel(const EdeUpConv a, float scale_h, float scale_w) {
     const int ngrp = a.cgrp >> 3;
     const long long total = (long long)a.n * a.oh * a.ow * ngrp;
-    const float* __restrict__ z = a.z;
+    const float* __restrict__ z = reinterpret_cast<const float*>(a.z);
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
         const int c = (int)(i % ngrp) << 3;
@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256) upconv_taps_kernel(const EdeUpConv a, flo
 //   y[n][py][px][c]       = act(scale * sum_ty inside_y(py+ty-pt) * lerp_y(rows[n][.][ty][px][c], py+ty-pt) + shift)
 // Pass 1 runs on the h low-resolution rows only; pass 2 reads 2*K vectors per output instead of 4*K*K.
 // grid = (n * h * K low-resolution (row, tap row) pairs, column blocks): no 64-bit index arithmetic per thread
-template <int K>
+template <int K, typename TZ>
 __global__ void __launch_bounds__(256) upconv_rows_kernel(const EdeUpConv a, float scale_w) {
     const int ngrp = a.cgrp >> 3;
     pdl_trigger();
@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(256) upconv_rows_kernel(const EdeUpConv a, flo
     const int px = t / ngrp, c = (t - px * ngrp) << 3;
     const int r = blockIdx.x;                                // (n * h + y) * K + ty
     const int ny = r / K, ty = r - ny * K;
-    const float* zrow = a.z + (long long)ny * a.w * a.z_cs + a.z_co + ty * K * a.cgrp + c;
+    const TZ* zrow = reinterpret_cast<const TZ*>(a.z) + (long long)ny * a.w * a.z_cs + a.z_co + ty * K * a.cgrp + c;
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
@@ -106,8 +106,8 @@ __global__ void __launch_bounds__(256) upconv_rows_kernel(const EdeUpConv a, flo
         const int x0 = (int)sx, x1 = x0 + (x0 < a.w - 1 ? 1 : 0);
         const float lx = sx - x0, hx = 1.f - lx;
         float v0[8], v1[8];
-        load8<float>(zrow + x0 * a.z_cs + tx * a.cgrp, v0);
-        load8<float>(zrow + x1 * a.z_cs + tx * a.cgrp, v1);
+        load8<TZ>(zrow + x0 * a.z_cs + tx * a.cgrp, v0);
+        load8<TZ>(zrow + x1 * a.z_cs + tx * a.cgrp, v1);
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[j] = fmaf(hx, v0[j], fmaf(lx, v1[j], acc[j]));
     }
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(THREADS, MINB) upconv_stream_kernel(const EdeU
 #pragma unroll
     for (int j = 0; j < V; ++j) { sc[j] = a.scale[c + j]; sf[j] = a.shift[c + j]; }
     const bool activated = c < a.act_c_end;
-    const float* zimg = a.z + (long long)n * a.h * a.w * a.z_cs + a.z_co + c;
+    const float* zimg = reinterpret_cast<const float*>(a.z) + (long long)n * a.h * a.w * a.z_cs + a.z_co + c;
     const int zrow_stride = a.w * a.z_cs;
     // row base of the output pixel (lane 0 of the view) -- store4 wants the row and the lane separately
     TY* yout = reinterpret_cast<TY*>(a.y) + (((long long)n * a.oh + oy0) * a.ow + px) * a.y_cs + a.y_co;
@@ -381,6 +381,8 @@ extern "C" int ede_upconv_taps(const EdeUpConv* a, void* stream) {
                 "ede_upconv_taps: channel counts must be multiples of 8");
     EDE_REQUIRE(a->n > 0 && a->h > 0 && a->w > 0 && a->oh > 0 && a->ow > 0 && a->cgrp > 0, "ede_upconv_taps: bad shape");
     EDE_REQUIRE(a->kh == a->kw && (a->kh == 3 || a->kh == 5), "ede_upconv_taps: only 3x3 and 5x5 taps are supported");
+    EDE_REQUIRE(a->z_dtype == EDE_F32 || (a->z_dtype == EDE_BF16 && a->rows != nullptr),
+                "ede_upconv_taps: z must be fp32, or bf16 with the rows workspace (separable form)");
     const float sh = a->oh > 1 ? (float)(a->h - 1) / (float)(a->oh - 1) : 0.f;
     const float sw = a->ow > 1 ? (float)(a->w - 1) / (float)(a->ow - 1) : 0.f;
     const long long total = (long long)a->n * a->oh * a->ow * (a->cgrp >> 3);
@@ -393,8 +395,13 @@ extern "C" int ede_upconv_taps(const EdeUpConv* a, void* stream) {
         const long long r1 = (long long)a->n * a->h * a->kh;
         EDE_REQUIRE(r1 < 0x7fffffffLL && col_blocks <= 65535u, "ede_upconv_taps: map too large");
         const dim3 g1((unsigned)r1, col_blocks);
-        if (a->kh == 5) (void)launch_pdl(upconv_rows_kernel<5>, g1, dim3(256), 0, st, *a, sw);
-        else (void)launch_pdl(upconv_rows_kernel<3>, g1, dim3(256), 0, st, *a, sw);
+        if (a->z_dtype == EDE_BF16) {
+            if (a->kh == 5) (void)launch_pdl(upconv_rows_kernel<5, __nv_bfloat16>, g1, dim3(256), 0, st, *a, sw);
+            else (void)launch_pdl(upconv_rows_kernel<3, __nv_bfloat16>, g1, dim3(256), 0, st, *a, sw);
+        } else {
+            if (a->kh == 5) (void)launch_pdl(upconv_rows_kernel<5, float>, g1, dim3(256), 0, st, *a, sw);
+            else (void)launch_pdl(upconv_rows_kernel<3, float>, g1, dim3(256), 0, st, *a, sw);
+        }
         EDE_LAUNCH_CHECK("upconv_rows_kernel");
         // output rows per thread: 4 when the map is upsampled >= 3x (three low-res rows cover a band), else 2
         const int R = sh <= 1.f / 3.f ? 4 : 2;

@@ -551,7 +551,11 @@ class Graph:
         wz = wz.permute(2, 3, 0, 1).reshape(k * k * cgrp, cin, 1, 1)       # lanes [(ty*k+tx)*cgrp + c]
         prev = self.count_ref_flops
         self.count_ref_flops = False
-        z = self.conv(x, [(wz, None, None, False)], 1, (0, 0, 0, 0), A.ACT_NONE, out_dtype=A.F32, tag=tag + ".z_gemm")
+        # z is the largest tensor of the op (25 taps x cgrp lanes per low-resolution pixel): bf16 halves what the GEMM
+        # writes and the gather reads; the sums of the gather stay fp32 (EDE_UPCONV_Z_BF16=0: fp32 z)
+        z_dtype = A.BF16 if (self.precision == "bf16" and os.environ.get("EDE_UPCONV_Z_BF16", "1") != "0"
+                             and os.environ.get("EDE_UPCONV_ROWS", "1") != "0" and x.h < oh) else A.F32
+        z = self.conv(x, [(wz, None, None, False)], 1, (0, 0, 0, 0), A.ACT_NONE, out_dtype=z_dtype, tag=tag + ".z_gemm")
         self.count_ref_flops = prev
         out = View(self.new_buf(x.n, oh, ow, cgrp, self.decoder_dtype if self.act_dtype != A.F32 else A.F32), 0, out_lanes)
         scale, shift = self._dev(torch.cat(scales)), self._dev(torch.cat(shifts))
@@ -563,7 +567,7 @@ class Graph:
             bufs.append(("rows", self.new_buf(x.n, x.h, k * ow, cgrp, A.F32)))
         st = A.EdeUpConv(z=None, y=None, scale=None, shift=None, rows=None, n=x.n, h=x.h, w=x.w,
                          z_cs=z.buf.cs, z_co=z.co, oh=oh, ow=ow, cgrp=cgrp, y_cs=out.buf.cs, y_co=out.co,
-                         y_dtype=out.dtype, kh=k, kw=k, pt=pad[0], pl=pad[1], act=act, act_c_end=act_end)
+                         y_dtype=out.dtype, kh=k, kw=k, pt=pad[0], pl=pad[1], act=act, act_c_end=act_end, z_dtype=z_dtype)
         self._add(A.OP_UPCONV, st, bufs, tag + ".taps",
                   [("scale", scale), ("shift", shift)])
         self.exec_flops += 2.0 * x.n * oh * ow * cgrp * k * k * 4

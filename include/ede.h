@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EDE_ABI_VERSION 12
+#define EDE_ABI_VERSION 13
 
 enum { EDE_F32 = 0, EDE_BF16 = 1, EDE_BF16X2 = 2,
        EDE_F32_TO_BF16X2 = 3 };   /* EdeDwConv.dtype / EdeSeScale.dtype only: x lanes are fp32, y lanes split bf16 (same
@@ -191,15 +191,17 @@ int ede_resize_planes_f32(const float* x, float* y, int64_t planes, int32_t h, i
 /* Tap gather of "conv(k x k, stride 1) of a bilinearly upsampled map" evaluated on the low-resolution grid.
  * replaces: F.interpolate(x, size, 'bilinear', align_corners=True) followed by conv1/conv2 of _UpProjection
  *   (ReSIDE/models/modules.py:34-37) where the projection is narrow (MFF, modules.py:259-263).
- * z: fp32 NHWC [n,h,w], lanes [(ty*kw+tx)*cgrp + c] = (W_tap x)[c], produced by ede_conv2d as a 1x1 GEMM.
+ * z: NHWC [n,h,w] of z_dtype (EDE_F32, or EDE_BF16 with the `rows` workspace: half the bytes of the largest tensor of the
+ *   op), lanes [(ty*kw+tx)*cgrp + c] = (W_tap x)[c], produced by ede_conv2d as a 1x1 GEMM.
  *   y[n,oy,ox,c] = act_c( scale[c] * sum_taps inside(oy+ty-pt, ox+tx-pl) * bilinear_ac(z[.., tap, c])(oy+ty-pt, ox+tx-pl)
  *                         + shift[c] ),  act applied to lanes c < act_c_end.
  * rows: optional fp32 workspace [n][h][kh][ow][cgrp]; when given the gather runs in its separable form (x-lerp of
  *   every tap on the h low-resolution rows into `rows`, then the y-lerp), NULL = one-pass 4-corner gather. */
 typedef struct EdeUpConv {
-    const float* z; void* y; const float* scale; const float* shift; float* rows;
+    const void* z; void* y; const float* scale; const float* shift; float* rows;
     int32_t n, h, w, z_cs, z_co, oh, ow, cgrp, y_cs, y_co, y_dtype;
     int32_t kh, kw, pt, pl, act, act_c_end;
+    int32_t z_dtype;        /* EDE_F32 (0, default) or EDE_BF16 */
 } EdeUpConv;
 int ede_upconv_taps(const EdeUpConv* a, void* stream);
 

@@ -24,7 +24,7 @@ def test_header_symbols_are_exported(lib):
 
 
 def test_version_and_error_plumbing(lib):
-    assert lib.ede_version() == 12
+    assert lib.ede_version() == 13
     assert lib.ede_fill_zero(None, -1, None) == -1            # EDE_E_ARG, no GPU touched
     assert b"ede_fill_zero" in lib.ede_last_error()
     assert lib.ede_plan_run(None, 0, None) == 0

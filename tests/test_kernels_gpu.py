@@ -414,10 +414,15 @@ def test_loss_full_size_properties(cuda, lib):
                                                     ((57, 76), (114, 152), 24, (16, 16), False),
                                                     ((14, 19), (57, 76), 40, (8, 8), True),
                                                     ((3, 4), (9, 7), 16, (8,), False)])
-def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, split):
+@pytest.mark.parametrize("z_bf16", [0, 1])
+def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, split, z_bf16, monkeypatch):
     """engine.Graph.upconv (1x1 GEMM on the low-res grid + ede_upconv_taps) == relu/bn(conv5x5(bilinear_ac(x)))
-    as _UpProjection computes it (modules.py:34-37): every tap, border and non-integer ratio (8->114)."""
+    as _UpProjection computes it (modules.py:34-37): every tap, border and non-integer ratio (8->114).
+    z_bf16 = 0: the per-tap products z stay fp32 (error = bf16 weights + bf16 output only); 1 (the plans' default): z is
+    stored as bf16 -- every one of the 25 tap terms carries a 2^-9 rounding and the terms cancel in the sum, so the
+    bound is set against the magnitude of the terms, not of the result (model-level effect: 3.29e-3 -> 3.34e-3)."""
     from efficientdepthestimation_b200 import engine
+    monkeypatch.setenv("EDE_UPCONV_Z_BF16", str(z_bf16))
     g = torch.Generator().manual_seed(hw[0] * 31 + cin)
     n, (h, w), (oh, ow) = 2, hw, ohw
     x = torch.randn(n, cin, h, w, generator=g)
@@ -452,7 +457,8 @@ def test_upconv_lowres_equals_conv_of_upsampled(cuda, lib, hw, ohw, cin, couts, 
     got = y.cpu()
     assert got.shape == ref.shape
     # output stored as bf16 (2^-9) on top of bf16 weights (identical on both sides)
-    assert bool(((got - ref).abs() <= 5e-3 * ref.abs() + 5e-3).all()), float((got - ref).abs().max())
+    atol = 5e-3 if not z_bf16 else 5e-3 + 2.0 ** -9 * 5.0 * float(ref.abs().max())     # 25 terms, each <= ~max|ref|
+    assert bool(((got - ref).abs() <= 5e-3 * ref.abs() + atol).all()), float((got - ref).abs().max())
 
 
 @pytest.mark.parametrize("cout,cin,k,passes,pack_g,use_maps,use_bn,use_bias", [
