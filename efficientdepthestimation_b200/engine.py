@@ -848,7 +848,13 @@ def emit(module, g: Graph, *args, **kw):
                 bn = mods[i + 1] if i + 1 < len(mods) and isinstance(mods[i + 1], nn.BatchNorm2d) else None
                 j = i + (2 if bn is not None else 1)
                 relu = j < len(mods) and isinstance(mods[j], nn.ReLU)
-                x = g.conv_bn_act(x, m, bn, A.ACT_RELU if relu else A.ACT_NONE, tag=f"seq.{i}")
+                nxt = mods[j + (1 if relu else 0)] if j + (1 if relu else 0) < len(mods) else None
+                # EfficientNet stem -> first MBConv block (expand ratio 1: its first op is the depthwise kernel, a
+                # CUDA-core consumer): fp32 lanes instead of split bf16, as between an expand conv and its depthwise conv
+                f32 = (g.expand_f32() and nxt is not None and getattr(nxt, "_cfg", {}).get("expand") == 1
+                       and hasattr(nxt, "_depthwise_conv"))
+                x = g.conv_bn_act(x, m, bn, A.ACT_RELU if relu else A.ACT_NONE, tag=f"seq.{i}",
+                                  out_dtype=A.F32 if f32 else None, hi_lo=f32)
                 i = j + (1 if relu else 0)
                 continue
             if isinstance(m, nn.MaxPool2d):
