@@ -497,7 +497,7 @@ extern "C" int ede_tapsum(const EdeTapSum* a, void* stream) {
     EDE_REQUIRE(((a->z_cs | a->z_co | a->y_cs | a->y_co) & 7) == 0, "ede_tapsum: channel strides must be multiples of 8");
     EDE_REQUIRE(a->n > 0 && a->n <= 65535 && a->h > 0 && a->w > 0 && a->kh > 0 && a->kw > 0 && a->kh * a->kw <= a->z_cs,
                 "ede_tapsum: bad shape");
-    EDE_REQUIRE(a->kh <= 8 && a->kw <= 8, "ede_tapsum: kernel larger than 8x8");
+    EDE_REQUIRE(a->kh * a->kw <= 32, "ede_tapsum: more than 32 taps (a block stages 8 float4 lanes per pixel)");
     const dim3 grid((unsigned)ceil_div(a->w, ede::TS_TW), (unsigned)ceil_div(a->h, ede::TS_TH), (unsigned)a->n);
     const size_t smem = (size_t)(ede::TS_TH + a->kh - 1) * (ede::TS_TW + a->kw - 1) * ((a->kh * a->kw) | 1) * sizeof(float);
     EDE_DISPATCH_DTYPE(a->y_dtype, TY, {

@@ -270,7 +270,7 @@ class Graph:
         cin = x.c
         if (_TAPSUM and self.precision == "bf16" and len(parts) == 1 and int(parts[0][0].shape[0]) == 1 and kh * kw >= 9
                 and kh * kw <= 32 and stride == 1 and res is None and not relu_in and (oh, ow) == (x.h, x.w)
-                and x.dtype != A.F32 and not tag.endswith(".z_gemm")):
+                and x.dtype != A.F32 and not tag.endswith(".z_gemm") and not self._npack_takes(x, 8, kh, kw, pad)):
             return self._conv_one_channel(x, parts[0], pad, act, out, out_dtype, tag)
         # a split-bf16 input is consumed as a plain bf16 tensor with twice the lanes (include/ede.h)
         split_in = x.dtype == A.BF16X2
@@ -356,6 +356,20 @@ class Graph:
         self._add(A.OP_CONV, st, refs, tag, [("scale", scale), ("shift", shift), ("w_umma", w_used),
                                              ("w_direct", job["w_direct"])])
         return out
+
+    def _npack_takes(self, x: View, cout_p: int, kh: int, kw: int, pad) -> bool:
+        """Would the tile picker run this stride-1 conv in conv_npack_kernel (taps of a kernel row on the UMMA N axis)?
+        For one output channel that beats the 1x1 GEMM + tap sum (R.conv2 of ENB0-HU batch 64: 0.101 ms against
+        0.062 + 0.072): the tap products never leave TMEM."""
+        if self.dry_no_lib or x.dtype == A.BF16X2:
+            return False
+        st = A.EdeConv(x=1, y=1, res=None, scale=1, shift=1, w_umma=1, w_direct=None, n=x.n, h=x.h, w=x.w, cin_p=x.c_p,
+                       x_cs=x.buf.cs, x_co=x.co, oh=x.h, ow=x.w, cout_p=cout_p, y_cs=cout_p, y_co=0, res_cs=0, res_co=0,
+                       kh=kh, kw=kw, sh=1, sw=1, pt=pad[0], pl=pad[1], act=A.ACT_NONE, act_c_end=0, x_dtype=x.dtype,
+                       y_dtype=A.F32, x_layout=A.NHWC, relu_in=0, w_umma_cout_p=P.ceil_to(cout_p, 16),
+                       w_umma_cin_p=P.ceil_to(x.c_p, 64), force_direct=0, w_passes=1, w_pack_g=-1, w_per_image=0)
+        cfg = A.umma_config(st)
+        return bool(cfg.eligible) and bool(cfg.pack_g & P.PACK_N)
 
     def _conv_one_channel(self, x: View, part, pad, act, out, out_dtype, tag) -> View:
         """k x k stride-1 conv to ONE channel (R.conv2, modules.py:296): a 128-row MMA would carry one useful row, so

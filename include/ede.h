@@ -222,7 +222,7 @@ int64_t ede_upconv_taps_static_max_bytes(void);
  * replaces: the 5x5 conv to a single channel + bias that ends the Hu decoder (R.conv2, ReSIDE/models/modules.py:285,296).
  * z: fp32 NHWC [n,h,w], lane ty*kw+tx = (W[0,:,ty,tx] . x) at that pixel (a 1x1 GEMM with kh*kw output lanes);
  *   y[n,oy,ox, lane 0] = act(scale[0] * sum_{ty,tx} inside(oy+ty-pt, ox+tx-pl) * z[n, oy+ty-pt, ox+tx-pl, ty*kw+tx] + shift[0]),
- *   lanes 1..7 of the 8-lane output group are written as zeros. */
+ *   lanes 1..7 of the 8-lane output group are written as zeros.  kh*kw <= 32. */
 typedef struct EdeTapSum {
     const float* z; void* y; const float* scale; const float* shift;
     int32_t n, h, w, z_cs, z_co, y_cs, y_co, y_dtype, kh, kw, pt, pl, act;

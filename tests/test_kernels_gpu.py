@@ -579,3 +579,29 @@ def test_se_scale_fp32_in_split_out(cuda, lib):
     got = split_load(y.view(n, hw, 1, 2 * c_p), c_p).view(n, hw, c_p).cpu()
     ref = x * gate.view(n, 1, c_p)
     assert bool(((got - ref).abs() <= 2e-5 * ref.abs() + 1e-7).all()), float((got - ref).abs().max())
+
+
+@pytest.mark.parametrize("k,hw", [(5, (33, 41)), (3, (8, 70)), (5, (114, 152))])
+def test_tapsum_one_channel_conv(cuda, lib, k, hw):
+    """ede_tapsum: y[p] = act(scale * sum_t z[p + offset(t)][t] + shift), taps outside the map contribute zero -- the second
+    half of a k x k conv to ONE channel (R.conv2, modules.py:285,296) after its 1x1 GEMM left the tap products in z."""
+    g = torch.Generator().manual_seed(k)
+    n, (h, w) = 2, hw
+    z_cs = P.ceil8(k * k)
+    z = torch.zeros(n, h, w, z_cs)
+    z[..., :k * k] = torch.randn(n, h, w, k * k, generator=g)
+    zd = z.to(cuda)
+    scale, shift = torch.tensor([1.7] + [0.0] * 7).to(cuda), torch.tensor([-0.3] + [0.0] * 7).to(cuda)
+    y = torch.full((n, h, w, 8), float("nan"), device=cuda)
+    a = A.EdeTapSum(z=zd.data_ptr(), y=y.data_ptr(), scale=scale.data_ptr(), shift=shift.data_ptr(), n=n, h=h, w=w,
+                    z_cs=z_cs, z_co=0, y_cs=8, y_co=0, y_dtype=A.F32, kh=k, kw=k, pt=k // 2, pl=k // 2, act=A.ACT_RELU)
+    A.check(lib.ede_tapsum(C.byref(a), stream()), "ede_tapsum")
+    torch.cuda.synchronize()
+    zp = F.pad(z[..., :k * k].permute(0, 3, 1, 2), (k // 2,) * 4)          # [n, taps, h + k - 1, w + k - 1]
+    ref = sum(zp[:, ty * k + tx, ty:ty + h, tx:tx + w] for ty in range(k) for tx in range(k))
+    ref = torch.relu(1.7 * ref - 0.3)
+    got = y.cpu()
+    assert torch.allclose(got[..., 0], ref, rtol=1e-5, atol=1e-5), float((got[..., 0] - ref).abs().max())
+    assert float(got[..., 1:].abs().sum()) == 0.0
+    a.kh = a.kw = 7                                      # 49 taps: more than z holds / a block stages per pixel
+    assert lib.ede_tapsum(C.byref(a), stream()) == -1
