@@ -1,5 +1,3 @@
 #!/bin/bash
-timeout 600 python bench.py --arch rn50-hu --batch 64 --quick --steps 40 2>/dev/null | tail -1 | python -c "
-import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['clocks'])"
-timeout 600 python bench.py --quick --steps 40 2>/dev/null | tail -1 | python -c "
-import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['clocks'])"
+timeout 300 python tools/profile_plan.py enb4-hu 32 --top 45 > gpurun_out/exp_plan_enb4.log 2>&1
+timeout 300 python tools/profile_plan.py enb4-lr 8 --top 45 > gpurun_out/exp_plan_enb4lr.log 2>&1
