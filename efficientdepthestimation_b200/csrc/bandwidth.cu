@@ -4,6 +4,8 @@
 // channel-group index fastest across a warp so that global accesses are fully coalesced.
 #include <stdlib.h>
 
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace ede {
@@ -161,6 +163,109 @@ __global__ void __launch_bounds__(1024) se_fc_kernel(const EdeSeFc a) {
             for (int q = 0; q < 4; ++q) {
                 const float g0 = lane + 2 * q < a.c_p ? mean[lane + 2 * q] : 0.f;
                 const float g1 = lane + 2 * q + 1 < a.c_p ? mean[lane + 2 * q + 1] : 0.f;
+                const float v0 = (bf16lo_f(hw[q]) + bf16lo_f(lw[q])) * g0, v1 = (bf16hi_f(hw[q]) + bf16hi_f(lw[q])) * g1;
+                const __nv_bfloat162 hh = __floats2bfloat162_rn(v0, v1);
+                oh[q] = *reinterpret_cast<const uint32_t*>(&hh);
+                const __nv_bfloat162 ll = __floats2bfloat162_rn(v0 - bf16lo_f(oh[q]), v1 - bf16hi_f(oh[q]));
+                ol[q] = *reinterpret_cast<const uint32_t*>(&ll);
+            }
+            dst[e] = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+            if (a.w_passes == 2) dst[lo_off + e] = make_uint4(ol[0], ol[1], ol[2], ol[3]);
+        }
+    }
+}
+
+// The same op across a thread-block CLUSTER of B CTAs per image.  One block per image leaves most of the machine idle
+// at the batch sizes of the BASELINE configs (8..64 blocks on 148 SMs) while the two FC phases of the wide EfficientNet-B4
+// stages are 300k MACs each.  Here every CTA of the cluster reads the squeeze vector, the hidden units are split over the
+// CTAs and exchanged through DISTRIBUTED SHARED MEMORY, and the gate channels and the weight fold are split as well;
+// cluster.sync() orders "everybody has read the slabs" before rank 0 clears them and publishes the gate slices that the
+// fold reads back from global memory.  Same arithmetic per output as se_fc_kernel (same summation orders): bit-identical.
+__global__ void __launch_bounds__(1024) se_fc_cluster_kernel(const EdeSeFc a) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const int B = (int)cluster.num_blocks(), rank = (int)cluster.block_rank();
+    extern __shared__ float sm[];                          // mean[c_p] | hid[csq] (own units) | hid_all[csq]
+    float* mean = sm;
+    float* hid = sm + a.c_p;
+    float* hid_all = hid + a.csq;
+    const int n = blockIdx.x / B;
+    pdl_trigger();
+    {
+        // the FC weights fall out of the L2 between forwards: pull this CTA's share in before the dependency wait
+        const char* w1b = reinterpret_cast<const char*>(a.w1);
+        const char* w2b = reinterpret_cast<const char*>(a.w2);
+        const int bytes = a.csq * a.c_p * 4;
+        for (int o = (rank * blockDim.x + threadIdx.x) * 128; o < bytes; o += B * blockDim.x * 128) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(w1b + o));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(w2b + o));
+        }
+        if (a.w_src) {
+            const char* wb = reinterpret_cast<const char*>(a.w_src);
+            const int wbytes = a.w_passes * a.w_rows * a.w_cols * 2;
+            for (int o = (rank * blockDim.x + threadIdx.x) * 128; o < wbytes; o += B * blockDim.x * 128)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(wb + o));
+        }
+    }
+    pdl_wait();
+    const int parts = a.pool_parts > 1 ? a.pool_parts : 1;
+    for (int i = threadIdx.x; i < a.c_p; i += blockDim.x) {
+        float sum = 0.f;
+        for (int s = 0; s < parts; ++s) sum += a.pool_sum[((long long)s * a.n + n) * a.c_p + i];   // slabs in order
+        mean[i] = i < a.c ? sum * a.inv_hw : 0.f;
+    }
+    cluster.sync();                                        // every CTA of the image has read the slabs
+    if (a.clear_pool && rank == 0)
+        for (int i = threadIdx.x; i < a.c_p; i += blockDim.x)
+            for (int s = 0; s < parts; ++s) a.pool_sum[((long long)s * a.n + n) * a.c_p + i] = 0.f;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    for (int j = rank * nw + warp; j < a.csq; j += B * nw) {           // hidden units of this CTA
+        float s = 0.f;
+        for (int c = lane; c < a.c; c += 32) s = fmaf(a.w1[(long long)j * a.c_p + c], mean[c], s);
+        s = warp_sum(s);
+        if (lane == 0) hid[j] = apply_act(s + a.b1[j], EDE_ACT_SWISH);
+    }
+    cluster.sync();                                        // all hidden units exist (release / acquire at cluster scope)
+    for (int j = threadIdx.x; j < a.csq; j += blockDim.x) {
+        const int owner = (j % (B * nw)) / nw;
+        hid_all[j] = cluster.map_shared_rank(hid, owner)[j];           // distributed shared memory read
+    }
+    __syncthreads();
+    const int cs = ((a.c_p + B - 1) / B + 7) & ~7;         // gate channels per CTA
+    const int c_lo = rank * cs, c_hi = min(a.c_p, c_lo + cs);
+    for (int c = c_lo + threadIdx.x; c < c_hi; c += blockDim.x) {
+        float s = 0.f;
+        if (c < a.c) {
+            s = a.b2[c];
+            if (a.w2_transposed) {
+                for (int j = 0; j < a.csq; ++j) s = fmaf(a.w2[(long long)j * a.c_p + c], hid_all[j], s);
+            } else {
+                for (int j = 0; j < a.csq; ++j) s = fmaf(a.w2[(long long)c * a.csq + j], hid_all[j], s);
+            }
+        }
+        a.gate[(long long)n * a.c_p + c] = c < a.c ? apply_act(s, EDE_ACT_SIGMOID) : 0.f;
+    }
+    __threadfence();
+    cluster.sync();                                        // gate slices published; nobody reads remote `hid` after this
+    if (a.w_src) {
+        for (int c = threadIdx.x; c < a.c_p; c += blockDim.x) mean[c] = a.gate[(long long)n * a.c_p + c];
+        __syncthreads();
+        const int rows = a.w_rows, cols8 = a.w_cols >> 3;
+        const uint4* src = reinterpret_cast<const uint4*>(a.w_src);
+        uint4* dst = reinterpret_cast<uint4*>(a.w_dst) + (long long)n * a.w_passes * rows * cols8;
+        const long long lo_off = (long long)rows * cols8;
+        for (int e = rank * blockDim.x + threadIdx.x; e < rows * cols8; e += B * blockDim.x) {
+            const int ci = (e % cols8) << 3;
+            const int lane8 = a.w_split ? ((ci >> 4) << 3) : ci;
+            const uint4 h = src[e];
+            uint4 l = make_uint4(0, 0, 0, 0);
+            if (a.w_passes == 2) l = src[lo_off + e];
+            const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+            uint32_t oh[4], ol[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float g0 = lane8 + 2 * q < a.c_p ? mean[lane8 + 2 * q] : 0.f;
+                const float g1 = lane8 + 2 * q + 1 < a.c_p ? mean[lane8 + 2 * q + 1] : 0.f;
                 const float v0 = (bf16lo_f(hw[q]) + bf16lo_f(lw[q])) * g0, v1 = (bf16hi_f(hw[q]) + bf16hi_f(lw[q])) * g1;
                 const __nv_bfloat162 hh = __floats2bfloat162_rn(v0, v1);
                 oh[q] = *reinterpret_cast<const uint32_t*>(&hh);
@@ -441,6 +546,29 @@ int ede_se_fc(const EdeSeFc* a, void* stream) {
                 "ede_se_fc: bad weight-fold description");
     const size_t smem = (size_t)(a->c_p + a->csq) * sizeof(float);
     EDE_REQUIRE(smem <= 48 * 1024, "ede_se_fc: too many channels (%d)", a->c_p);
+    // A cluster of B CTAs per image where one block per image would leave the machine idle and the FCs are not trivial
+    // (se_fc_cluster_kernel); B = the largest of 8 / 4 / 2 that keeps n * B within two waves.
+    const char* ck_env = getenv("EDE_SE_FC_CLUSTER");      // 0: never; 2 / 4 / 8: force that cluster size (tests)
+    const int cluster_knob = ck_env && *ck_env ? atoi(ck_env) : -1;
+    int B = 1;
+    if (cluster_knob != 0) {
+        const long long macs = 2LL * a->csq * a->c_p + (a->w_src ? (long long)a->w_passes * a->w_rows * a->w_cols / 4 : 0);
+        for (int b = 8; b >= 2; b >>= 1)
+            if ((long long)a->n * b <= 296) { B = b; break; }
+        if (cluster_knob > 0) B = cluster_knob;
+        else if (macs < 200000) B = 1;                       // three cluster barriers cost more than the FCs of the narrower
+                                                             // stages save (measured: all of EfficientNet-B0 at batch 64)
+    }
+    if (B > 1) {
+        const size_t smem_c = (size_t)(a->c_p + 2 * a->csq) * sizeof(float);
+        const cudaError_t e = launch_pdl_cluster(se_fc_cluster_kernel, dim3((unsigned)(a->n * B)), dim3(a->c_p >= 384 || a->w_src ? 1024 : 512),
+                                                 smem_c, (cudaStream_t)stream, (unsigned)B, *a);
+        if (e == cudaSuccess) {
+            EDE_LAUNCH_CHECK("se_fc_cluster_kernel");
+            return EDE_OK;
+        }
+        (void)cudaGetLastError();                            // cluster launch refused: the one-block form below
+    }
     // latency bound (one block per image, three dependent phases): wide blocks for the wide late stages
     (void)launch_pdl(se_fc_kernel, dim3(a->n), dim3(a->c_p >= 384 || a->w_src ? 1024 : 512), smem,
                      (cudaStream_t)stream, *a);

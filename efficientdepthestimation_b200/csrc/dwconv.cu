@@ -89,7 +89,9 @@ struct alignas(64) DwParams {
     int cols;              // consumer warps per block (each owns 64 / CH adjacent output columns)
     int row_bytes;         // bytes of one ring slot: (cols * (64/CH) * S + K - S) pixels x CH lanes
     int tx_bytes;          // bytes one TMA row box delivers (row_bytes before the 128-byte rounding)
-    int zsplit;            // grid.z: a block walks images blockIdx.z, blockIdx.z + zsplit, ...
+    int zsplit;            // grid.z: a block walks (image, row band) units blockIdx.z, blockIdx.z + zsplit, ...
+    int bands, band_oh;    // row bands per image and output rows per band: a walk can start at any output row (it
+                           // re-reads K - S input rows), so small batches of large maps still fill the machine
     int pool_write;        // 1: every column strip stores its squeeze sums into its own slab of pool_sum
 };
 
@@ -121,7 +123,7 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
     const int ow0 = blockIdx.x * p.cols * SUB * NC;
     const int c0 = blockIdx.y * CH;
     const int n_act = min(p.cols, (a.ow - ow0 + SUB * NC - 1) / (SUB * NC));   // consumer warps that own a real output column
-    const int rows_in = (a.oh - 1) * S + K;               // input rows (incl. padding rows) one image's walk touches
+    const int n_units = a.n * p.bands;                    // (image, row band) walks
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < DEPTH; ++s) {
@@ -138,13 +140,17 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
         // ===================== producer: one TMA row per ring slot, images back to back
         if (lane == 0) {
             int g = 0;                                     // rows issued so far (ring position)
-            for (int n = blockIdx.z; n < a.n; n += p.zsplit)
-                for (int ir = 0; ir < rows_in; ++ir, ++g) {
+            for (int v = blockIdx.z; v < n_units; v += p.zsplit) {
+                const int n = v / p.bands, oh_first = (v - n * p.bands) * p.band_oh;
+                const int rows_out = min(p.band_oh, a.oh - oh_first);
+                const int ir0 = oh_first * S, rows_in = (rows_out - 1) * S + K;   // input rows (incl. padding rows) of the walk
+                for (int ir = ir0; ir < ir0 + rows_in; ++ir, ++g) {
                     const int slot = g & (DEPTH - 1);
                     mbar_wait(empty(slot), ((g / DEPTH) & 1) ^ 1);
                     mbar_expect_tx(full(slot), (uint32_t)p.tx_bytes);
                     tma_load_4d(ring + slot * p.row_bytes, &p.tm_x, full(slot), c0, ow0 * S - a.pl, ir - a.pt, n);
                 }
+            }
         }
     } else if (warp < n_act) {
         // ===================== consumers
@@ -164,8 +170,10 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
         int slot = 0;                                      // ring slot of the next row this warp loads ...
         uint32_t phase = 0;                                // ... and its barrier phase
         const long long y_row = (long long)a.ow * a.y_cs;  // elements between two output rows
-        for (int n = blockIdx.z; n < a.n; n += p.zsplit) {
-            T* yrow = reinterpret_cast<T*>(a.y) + ((long long)n * a.oh * a.ow + (ok ? ow : 0)) * a.y_cs + a.y_co;
+        for (int v = blockIdx.z; v < n_units; v += p.zsplit) {
+            const int n = v / p.bands, band = v - n * p.bands, oh_first = band * p.band_oh;
+            const int rows_out = min(p.band_oh, a.oh - oh_first);
+            T* yrow = reinterpret_cast<T*>(a.y) + (((long long)n * a.oh + oh_first) * a.ow + (ok ? ow : 0)) * a.y_cs + a.y_co;
             float2 psum = make_float2(0.f, 0.f);
             float2 xw[K][NI];                              // [row slot][input column]
             auto load_row = [&](float2 (&row)[NI]) {
@@ -181,11 +189,11 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
             };
 #pragma unroll
             for (int ky = 0; ky < K - S; ++ky) load_row(xw[ky]);
-            for (int oh0 = 0; oh0 < a.oh; oh0 += K) {
+            for (int oh0 = 0; oh0 < rows_out; oh0 += K) {  // output rows relative to the band
 #pragma unroll
                 for (int u = 0; u < K; ++u) {
                     const int oh = oh0 + u;
-                    if (oh < a.oh) {                       // block-uniform
+                    if (oh < rows_out) {                   // block-uniform
                         // window row ky of output row oh lives in slot (ky + S*u) % K; the S new rows arrive now
 #pragma unroll
                         for (int j = 0; j < S; ++j) load_row(xw[(K - S + j + S * u) % K]);
@@ -224,7 +232,7 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
                         for (int r = 0; r < n_act * SUB; ++r) sum += pool_s[r * CH + ch];
                         // one slab per column strip: plain stores, summed in slab order by se_fc (reproducible);
                         // more strips than slabs (very wide maps): atomics on slab 0
-                        if (p.pool_write) a.pool_sum[((long long)blockIdx.x * a.n + n) * a.c_p + c0 + ch] = sum;
+                        if (p.pool_write) a.pool_sum[((long long)(blockIdx.x * p.bands + band) * a.n + n) * a.c_p + c0 + ch] = sum;
                         else atomicAdd(a.pool_sum + (long long)n * a.c_p + c0 + ch, sum);
                     }
                 }
@@ -232,6 +240,43 @@ __global__ void __launch_bounds__(32 * (DwCols<K>::value + 1), 1) dwconv_tma_ker
             }
         }
     }
+}
+
+// Row bands and image groups.  One block per SM is resident (registers).  A block's fixed cost (weights, barrier init,
+// ring fill) is a few rows' worth of work, so small maps let one block walk several images, and large maps at a small
+// batch are cut into row bands (each band re-reads K - S input rows): pick (bands, z) that minimises
+// waves x (walks per block x (rows per walk + 3) + 6).  Pure host arithmetic on 148 SMs: ede_dwconv2d_pool_parts must
+// give the same answer without a device (the squeeze slabs are per column strip AND band).
+static void pick_bands_z(const EdeDwConv& a, int units, int* bands_out, int* z_out) {
+    const char* b_env = getenv("EDE_DW_BANDS");               // debug / tests: force the number of row bands
+    static const char* z_env = getenv("EDE_DW_ZSPLIT");       // debug / tests: force the number of walk groups
+    const int sms = 148;
+    struct Memo { int n, oh, units, b, z; };
+    thread_local Memo memo[16];
+    thread_local int memo_n = 0;
+    if (!(b_env && *b_env) && !(z_env && *z_env))
+        for (int i = 0; i < memo_n; ++i)
+            if (memo[i].n == a.n && memo[i].oh == a.oh && memo[i].units == units) { *bands_out = memo[i].b; *z_out = memo[i].z; return; }
+    int best_b = 1, best_z = a.n;
+    double best_cost = 1e30;
+    // bands only where whole images cannot fill the machine (measured: with >= one walk per SM the band split of the
+    // 114x152x32 map of ENB0-HU batch 64 cost 8 %: more halo rows, same occupancy)
+    const int max_b = b_env && *b_env ? std::max(1, std::min(a.oh, atoi(b_env)))
+                                      : (units * a.n >= sms ? 1 : std::max(1, a.oh / 12));
+    for (int b = (b_env && *b_env) ? max_b : 1; b <= max_b; ++b) {
+        const int band_oh = ceil_div(a.oh, b);
+        if (ceil_div(a.oh, band_oh) != b) continue;           // every band owns at least one row
+        const int walks = a.n * b;
+        for (int z = 1; z <= walks; ++z) {
+            const double waves = (double)ceil_div(units * z, sms);
+            const double cost = waves * ((double)ceil_div(walks, z) * (band_oh + 3.0) + 6.0);
+            if (cost < best_cost - 1e-9) { best_cost = cost; best_b = b; best_z = z; }
+        }
+    }
+    if (z_env && *z_env) best_z = std::max(1, std::min(a.n * best_b, atoi(z_env)));
+    else if (!(b_env && *b_env)) { memo[memo_n % 16] = Memo{a.n, a.oh, units, best_b, best_z}; if (memo_n < 16) ++memo_n; }
+    *bands_out = best_b;
+    *z_out = best_z;
 }
 
 // consumer warps per block: as many as registers allow, sized to waste as little of the last tile as possible
@@ -254,9 +299,12 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st, int* strips
     memset(&p, 0, sizeof(p));
     p.a = a;
     p.cols = pick_cols(ceil_div(a.ow, SUB * NC), DwCols<K>::value);
-    if (strips_out) {                                     // host query: column strips (grid.x) of this shape
+    const int units = ceil_div(a.ow, p.cols * SUB * NC) * ceil_div(a.c_p, CH);
+    int bands = 1, best_z = a.n;
+    pick_bands_z(a, units, &bands, &best_z);
+    if (strips_out) {                                     // host query: squeeze slabs = column strips (grid.x) x row bands
         if (p.cols * SUB * NC * S + K - S > 256) return 1;
-        *strips_out = ceil_div(a.ow, p.cols * SUB * NC);
+        *strips_out = ceil_div(a.ow, p.cols * SUB * NC) * bands;
         return 0;
     }
     EncodeTiledFn enc = get_encode_fn();
@@ -291,24 +339,12 @@ static int dwconv_tma_launch_ch(const EdeDwConv& a, cudaStream_t st, int* strips
         }
         attr_set[dev] = true;
     }
-    // One block per SM is resident (registers).  A block's fixed cost (weights, barrier init, ring fill) is a few
-    // rows' worth of work, so small maps let one block walk several images: pick the z split that minimises
-    // waves x (images per block x rows + fixed cost).
-    const int units = ceil_div(a.ow, p.cols * SUB * NC) * ceil_div(a.c_p, CH);
-    const int sms = std::max(1, sm_count[dev]);
-    int best_z = a.n;
-    double best_cost = 1e30;
-    for (int z = 1; z <= a.n; ++z) {
-        const double waves = (double)ceil_div(units * z, sms);
-        const double cost = waves * ((double)ceil_div(a.n, z) * (a.oh + 3.0) + 6.0);   // +3 rows per image switch
-        if (cost < best_cost - 1e-9) { best_cost = cost; best_z = z; }
-    }
-    static const char* z_env = getenv("EDE_DW_ZSPLIT");       // debug / tests: force the number of image groups
-    if (z_env && *z_env) best_z = std::max(1, std::min(a.n, atoi(z_env)));
     p.zsplit = best_z;
+    p.bands = bands;
+    p.band_oh = ceil_div(a.oh, bands);
     dim3 grid((unsigned)ceil_div(a.ow, p.cols * SUB * NC), (unsigned)ceil_div(a.c_p, CH), (unsigned)p.zsplit);
     if (grid.y > 65535u || grid.z > 65535u || smem > 200 * 1024) return 1;
-    p.pool_write = a.pool_sum != nullptr && a.pool_parts > 1 && (int)grid.x <= a.pool_parts;
+    p.pool_write = a.pool_sum != nullptr && a.pool_parts > 1 && (int)grid.x * bands <= a.pool_parts;
     if (launch_pdl(dwconv_tma_kernel<T, K, S, CH, NC>, grid, dim3(32 * (p.cols + 1)), (size_t)smem, st, p) != cudaSuccess) {
         (void)cudaGetLastError();
         return 1;

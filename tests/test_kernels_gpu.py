@@ -561,6 +561,53 @@ def test_upconv_streaming_form_matches_the_separable_form(cuda, lib, shape):
     assert torch.allclose(ys[0], ys[1], rtol=1e-5, atol=2e-5), float((ys[0] - ys[1]).abs().max())
 
 
+@pytest.mark.parametrize("bands", [2, 3])
+@pytest.mark.parametrize("dt", [A.BF16X2, A.F32_TO_BF16X2, A.BF16])
+@pytest.mark.parametrize("k,s,pad", [(3, 1, (1, 1, 1, 1)), (5, 2, (1, 1, 2, 2)), (5, 1, (2, 2, 2, 2))])
+def test_dwconv_row_bands(cuda, lib, dt, k, s, pad, bands, monkeypatch):
+    """The row-streaming depthwise kernel cut into row bands per image (small batches of large maps: ENB4-LR 192x192 at
+    batch 8 ran 24 blocks on 148 SMs): every band re-reads its K - S halo rows, the squeeze sums land in one slab per
+    (column strip, band) and add up to the unsplit result."""
+    g = torch.Generator().manual_seed(k + s + bands)
+    n, c, h, w = 2, 40, 61, 47
+    c_p = P.ceil8(c)
+    pt, pl, pb, pr = pad
+    oh, ow = (h + pt + pb - k) // s + 1, (w + pl + pr - k) // s + 1
+    x = torch.randn(n, c, h, w, generator=g).to(cuda)
+    wt = (torch.randn(c, 1, k, k, generator=g) / k).to(cuda)
+    scale, shift = (0.5 + torch.rand(c, generator=g)).to(cuda), (0.2 * torch.randn(c, generator=g)).to(cuda)
+    if dt == A.BF16X2:
+        xin = split_store(nhwc(x, c_p, A.F32))
+    elif dt == A.F32_TO_BF16X2:
+        xin = nhwc(x, c_p, A.F32)
+    else:
+        xin = nhwc(x, c_p, dt)
+    lanes = P.identity_map(c, c_p)
+    wk = torch.zeros(k * k, c_p, device=cuda)
+    wk[:, :c] = wt.reshape(c, k * k).t()
+    sc, sf = P.place_lanes(scale, lanes), P.place_lanes(shift, lanes)
+    outs = []
+    for forced in (None, bands):
+        if forced is None:
+            monkeypatch.setenv("EDE_DW_BANDS", "1")
+        else:
+            monkeypatch.setenv("EDE_DW_BANDS", str(forced))
+        y = torch.zeros(n, oh, ow, (2 if dt != A.BF16 else 1) * c_p, device=cuda, dtype=torch.bfloat16)
+        a = A.EdeDwConv(x=xin.data_ptr(), y=y.data_ptr(), w=wk.data_ptr(), scale=sc.data_ptr(), shift=sf.data_ptr(),
+                        pool_sum=None, n=n, h=h, w_=w, c_p=c_p, x_cs=c_p, x_co=0, oh=oh, ow=ow, y_cs=c_p, y_co=0, k=k, s=s,
+                        pt=pt, pl=pl, act=A.ACT_SWISH, dtype=dt)
+        parts = int(lib.ede_dwconv2d_pool_parts(C.byref(a)))
+        pool = torch.zeros(parts, n, c_p, device=cuda)
+        a.pool_sum, a.pool_parts = pool.data_ptr(), parts
+        A.check(lib.ede_dwconv2d(C.byref(a), stream()), "ede_dwconv2d")
+        torch.cuda.synchronize()
+        outs.append((y.clone(), pool.sum(0), parts))
+    (y1, p1, parts1), (yb, pb_, partsb) = outs
+    assert partsb == parts1 * bands, (parts1, partsb)
+    assert torch.equal(y1, yb)                                     # same arithmetic per output, another walk order
+    assert torch.allclose(p1, pb_, rtol=1e-5, atol=1e-3)
+
+
 def test_se_scale_fp32_in_split_out(cuda, lib):
     """ede_se_scale with EDE_F32_TO_BF16X2: the gate multiply reads the depthwise kernel's fp32 lanes and writes the split
     lanes the project conv consumes (late MBConv blocks, where the gate is not folded into the weights)."""
@@ -605,3 +652,52 @@ def test_tapsum_one_channel_conv(cuda, lib, k, hw):
     assert float(got[..., 1:].abs().sum()) == 0.0
     a.kh = a.kw = 7                                      # 49 taps: more than z holds / a block stages per pixel
     assert lib.ede_tapsum(C.byref(a), stream()) == -1
+
+
+@pytest.mark.parametrize("n,c,csq,parts,fold", [(3, 150, 6, 1, False), (8, 672, 28, 3, False), (5, 96, 4, 2, True),
+                                               (2, 1152, 48, 1, True)])
+def test_se_fc_cluster_matches_one_block_per_image(cuda, lib, n, c, csq, parts, fold, monkeypatch):
+    """ede_se_fc across a thread-block cluster (hidden units exchanged through distributed shared memory, gate channels
+    and the weight fold split over the CTAs) == the one-block-per-image kernel, bit for bit: gate, cleared squeeze slabs
+    and the per-image gate-scaled project weights; the gate also against an fp64 reference."""
+    g = torch.Generator().manual_seed(n * 7 + csq)
+    c_p = P.ceil8(c) + 8
+    pool0 = torch.zeros(parts, n, c_p)
+    pool0[:, :, :c] = torch.rand(parts, n, c, generator=g) * 50
+    w1 = torch.zeros(csq, c_p); w1[:, :c] = torch.randn(csq, c, generator=g) / c ** 0.5
+    w2t = torch.zeros(csq, c_p); w2t[:, :c] = torch.randn(csq, c, generator=g) / csq ** 0.5
+    b1 = 0.1 * torch.randn(csq, generator=g)
+    b2 = torch.zeros(c_p); b2[:c] = 0.1 * torch.randn(c, generator=g)
+    rows, cols, passes = 32, 2 * c_p, 2                      # a split-input project conv: columns = doubled lanes
+    w_src = (torch.randn(passes, rows, cols, generator=g) * 0.1).to(torch.bfloat16)
+    dev = lambda t: t.to(cuda)                              # noqa: E731
+    w1d, w2d, b1d, b2d, wsd = dev(w1), dev(w2t), dev(b1), dev(b2), dev(w_src)
+    outs = []
+    for knob in ("0", "8", "2"):
+        monkeypatch.setenv("EDE_SE_FC_CLUSTER", knob)
+        pool = dev(pool0.clone())
+        gate = torch.full((n, c_p), float("nan"), device=cuda)
+        w_dst = torch.full((n, passes, rows, cols), float("nan"), device=cuda, dtype=torch.bfloat16)
+        f = A.EdeSeFc(pool_sum=pool.data_ptr(), w1=w1d.data_ptr(), b1=b1d.data_ptr(), w2=w2d.data_ptr(), b2=b2d.data_ptr(),
+                      gate=gate.data_ptr(), n=n, c=c, c_p=c_p, csq=csq, inv_hw=1.0 / 266, clear_pool=1, w2_transposed=1,
+                      pool_parts=parts, w_src=wsd.data_ptr() if fold else None, w_dst=w_dst.data_ptr() if fold else None,
+                      w_rows=rows, w_cols=cols, w_passes=passes, w_split=1)
+        A.check(lib.ede_se_fc(C.byref(f), stream()), "ede_se_fc")
+        torch.cuda.synchronize()
+        assert float(pool.abs().sum()) == 0.0               # slabs cleared for the next forward
+        outs.append((gate.cpu(), w_dst.cpu() if fold else None))
+    for gate_k, wd_k in outs[1:]:
+        assert torch.equal(outs[0][0], gate_k)
+        if fold:
+            assert torch.equal(outs[0][1].view(torch.int16), wd_k.view(torch.int16))
+    mean = pool0.double().sum(0)[:, :c] / 266
+    hid = mean @ w1[:, :c].double().t() + b1.double()
+    hid = hid * torch.sigmoid(hid)
+    gref = torch.sigmoid(hid @ w2t[:, :c].double() + b2[:c].double())
+    assert torch.allclose(outs[0][0][:, :c].double(), gref, rtol=1e-4, atol=1e-5) and float(outs[0][0][:, c:].abs().sum()) == 0
+    if fold:                                                # column ci of the weights scaled by the gate of its lane
+        lane = (torch.arange(cols) // 16) * 8 + torch.arange(cols) % 8
+        gcol = outs[0][0][:, lane]                          # [n, cols]
+        ref = (w_src[0].float() + w_src[1].float()).unsqueeze(0) * gcol.unsqueeze(1)
+        got = outs[0][1][:, 0].float() + outs[0][1][:, 1].float()
+        assert torch.allclose(got, ref, rtol=2e-5, atol=1e-7)
