@@ -133,3 +133,20 @@ def test_tile_picker_shares_the_pixel_box_between_weight_passes(lib, monkeypatch
     monkeypatch.setenv("EDE_UMMA_SHARE_PASSES", "0")
     cfg = A.umma_config(deep)
     assert cfg.b_stage_bytes == cfg.n_pad * cfg.ck * 2
+
+
+def test_dwconv_pool_parts_counts_row_bands(lib, monkeypatch):
+    """ede_dwconv2d_pool_parts (host only): one squeeze slab per column strip and row band of the row-streaming kernel.
+    Bands appear only where whole images cannot fill 148 SMs (ENB4-LR 192x192x48 at batch 8), not at batch 64."""
+    def parts(n, h, w, c_p, k=3, s=1):
+        a = A.EdeDwConv(x=8, y=8, w=8, scale=8, shift=8, pool_sum=None, n=n, h=h, w_=w, c_p=c_p, x_cs=c_p, x_co=0,
+                        oh=h // s, ow=w // s, y_cs=c_p, y_co=0, k=k, s=s, pt=k // 2, pl=k // 2, act=A.ACT_SWISH,
+                        dtype=A.F32_TO_BF16X2)
+        return int(lib.ede_dwconv2d_pool_parts(ctypes.byref(a)))
+    monkeypatch.setenv("EDE_DW_BANDS", "1")
+    strips_small, strips_big = parts(8, 192, 192, 48), parts(64, 114, 152, 32)
+    monkeypatch.delenv("EDE_DW_BANDS")
+    assert parts(8, 192, 192, 48) > strips_small and parts(8, 192, 192, 48) % strips_small == 0
+    assert parts(64, 114, 152, 32) == strips_big
+    monkeypatch.setenv("EDE_DW_BANDS", "3")
+    assert parts(64, 114, 152, 32) == 3 * strips_big
