@@ -249,7 +249,7 @@ def per_op_times(plan, dev, reps=3):
     return out
 
 
-KIND_NAMES = {2: "dwconv_tma_kernel / dwconv_tile_kernel", 4: "se_scale_kernel", 5: "resize_kernel", 6: "maxpool_kernel", 7: "eltwise_kernel",
+KIND_NAMES = {2: "dwconv_tma_kernel / dwconv_tile_kernel", 4: "se_scale_kernel", 5: "resize_rows_kernel / resize_kernel", 6: "maxpool_kernel", 7: "eltwise_kernel",
               8: "nchw_to_nhwc_kernel", 9: "nhwc_to_nchw_kernel", 11: "upconv_rows/cols_kernel", 12: "stem_conv_kernel"}
 
 
