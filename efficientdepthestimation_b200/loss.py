@@ -25,7 +25,11 @@ def _check_pair(pred: torch.Tensor, label: torch.Tensor):
 
 
 def loss_metric_sums(pred: torch.Tensor, label: torch.Tensor, out: torch.Tensor = None) -> torch.Tensor:
-    """16 fp64 partial sums (layout in include/ede.h) ACCUMULATED into `out` (device tensor); async."""
+    """16 fp64 partial sums (layout in include/ede.h) ACCUMULATED into `out` (device tensor); async.
+
+    Accumulating several batches into one `out` means one NaN prediction poisons sums [0..7] of the whole run; the
+    reference's AverageMeter drops only the offending batch (ReSIDE/util.py:131).  To keep that behaviour pass a fresh
+    `out` per batch (the default) and feed it to ``MetricsTracker.update_from_sums`` -- the tracker checks per batch."""
     pred, label = _check_pair(pred, label)
     if out is None:
         out = torch.zeros(16, dtype=torch.float64, device=pred.device)
