@@ -1076,6 +1076,11 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
     EdeUmmaCfg best{};
     double best_time = 1e300;
     const bool unpacked_ok = a.w_pack_g <= 1;            // -1: caller asks which packing to prepack for
+    // Weight boxes of the pixels-on-M candidates are charged at 40 B/clk, not 27: every CTA streams the SAME weights (L2
+    // hits, no DRAM behind them) and the wide convs of ResNet-50's decoder were measured at ~50 B/clk of TMA ingest with
+    // N = 256 tiles the 27 B/clk model had rejected (D.up2 / D.up3 of RN50-HU: 0.71 -> 0.65 / 0.63 ms; sum of the plan's
+    // ops 11.85 -> 11.59 ms, ENB4-HU 4.56 -> 4.50, ENB0-HU unchanged).  EDE_UMMA_WBPC overrides.
+    const double w_bpc = (double)env_int("EDE_UMMA_WBPC", 40);
     // contention factors on top of the isolated MMA rates (TMA fills and the MMA operand reads share the
     // 128 B/clk of shared-memory bandwidth; measured on the decoder convs with tools/cta_timeline.py)
     const double F_NOSWAP = 1.5, F_SWAP = 1.3;
@@ -1104,7 +1109,7 @@ static void umma_config(const EdeConv& a, EdeUmmaCfg& c) {
                 const long long tiles = (long long)cand.tiles_w * cand.tiles_h * n_img * n_tiles;
                 const double rounds = (double)ceil_div((int)std::min<long long>(tiles, 1 << 30), NUM_SMS_MODEL);
                 const double mma = (double)taps_w * cand.m_tiles * ks_total * t_mma;
-                const double mem = (a_bytes_tile + b_bytes_tile) / L2_BYTES_PER_CLK_PER_SM;
+                const double mem = a_bytes_tile / L2_BYTES_PER_CLK_PER_SM + b_bytes_tile / w_bpc;
                 const double epi = cand.m_tiles * 128.0 * n_pad * EPI_CYCLES_PER_ROW_COL * 4.0 + 600.0;
                 // operand ring too shallow to cover the L2 latency (~1500 clk) -> exposed waits
                 const double per_stage = mma / std::max(1, n_chunks * taps_w);
